@@ -1,0 +1,224 @@
+"""CPU oracle for the stereo hot path -- TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline / reference arm may
+import this package.  The product (``multiview_b200``) never does.
+
+Two layers live here:
+
+* ``libmvoracle.so`` (``sgbm_oracle.c``, ``image_oracle.c``, ``geom_oracle.c``): the plain-C
+  restatement of the reference algorithm, each function citing the reference file:line it follows.
+* ``cv2ref``: thin calls into Python ``cv2`` (OpenCV 4.13.0 in this image), i.e. the same
+  third-party dependency the reference links (pinned 4.4.0 there), used to PIN the restatement for
+  a1-a4 (remap, grey, blur, StereoSGBM).  The fp64 geometry (a6-a10) has no runnable reference:
+  parity unpinned (see geom_oracle.c header and DESIGN.md).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libmvoracle.so")
+_SRC = ["sgbm_oracle.c", "image_oracle.c", "geom_oracle.c"]
+
+
+def build(force: bool = False) -> str:
+    """Compile the C oracle (gcc, -ffp-contract=off).  Returns the .so path."""
+    srcs = [os.path.join(_HERE, s) for s in _SRC]
+    stale = force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs)
+    if stale:
+        subprocess.check_call(["make", "-s", "-B", "-C", _HERE, "libmvoracle.so"])
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = ctypes.CDLL(build())
+        _lib.orc_point_cloud.restype = ctypes.c_int
+    return _lib
+
+
+class SgbmParams(ctypes.Structure):
+    """Mirror of StereoSGBMDisparity::Params (stereosgbm_disp.hpp:23-33), OpenCV setter order."""
+
+    _fields_ = [(n, ctypes.c_int) for n in ("block", "disp12_max_diff", "min_disp", "num_disp", "speckle_win",
+                                            "speckle_range", "prefilter_cap", "uniqueness", "mode", "p1", "p2")]
+
+    @classmethod
+    def reference_defaults(cls, num_disp=96, mode=3):
+        return cls(13, 596, 1, num_disp, 600, 250, 54, 3, mode, 22, 1000)
+
+
+class Bcam(ctypes.Structure):
+    _fields_ = [("krr_inv", ctypes.c_double * 9 * 2), ("c", ctypes.c_double * 3 * 2)]
+
+
+class HistParams(ctypes.Structure):
+    _fields_ = [("hist_sz", ctypes.c_float), ("min_z", ctypes.c_float), ("max_z", ctypes.c_float),
+                ("weighting", ctypes.c_int), ("use_still", ctypes.c_int)]
+
+
+def _p(a):
+    return ctypes.c_void_p(a.ctypes.data) if a is not None else None
+
+
+def _sz(v):
+    return ctypes.c_size_t(int(v))
+
+
+def sgbm_dims(p: SgbmParams, W: int):
+    mn, w1 = ctypes.c_int(), ctypes.c_int()
+    ok = lib().orc_sgbm_dims(ctypes.byref(p), W, ctypes.byref(mn), ctypes.byref(w1))
+    return bool(ok), mn.value, w1.value
+
+
+def sgbm_compute(p: SgbmParams, L: np.ndarray, R: np.ndarray, taps: bool = False):
+    """StereoSGBM::compute restatement.  Returns disp16 (H,W) int16, or a dict with taps."""
+    L = np.ascontiguousarray(L, np.uint8)
+    R = np.ascontiguousarray(R, np.uint8)
+    H, W = L.shape
+    ok, minx1, w1 = sgbm_dims(p, W)
+    if not ok:
+        raise ValueError("image too narrow for the disparity range")
+    disp = np.empty((H, W), np.int16)
+    C = S1 = S = raw = None
+    if taps:
+        C = np.empty((H, w1, p.num_disp), np.int16)
+        S1 = np.empty_like(C)
+        S = np.empty_like(C)
+        raw = np.empty((H, W), np.int16)
+    rc = lib().orc_sgbm_compute(ctypes.byref(p), _p(L), _p(R), W, H, _sz(W), _p(disp), _p(C), _p(S1), _p(S), _p(raw))
+    if rc:
+        raise RuntimeError(f"orc_sgbm_compute rc={rc}")
+    if taps:
+        return {"disp": disp, "C": C, "S1": S1, "S": S, "raw": raw, "minX1": minx1, "W1": w1}
+    return disp
+
+
+def disp_to_float(disp16: np.ndarray) -> np.ndarray:
+    d = np.ascontiguousarray(disp16, np.int16)
+    out = np.empty(d.shape, np.float32)
+    lib().orc_disp_to_float(_p(d), d.shape[1], d.shape[0], _p(out))
+    return out
+
+
+def median3_s16(a):
+    a = np.ascontiguousarray(a, np.int16)
+    out = np.empty_like(a)
+    H, W = a.shape
+    lib().orc_median3_s16(_p(a), _sz(2 * W), W, H, _p(out), _sz(2 * W))
+    return out
+
+
+def filter_speckles(a, new_val, max_size, max_diff):
+    a = np.array(a, np.int16, order="C")
+    H, W = a.shape
+    lib().orc_filter_speckles_s16(_p(a), _sz(2 * W), W, H, int(new_val), int(max_size), int(max_diff))
+    return a
+
+
+def remap_cubic_bgr8(src, mapx, mapy, border=(255, 255, 255)):
+    src = np.ascontiguousarray(src, np.uint8)
+    mapx = np.ascontiguousarray(mapx, np.float32)
+    mapy = np.ascontiguousarray(mapy, np.float32)
+    sh, sw, _ = src.shape
+    h, w = mapx.shape
+    dst = np.empty((h, w, 3), np.uint8)
+    b = (ctypes.c_uint8 * 3)(*border)
+    lib().orc_remap_cubic_bgr8(_p(src), sw, sh, _sz(sw * 3), _p(mapx), _p(mapy), _sz(w * 4), w, h, b, _p(dst), _sz(w * 3))
+    return dst
+
+
+def bgr2gray(src):
+    src = np.ascontiguousarray(src, np.uint8)
+    h, w, _ = src.shape
+    dst = np.empty((h, w), np.uint8)
+    lib().orc_bgr2gray(_p(src), _sz(w * 3), w, h, _p(dst), _sz(w))
+    return dst
+
+
+def gauss_blur_u8(img, n=31, sigma=2.15):
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    dst = np.empty_like(img)
+    rc = lib().orc_gauss_blur_u8(_p(img), _sz(w), w, h, int(n), ctypes.c_double(sigma), _p(dst), _sz(w))
+    if rc:
+        raise RuntimeError(f"orc_gauss_blur_u8 rc={rc}")
+    return dst
+
+
+def presmooth(img, sigma=2.15):
+    """Disparity::calculate prologue, disparity.cpp:106-155: grey, then the 31x31 blur TWICE."""
+    g = bgr2gray(img) if img.ndim == 3 else np.ascontiguousarray(img, np.uint8)
+    if sigma > 0.0:
+        for _ in range(2):
+            g = gauss_blur_u8(g, 31, sigma)
+    return g
+
+
+def bcam_init(q, t, baseline, K) -> Bcam:
+    out = Bcam()
+    q = (ctypes.c_double * 4)(*q)
+    t = (ctypes.c_double * 3)(*t)
+    Kc = (ctypes.c_double * 9)(*np.asarray(K, np.float64).ravel())
+    lib().orc_bcam_init(q, t, ctypes.c_double(baseline), Kc, ctypes.byref(out))
+    return out
+
+
+def solve3d(b: Bcam, x0, x1, y):
+    out = (ctypes.c_double * 3)()
+    lib().orc_solve3d(ctypes.byref(b), ctypes.c_double(x0), ctypes.c_double(x1), ctypes.c_double(y), out)
+    return np.array(out[:])
+
+
+def point_cloud(b: Bcam, disp: np.ndarray, left_is_ref=True):
+    disp = np.ascontiguousarray(disp, np.float32)
+    h, w = disp.shape
+    Xs = np.empty((h * w, 3), np.float64)
+    xy = np.empty((h * w, 2), np.int32)
+    lookup = np.empty((h, w), np.int32)
+    C = np.empty(3, np.float64)
+    n = lib().orc_point_cloud(ctypes.byref(b), _p(disp), _sz(w * 4), w, h, int(left_is_ref), _p(Xs), _p(xy), _p(lookup), _p(C))
+    return {"Xs": Xs[:n].copy(), "xy": xy[:n].copy(), "lookup": lookup, "C": C, "N": n}
+
+
+def hist_dims(aabb, hist_sz):
+    w, h = ctypes.c_int(), ctypes.c_int()
+    a = (ctypes.c_double * 4)(*aabb)
+    lib().orc_hist_dims(a, ctypes.c_float(hist_sz), ctypes.byref(w), ctypes.byref(h))
+    return w.value, h.value
+
+
+def floor_hist_camera(hp: HistParams, et, aabb, cam_center, Xs, xy, labels=None, still_score=None):
+    """et = (tx,ty,tz, qx,qy,qz,qw, scale); aabb = (left, top, right, bottom)."""
+    Xs = np.ascontiguousarray(Xs, np.float64)
+    xy = np.ascontiguousarray(xy, np.int32)
+    hw, hh = hist_dims(aabb, hp.hist_sz)
+    hist = np.empty((hh, hw), np.float32)
+    etc = (ctypes.c_double * 8)(*et)
+    a = (ctypes.c_double * 4)(*aabb)
+    cc = (ctypes.c_double * 3)(*cam_center)
+    lw = lh = nl = 0
+    if labels is not None:
+        labels = np.ascontiguousarray(labels, np.int32)
+        lh, lw = labels.shape
+        still_score = np.ascontiguousarray(still_score, np.float64)
+        nl = still_score.shape[0]
+    lib().orc_floor_hist_camera(ctypes.byref(hp), etc, a, cc, _p(Xs), _p(xy), Xs.shape[0], _p(labels), lw, lh,
+                                _p(still_score), nl, _p(hist), hw, hh)
+    return hist
+
+
+def hist_sum(cam_hists):
+    ch = np.ascontiguousarray(cam_hists, np.float32)
+    n, hh, hw = ch.shape
+    out = np.empty((hh, hw), np.float32)
+    lib().orc_hist_sum(_p(ch), n, hw, hh, _p(out))
+    return out

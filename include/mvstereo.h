@@ -1,0 +1,204 @@
+/*
+ * mvstereo.h -- C ABI of libmvstereo: the B200 (sm_100a) implementation of multiview's per-frame
+ * stereo reconstruction hot path (rectify -> SGM disparity -> point cloud -> floor histogram).
+ *
+ * The reference has no FFI for this path; the operator boundary is the four static call sites that
+ * its pipeline nodes make.  Each entry point below names the reference
+ * interface it replaces.  Paths are relative to multiview/multiview_cpp/src/perceive/.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative mvs_status otherwise; nothing throws or aborts
+ *     (the reference's nodes are noexcept and return nullptr on failure, pipeline-task.hpp:266-272);
+ *   - a context owns one CUDA stream and a grow-only device arena; contexts are independent, so the
+ *     pipeline's pool threads use one context each (execute() "MUST BE REENTRANT", pipeline-task.hpp:292-295);
+ *     a single context must not be used from two threads at once;
+ *   - pointers are HOST pointers unless the name ends in _dev; steps are in bytes (cv::Mat::step);
+ *   - there is no CPU fallback: without a CUDA device mvs_ctx_create fails.
+ */
+#ifndef MVSTEREO_H
+#define MVSTEREO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mvs_ctx mvs_ctx;
+
+typedef enum {
+    MVS_OK = 0,
+    MVS_ERR_ARG = -1,         /* bad argument (null pointer, non-positive size, unsupported enum) */
+    MVS_ERR_CUDA = -2,        /* a CUDA runtime call failed; see mvs_last_error */
+    MVS_ERR_UNSUPPORTED = -3, /* parameters outside the supported range (see mvs_sgbm_check) */
+    MVS_ERR_NOMEM = -4
+} mvs_status;
+
+/* cv::INTER_* values accepted by mvs_remap_bgr8 (calc_rectified.hpp:17-22). */
+enum { MVS_INTER_NEAREST = 0, MVS_INTER_LINEAR = 1, MVS_INTER_CUBIC = 2 };
+
+/* cv::StereoSGBM modes (stereosgbm_disp.cpp:55-80): 0 = 5-path, 1 = 8-path full DP, 3 = 4-path HH4. */
+enum { MVS_MODE_SGBM = 0, MVS_MODE_HH = 1, MVS_MODE_HH4 = 3 };
+
+/* FloorHistogram::WeightingMethod (cost-functions/floor-histogram.hpp:20). */
+enum { MVS_WGT_NONE = 0, MVS_WGT_NORM = 1, MVS_WGT_QUADRANCE = 2 };
+
+/* -- context ------------------------------------------------------------------------------------ */
+int mvs_ctx_create(int device, mvs_ctx** out);
+void mvs_ctx_destroy(mvs_ctx* ctx);
+const char* mvs_last_error(const mvs_ctx* ctx); /* never NULL */
+int mvs_sync(mvs_ctx* ctx);                     /* wait for the context's stream */
+void* mvs_stream(mvs_ctx* ctx);                 /* the cudaStream_t, for callers that enqueue their own work */
+const char* mvs_version(void);
+
+/* -- a1: rectification -----------------------------------------------------------------------------
+ * Replaces cv::remap(in, rectified, mapx, mapy, interp, BORDER_CONSTANT, Scalar(255,255,255)) in
+ * calc_rectified::Task::execute, pipeline/nodes/calc_rectified.cpp:109-115.
+ * src: BGR 8UC3 sw x sh; mapx/mapy: CV_32FC1 w x h; dst: BGR 8UC3 w x h.  Bit-exact for INTER_CUBIC,
+ * INTER_LINEAR and INTER_NEAREST. */
+int mvs_remap_bgr8(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
+                   const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border_bgr[3],
+                   uint8_t* dst, size_t dstep);
+
+/* -- a2: grey + pre-smoothing ----------------------------------------------------------------------
+ * Replaces the prologue of Disparity::calculate, cost-functions/disparity/disparity.cpp:106-155:
+ * cv::cvtColor(BGR2GRAY) when channels == 3, then cv::GaussianBlur(31x31, sigma) applied TWICE when
+ * sigma > 0.  dst is 8UC1 w x h.  Bit-exact. */
+int mvs_presmooth(mvs_ctx* ctx, const uint8_t* src, int channels, int w, int h, size_t step, double sigma,
+                  uint8_t* dst, size_t dstep);
+
+/* -- a3/a4: semi-global matching -------------------------------------------------------------------
+ * Field order and meaning follow StereoSGBMDisparity::Params,
+ * cost-functions/disparity/strategies/stereosgbm_disp.hpp:23-33 (sg_SAD_window_size, sg_12_max_diff,
+ * sg_min_disparity, sg_num_disparities, sg_speckle_window_size, sg_speckle_range, sg_prefilter_cap,
+ * sg_uniqueness_ratio, sg_mode, sg_p1, sg_p2). */
+typedef struct {
+    int block, disp12_max_diff, min_disp, num_disp, speckle_win, speckle_range, prefilter_cap, uniqueness,
+        mode, p1, p2;
+} mvs_sgbm_params;
+
+/* Returns MVS_OK when the parameter set is inside the bit-exact domain for a w-pixel-wide image:
+ * num_disp a positive multiple of 16 and <= 256, min_disp >= 0, odd block in [1, 13] such that
+ * block^2 * (2*ftzero + 63) + P2 <= 32767 (16-bit costs cannot wrap), mode in {0, 1, 3}. */
+int mvs_sgbm_check(const mvs_sgbm_params* p, int w, int h);
+
+/* Replaces cv::StereoSGBM::compute(left, right, disp16S) as called from
+ * StereoSGBMDisparity::calculate, strategies/stereosgbm_disp.cpp:121-125 (left is the reference image).
+ * l, r: 8UC1 w x h; disp16: CV_16S w x h, Q4 fixed point, invalid = (min_disp - 1) * 16.  Bit-exact. */
+int mvs_sgbm_compute16(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
+                       size_t step, int16_t* disp16, size_t dstep);
+
+/* Replaces Disparity::calculate(p, l_is_ref = true, STEREO_SGBM, image0, image1, out, confidence),
+ * cost-functions/disparity/disparity.cpp:68-182 with strategies/stereosgbm_disp.cpp:84-156:
+ * grey + double blur (a2), StereoSGBM (a3), then out = |d16| / 16, values > 150 -> 0 (:141-150).
+ * l, r: 8UC1 or 8UC3 (channels = 1 | 3); out: CV_32FC1 w x h.  Bit-exact. */
+int mvs_disparity_sgbm(mvs_ctx* ctx, const mvs_sgbm_params* p, double presmooth_sigma, const uint8_t* l,
+                       const uint8_t* r, int channels, int w, int h, size_t step, float* out, size_t ostep);
+
+/* -- a6/a7: point cloud -----------------------------------------------------------------------------
+ * The 24 doubles of BinocularCamera that the device needs: KRR_inv_[2] (row-major 3x3) and C_[2],
+ * geometry/projective/binocular-camera.hpp (members filled by binocular-camera.cpp:682-785). */
+typedef struct {
+    double krr_inv[2][9];
+    double c[2][3];
+} mvs_bcam;
+
+/* Replaces PointCloud::init(disparity, left_is_reference, bino_cam), geometry/point-cloud.cpp:10-72
+ * (solve3d: geometry/projective/binocular-camera.cpp:908-927).  disp: CV_32FC1 w x h.
+ * Xs: capacity w*h*3 doubles (std::vector<Vector3>), xy: capacity w*h*2 int32 (std::vector<Point2>),
+ * lookup: w*h int32, row stride w (IntImage).  *n_out receives N.  xy/lookup/N bit-exact; Xs and
+ * centroid within 1e-4 relative (fp64 evaluated without FMA, centroid summed in a different order). */
+int mvs_point_cloud(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, size_t step, int w, int h,
+                    int left_is_ref, double* Xs, int32_t* xy, int32_t* lookup, int32_t* n_out, double centroid[3]);
+
+/* -- a9/a10: floor histogram ------------------------------------------------------------------------
+ * Subset of FloorHistogram::Params used per point, cost-functions/floor-histogram.hpp:28-36. */
+typedef struct {
+    float hist_sz, min_z, max_z;
+    int weighting; /* MVS_WGT_* */
+    int use_still; /* apply_slic_still_weights */
+} mvs_hist_params;
+
+/* ensure_floor_hist_dims, cost-functions/floor-histogram.cpp:19-35.  aabb = {left, top, right, bottom}. */
+int mvs_hist_dims(const double aabb[4], float hist_sz, int* hw, int* hh);
+
+/* Replaces process_camera_i inside FloorHistogram::calculate, cost-functions/floor-histogram.cpp:197-275
+ * (histogram part; the super-pixel centroid table :269-286 is out of scope).
+ * et = {tx,ty,tz, qx,qy,qz,qw, scale} of EuclideanTransform (geometry/euclidean-transform.hpp:121-124);
+ * cam_center = translations[cam] (pipeline/nodes/floor_hist.cpp:122); labels (int32 lw x lh, row stride lw)
+ * and still_score (n_labels doubles) may be NULL.  cam_hist: float hw x hh, row stride hw, overwritten.
+ * Counts (MVS_WGT_NONE without still weights) are bit-exact; weighted sums are float accumulations in a
+ * different order (<= 1e-5 relative). */
+int mvs_floor_hist_camera(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
+                          const double cam_center[3], const double* Xs, const int32_t* xy, int32_t n,
+                          const int32_t* labels, int lw, int lh, const double* still_score, int n_labels,
+                          float* cam_hist, int hw, int hh);
+
+/* Replaces `hist += camera_info[cam].hist` over cameras, cost-functions/floor-histogram.cpp:296-300.
+ * cam_hists: n_cams consecutive hw x hh float images, summed in camera order. */
+int mvs_hist_sum(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int hh, float* hist);
+
+/* -- device-resident frame path ----------------------------------------------------------------------
+ * One camera-frame through a1 -> a10 without leaving the GPU: what calc_rectified[2c],[2c+1] ->
+ * disp_init[c] -> disp_map_update[c] (pass-through, disp_map_update.cpp:89-93) -> floor_hist compute
+ * for one camera (pipeline/frame-results.cpp:206-255).  Inputs are host or device pointers (flag);
+ * results stay on the device inside the context until fetched. */
+typedef struct {
+    /* sensor images: BGR 8UC3 sw x sh, byte step sstep; rectification maps CV_32FC1 w x h, byte step mstep */
+    const uint8_t* sensor[2];
+    const float* mapx[2];
+    const float* mapy[2];
+    int sw, sh, w, h;
+    size_t sstep, mstep;
+    int inputs_on_device; /* 0: host pointers (copied in), 1: device pointers (used in place) */
+    mvs_sgbm_params sgbm;
+    double presmooth_sigma;
+    mvs_bcam bcam;
+    mvs_hist_params hist;
+    double et[8];
+    double aabb[4];
+    double cam_center[3];
+} mvs_frame_desc;
+
+/* Device-side results of the last mvs_frame_run on this context slot (valid until the next run on it). */
+typedef struct {
+    const uint8_t* rectified_dev[2]; /* BGR 8UC3 w x h, step 3*w */
+    const int16_t* disp16_dev;       /* CV_16S w x h */
+    const float* disp_dev;           /* CV_32FC1 w x h */
+    const double* Xs_dev;            /* N x 3 */
+    const int32_t* xy_dev;           /* N x 2 */
+    const int32_t* lookup_dev;       /* w x h */
+    const float* cam_hist_dev;       /* hw x hh */
+    const int32_t* n_dev;            /* N (device scalar) */
+    const double* centroid_dev;      /* 3 doubles */
+    int hw, hh;
+} mvs_frame_result;
+
+/* Enqueue the whole path for one camera-frame on the context's stream (asynchronous).  `slot` selects
+ * one of the context's result sets (0 <= slot < 64) so that several camera-frames can be in flight. */
+int mvs_frame_run(mvs_ctx* ctx, int slot, const mvs_frame_desc* desc, mvs_frame_result* out);
+
+/* Copy results of a slot to host buffers (any may be NULL).  Synchronises the stream. */
+int mvs_frame_fetch(mvs_ctx* ctx, int slot, float* disp, size_t dstep, double* Xs, int32_t* xy, int32_t* lookup,
+                    int32_t* n_out, double centroid[3], float* cam_hist);
+
+/* Sum the per-camera histograms of slots [0, n_slots) in slot order into a device buffer owned by the
+ * context (floor-histogram.cpp:296-300); returns its device address (hw*hh floats).  This buffer is what
+ * a multi-GPU caller hands to ncclAllReduce / ncclAllGather. */
+int mvs_frame_hist_sum(mvs_ctx* ctx, int n_slots, float** hist_dev, int* hw, int* hh);
+
+/* -- test taps (kernel-level parity; not used by the reference-facing path) ---------------------------
+ * Run cost volume + aggregation for grey images and copy the 16-bit volumes back ([h][w1][num_disp]).
+ * Either output may be NULL. */
+int mvs_sgbm_volumes(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
+                     size_t step, int16_t* C, int16_t* S, int16_t* raw_disp16);
+
+/* Time (ms, CUDA events on the context stream) spent in the named stage during the last sgbm call:
+ * "cost", "aggregate", "wta", "post".  Returns < 0 when unknown. */
+float mvs_stage_ms(mvs_ctx* ctx, const char* stage);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MVSTEREO_H */

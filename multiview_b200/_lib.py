@@ -1,0 +1,95 @@
+"""ctypes binding of libmvstereo.so (the C ABI declared in include/mvstereo.h).
+
+There is no CPU fallback: if the shared library is missing or no CUDA device is present, every entry
+point raises.  Build with ``python -m multiview_b200.build`` (nvcc, sm_100a).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmvstereo.so")
+
+c_int, c_size_t, c_void_p, c_double, c_float = C.c_int, C.c_size_t, C.c_void_p, C.c_double, C.c_float
+
+
+class SgbmParams(C.Structure):
+    _fields_ = [(n, c_int) for n in ("block", "disp12_max_diff", "min_disp", "num_disp", "speckle_win", "speckle_range",
+                                     "prefilter_cap", "uniqueness", "mode", "p1", "p2")]
+
+
+class Bcam(C.Structure):
+    _fields_ = [("krr_inv", c_double * 9 * 2), ("c", c_double * 3 * 2)]
+
+
+class HistParams(C.Structure):
+    _fields_ = [("hist_sz", c_float), ("min_z", c_float), ("max_z", c_float), ("weighting", c_int), ("use_still", c_int)]
+
+
+class FrameDesc(C.Structure):
+    _fields_ = [("sensor", c_void_p * 2), ("mapx", c_void_p * 2), ("mapy", c_void_p * 2),
+                ("sw", c_int), ("sh", c_int), ("w", c_int), ("h", c_int),
+                ("sstep", c_size_t), ("mstep", c_size_t), ("inputs_on_device", c_int),
+                ("sgbm", SgbmParams), ("presmooth_sigma", c_double), ("bcam", Bcam), ("hist", HistParams),
+                ("et", c_double * 8), ("aabb", c_double * 4), ("cam_center", c_double * 3)]
+
+
+class FrameResult(C.Structure):
+    _fields_ = [("rectified_dev", c_void_p * 2), ("disp16_dev", c_void_p), ("disp_dev", c_void_p), ("Xs_dev", c_void_p),
+                ("xy_dev", c_void_p), ("lookup_dev", c_void_p), ("cam_hist_dev", c_void_p), ("n_dev", c_void_p),
+                ("centroid_dev", c_void_p), ("hw", c_int), ("hh", c_int)]
+
+
+# name -> (restype, argtypes); must list every symbol include/mvstereo.h declares
+SIGNATURES = {
+    "mvs_ctx_create": (c_int, [c_int, C.POINTER(c_void_p)]),
+    "mvs_ctx_destroy": (None, [c_void_p]),
+    "mvs_last_error": (C.c_char_p, [c_void_p]),
+    "mvs_sync": (c_int, [c_void_p]),
+    "mvs_stream": (c_void_p, [c_void_p]),
+    "mvs_version": (C.c_char_p, []),
+    "mvs_remap_bgr8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p, c_void_p, c_size_t, c_int, c_int,
+                               c_int, c_void_p, c_void_p, c_size_t]),
+    "mvs_presmooth": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_size_t, c_double, c_void_p, c_size_t]),
+    "mvs_sgbm_check": (c_int, [C.POINTER(SgbmParams), c_int, c_int]),
+    "mvs_sgbm_compute16": (c_int, [c_void_p, C.POINTER(SgbmParams), c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p,
+                                   c_size_t]),
+    "mvs_disparity_sgbm": (c_int, [c_void_p, C.POINTER(SgbmParams), c_double, c_void_p, c_void_p, c_int, c_int, c_int,
+                                   c_size_t, c_void_p, c_size_t]),
+    "mvs_point_cloud": (c_int, [c_void_p, C.POINTER(Bcam), c_void_p, c_size_t, c_int, c_int, c_int, c_void_p, c_void_p,
+                                c_void_p, C.POINTER(C.c_int32), c_void_p]),
+    "mvs_hist_dims": (c_int, [c_void_p, c_float, C.POINTER(c_int), C.POINTER(c_int)]),
+    "mvs_floor_hist_camera": (c_int, [c_void_p, C.POINTER(HistParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      C.c_int32, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int]),
+    "mvs_hist_sum": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "mvs_frame_run": (c_int, [c_void_p, c_int, C.POINTER(FrameDesc), C.POINTER(FrameResult)]),
+    "mvs_frame_fetch": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, C.POINTER(C.c_int32),
+                                c_void_p, c_void_p]),
+    "mvs_frame_hist_sum": (c_int, [c_void_p, c_int, C.POINTER(c_void_p), C.POINTER(c_int), C.POINTER(c_int)]),
+    "mvs_sgbm_volumes": (c_int, [c_void_p, C.POINTER(SgbmParams), c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p,
+                                 c_void_p, c_void_p]),
+    "mvs_stage_ms": (c_float, [c_void_p, C.c_char_p]),
+}
+
+_lib = None
+
+
+class MvsError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen libmvstereo.so and set the prototypes.  Raises if the library is missing (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise MvsError(f"{LIB_PATH} is missing: build it with `python -m multiview_b200.build` (there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib

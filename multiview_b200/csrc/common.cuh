@@ -1,0 +1,103 @@
+// Internal declarations shared by the libmvstereo translation units (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/mvstereo.h"
+
+#define MVS_MAX_SLOTS 64
+
+// Grow-only named device buffers: allocated on first use, reused on every later frame, freed with the
+// context.  Replaces the reference's per-call cudaMalloc/cudaFree (strategies/sgm_disp.cpp:36-60,173).
+struct Arena {
+    struct Buf { void* p = nullptr; size_t cap = 0; };
+    std::map<std::string, Buf> bufs;
+    size_t total = 0;
+};
+
+struct StageTimer {
+    cudaEvent_t beg = nullptr, end = nullptr;
+    bool used = false;
+};
+
+struct FrameSlot {
+    int w = 0, h = 0, hw = 0, hh = 0;
+    bool valid = false;
+};
+
+struct mvs_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    Arena arena;
+    char err[512];
+    std::map<std::string, StageTimer> timers;
+    FrameSlot slots[MVS_MAX_SLOTS];
+    int16_t* cubic_tab_dev = nullptr;  // 32*32*16 Q15 bicubic weights
+    int sm_count = 148;
+};
+
+int mvs_fail(mvs_ctx* ctx, int code, const char* fmt, ...);
+void* arena_get(mvs_ctx* ctx, const char* name, size_t bytes);  // nullptr on failure (error recorded)
+void stage_begin(mvs_ctx* ctx, const char* stage);
+void stage_end(mvs_ctx* ctx, const char* stage);
+
+#define MVS_CUDA(ctx, call)                                                                         \
+    do {                                                                                            \
+        cudaError_t e__ = (call);                                                                   \
+        if (e__ != cudaSuccess)                                                                     \
+            return mvs_fail(ctx, MVS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
+                            __FILE__, __LINE__);                                                    \
+    } while (0)
+
+#define MVS_LAUNCH_CHECK(ctx, name)                                                                 \
+    do {                                                                                            \
+        cudaError_t e__ = cudaGetLastError();                                                       \
+        if (e__ != cudaSuccess)                                                                     \
+            return mvs_fail(ctx, MVS_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e__)); \
+    } while (0)
+
+#define MVS_ARENA(ctx, T, var, name, count)                                   \
+    T* var = (T*)arena_get(ctx, name, sizeof(T) * (size_t)(count));          \
+    if (!var) return MVS_ERR_NOMEM
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+// ---- geometry of the SGBM volumes ------------------------------------------------------------------
+struct SgbmGeom {
+    int W, H, D, minD, minX1, W1;
+    int Dp;  // disparities per pixel in the device volumes (D rounded up to a multiple of 64)
+    int SW2, SH2, ftzero, P1, P2, ur, d12, INV;
+    int mode;
+    size_t cells() const { return (size_t)H * W1 * Dp; }
+};
+int sgbm_geom(mvs_ctx* ctx, const mvs_sgbm_params* p, int w, int h, SgbmGeom* g);
+
+// ---- device-pointer stage entry points (all asynchronous on ctx->stream) ------------------------------
+int remap_bgr8_dev(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
+                   const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border[3], uint8_t* dst,
+                   size_t dstep);
+int presmooth_dev(mvs_ctx* ctx, const char* tag, const uint8_t* src, int channels, int w, int h, size_t step,
+                  double sigma, uint8_t* dst, size_t dstep);
+// grey images (step == w) -> disparity16 (step == w*2); volumes stay in the arena ("sgbm.C", "sgbm.S")
+int sgbm_compute16_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
+                       int16_t* disp16, int16_t* raw16 /* optional pre-median tap */);
+int disp_to_float_dev(mvs_ctx* ctx, const int16_t* d16, int w, int h, float* out);
+int point_cloud_dev(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, int w, int h, int left_is_ref, double* Xs,
+                    int32_t* xy, int32_t* lookup, int32_t* n_dev, double* centroid_dev);
+int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
+                          const double cam_center[3], const double* Xs, const int32_t* xy, const int32_t* n_dev,
+                          int n_host /* used when n_dev == nullptr */, const int32_t* labels, int lw, int lh,
+                          const double* still, int n_labels, float* cam_hist, int hw, int hh);
+int hist_sum_dev(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int hh, float* hist);
+
+// stage kernels of the SGBM chain (cost.cu, aggregate.cu, wta_post.cu)
+int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, const uint8_t* r, int16_t* C);
+int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);
+int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16);
+int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, const int16_t* raw16, int16_t* disp16);

@@ -1,0 +1,121 @@
+// Context, error reporting, device arena, stage timers.
+#include <stdarg.h>
+
+#include <new>
+
+#include "common.cuh"
+
+static const char* kVersion = "mvstereo-b200 0.1 (sm_100a)";
+
+extern "C" const char* mvs_version(void) { return kVersion; }
+
+int mvs_fail(mvs_ctx* ctx, int code, const char* fmt, ...)
+{
+    if (ctx) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+void* arena_get(mvs_ctx* ctx, const char* name, size_t bytes)
+{
+    Arena::Buf& b = ctx->arena.bufs[name];
+    if (bytes == 0) bytes = 256;
+    if (b.cap >= bytes) return b.p;
+    if (b.p) {
+        // growing: earlier work on the stream may still use the old block
+        cudaStreamSynchronize(ctx->stream);
+        cudaFree(b.p);
+        ctx->arena.total -= b.cap;
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    size_t cap = (bytes + 255) & ~(size_t)255;
+    cudaError_t e = cudaMalloc(&b.p, cap);
+    if (e != cudaSuccess) {
+        b.p = nullptr;
+        mvs_fail(ctx, MVS_ERR_NOMEM, "cudaMalloc(%zu) for '%s' failed: %s", cap, name, cudaGetErrorString(e));
+        return nullptr;
+    }
+    b.cap = cap;
+    ctx->arena.total += cap;
+    return b.p;
+}
+
+void stage_begin(mvs_ctx* ctx, const char* stage)
+{
+    StageTimer& t = ctx->timers[stage];
+    if (!t.beg) {
+        cudaEventCreate(&t.beg);
+        cudaEventCreate(&t.end);
+    }
+    cudaEventRecord(t.beg, ctx->stream);
+}
+
+void stage_end(mvs_ctx* ctx, const char* stage)
+{
+    StageTimer& t = ctx->timers[stage];
+    if (!t.end) return;
+    cudaEventRecord(t.end, ctx->stream);
+    t.used = true;
+}
+
+extern "C" float mvs_stage_ms(mvs_ctx* ctx, const char* stage)
+{
+    if (!ctx || !stage) return -1.f;
+    auto it = ctx->timers.find(stage);
+    if (it == ctx->timers.end() || !it->second.used) return -1.f;
+    if (cudaEventSynchronize(it->second.end) != cudaSuccess) return -1.f;
+    float ms = -1.f;
+    if (cudaEventElapsedTime(&ms, it->second.beg, it->second.end) != cudaSuccess) return -1.f;
+    return ms;
+}
+
+extern "C" int mvs_ctx_create(int device, mvs_ctx** out)
+{
+    if (!out) return MVS_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) return MVS_ERR_CUDA;
+    if (cudaSetDevice(device) != cudaSuccess) return MVS_ERR_CUDA;
+    mvs_ctx* ctx = new (std::nothrow) mvs_ctx();
+    if (!ctx) return MVS_ERR_NOMEM;
+    ctx->device = device;
+    ctx->err[0] = 0;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        return MVS_ERR_CUDA;
+    }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    *out = ctx;
+    return MVS_OK;
+}
+
+extern "C" void mvs_ctx_destroy(mvs_ctx* ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto& kv : ctx->arena.bufs)
+        if (kv.second.p) cudaFree(kv.second.p);
+    for (auto& kv : ctx->timers) {
+        if (kv.second.beg) cudaEventDestroy(kv.second.beg);
+        if (kv.second.end) cudaEventDestroy(kv.second.end);
+    }
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" const char* mvs_last_error(const mvs_ctx* ctx) { return ctx ? ctx->err : "null context"; }
+
+extern "C" int mvs_sync(mvs_ctx* ctx)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MVS_OK;
+}
+
+extern "C" void* mvs_stream(mvs_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }

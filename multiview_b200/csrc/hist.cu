@@ -1,0 +1,161 @@
+// a9/a10: floor-histogram binning of one camera's point cloud and the camera sum
+// (reference: cost-functions/floor-histogram.cpp:19-35,197-300; floor-histogram.hpp:90-96;
+//  geometry/euclidean-transform.hpp:121-124; geometry/quaternion.hpp:126-156,205-213,274-277).
+// fp64 geometry compiled with --fmad=false (bin = round(...) flips on last-ulp differences), fp32 weights.
+#include <math.h>
+
+#include "common.cuh"
+
+struct HistArgs {
+    double et[8];   // tx,ty,tz, qx,qy,qz,qw, scale
+    double aabb[4]; // left, top, right, bottom
+    double cc[3];   // camera centre used by the distance weights
+    double hist_sz, min_z, max_z;
+    int weighting, use_still, lw, lh, n_labels, hw, hh;
+};
+
+struct Q { double x, y, z, w; };
+__device__ __forceinline__ Q qmul(Q a, Q b)  // quaternion.hpp:205-213
+{
+    Q c;
+    c.x = a.y * b.z - a.z * b.y + a.x * b.w + a.w * b.x;
+    c.y = a.z * b.x - a.x * b.z + a.y * b.w + a.w * b.y;
+    c.z = a.x * b.y - a.y * b.x + a.z * b.w + a.w * b.z;
+    c.w = a.w * b.w - a.x * b.x - a.y * b.y - a.z * b.z;
+    return c;
+}
+
+__global__ void __launch_bounds__(256)
+floor_hist_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __restrict__ xy, const int32_t* n_dev,
+                  int n_host, const int32_t* __restrict__ labels, const double* __restrict__ still,
+                  float* __restrict__ hist)
+{
+    const int n = n_dev ? *n_dev : n_host;
+    // rotation.inverse() = conjugate().normalised()
+    Q q = {a.et[3], a.et[4], a.et[5], a.et[6]};
+    Q inv = {-q.x, -q.y, -q.z, q.w};
+    double mag2 = inv.x * inv.x + inv.y * inv.y + inv.z * inv.z + inv.w * inv.w;
+    if (fabs(mag2 - 1.0) > 1e-9) {
+        double s = 1.0 / sqrt(mag2);
+        inv.x *= s; inv.y *= s; inv.z *= s; inv.w *= s;
+    }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        double X0 = Xs[3 * (size_t)i], X1 = Xs[3 * (size_t)i + 1], X2 = Xs[3 * (size_t)i + 2];
+        Q v = {X0 * a.et[7], X1 * a.et[7], X2 * a.et[7], 0.0};
+        Q r = qmul(qmul(q, v), inv);
+        double Yx = r.x + a.et[0], Yy = r.y + a.et[1], Yz = r.z + a.et[2];
+        double zx = (Yx - a.aabb[0]) / a.hist_sz + 1e-9, zy = (Yy - a.aabb[1]) / a.hist_sz + 1e-9;
+        // int(std::round(.)) of an out-of-int-range double is UB in the reference; clamp keeps such points out
+        double rx = round(zx), ry = round(zy);
+        if (!(rx >= 0.0 && rx < (double)a.hw && ry >= 0.0 && ry < (double)a.hh)) continue;
+        if (Yz < a.min_z || Yz > a.max_z) continue;
+        int bx = (int)rx, by = (int)ry;
+        double dx = X0 - a.cc[0], dy = X1 - a.cc[1], dz = X2 - a.cc[2];
+        double q2 = dx * dx + dy * dy + dz * dz;
+        double wgt = a.weighting == MVS_WGT_NONE ? 1.0 : (a.weighting == MVS_WGT_NORM ? sqrt(q2) : q2);
+        if (a.use_still && labels) {
+            int px = xy[2 * (size_t)i], py = xy[2 * (size_t)i + 1];
+            int label = ((unsigned)px < (unsigned)a.lw && (unsigned)py < (unsigned)a.lh) ? labels[(size_t)py * a.lw + px] : -1;
+            if (label >= 0 && label < a.n_labels) wgt *= 1.0 + 10.0 * still[label];
+        }
+        atomicAdd(hist + (size_t)by * a.hw + bx, (float)wgt);
+    }
+}
+
+__global__ void hist_sum_kernel(const float* __restrict__ cam_hists, int n_cams, size_t n, float* __restrict__ hist)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s = 0.0f;
+    for (int c = 0; c < n_cams; ++c) s += cam_hists[(size_t)c * n + i];  // camera order, like hist += cam_hist
+    hist[i] = s;
+}
+
+extern "C" int mvs_hist_dims(const double aabb[4], float hist_sz, int* hw, int* hh)
+{
+    if (!aabb || !hw || !hh || !(hist_sz > 0.0f)) return MVS_ERR_ARG;
+    double inv = 1.0 / (double)hist_sz;
+    *hh = (int)(ceil((aabb[3] - aabb[1]) * inv) + 1e-9);
+    *hw = (int)(ceil((aabb[2] - aabb[0]) * inv) + 1e-9);
+    return (*hw > 0 && *hh > 0) ? MVS_OK : MVS_ERR_ARG;
+}
+
+int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
+                          const double cam_center[3], const double* Xs, const int32_t* xy, const int32_t* n_dev,
+                          int n_host, const int32_t* labels, int lw, int lh, const double* still, int n_labels,
+                          float* cam_hist, int hw, int hh)
+{
+    HistArgs a;
+    memcpy(a.et, et, sizeof(a.et));
+    memcpy(a.aabb, aabb, sizeof(a.aabb));
+    memcpy(a.cc, cam_center, sizeof(a.cc));
+    a.hist_sz = (double)p->hist_sz; a.min_z = (double)p->min_z; a.max_z = (double)p->max_z;
+    a.weighting = p->weighting; a.use_still = p->use_still && labels && still;
+    a.lw = lw; a.lh = lh; a.n_labels = n_labels; a.hw = hw; a.hh = hh;
+    MVS_CUDA(ctx, cudaMemsetAsync(cam_hist, 0, sizeof(float) * (size_t)hw * hh, ctx->stream));
+    int blocks = ctx->sm_count * 8;
+    floor_hist_kernel<<<blocks, 256, 0, ctx->stream>>>(a, Xs, xy, n_dev, n_host, labels, still, cam_hist);
+    MVS_LAUNCH_CHECK(ctx, "floor_hist_kernel");
+    return MVS_OK;
+}
+
+int hist_sum_dev(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int hh, float* hist)
+{
+    size_t n = (size_t)hw * hh;
+    hist_sum_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(cam_hists, n_cams, n, hist);
+    MVS_LAUNCH_CHECK(ctx, "hist_sum_kernel");
+    return MVS_OK;
+}
+
+extern "C" int mvs_floor_hist_camera(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
+                                     const double cam_center[3], const double* Xs, const int32_t* xy, int32_t n,
+                                     const int32_t* labels, int lw, int lh, const double* still_score, int n_labels,
+                                     float* cam_hist, int hw, int hh)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    int ew = 0, eh = 0;
+    if (!p || !et || !aabb || !cam_center || !cam_hist || n < 0 || (n > 0 && (!Xs || !xy)) ||
+        mvs_hist_dims(aabb, p->hist_sz, &ew, &eh) || ew != hw || eh != hh ||
+        p->weighting < MVS_WGT_NONE || p->weighting > MVS_WGT_QUADRANCE)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_floor_hist_camera: bad argument (hist is %dx%d for these bounds)", ew, eh);
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    MVS_ARENA(ctx, double, dXs, "hist.api.Xs", (size_t)n * 3);
+    MVS_ARENA(ctx, int32_t, dxy, "hist.api.xy", (size_t)n * 2);
+    MVS_ARENA(ctx, float, dh, "hist.api.hist", (size_t)hw * hh);
+    int32_t* dl = nullptr;
+    double* ds = nullptr;
+    if (n > 0) {
+        MVS_CUDA(ctx, cudaMemcpyAsync(dXs, Xs, (size_t)n * 24, cudaMemcpyHostToDevice, s));
+        MVS_CUDA(ctx, cudaMemcpyAsync(dxy, xy, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    }
+    if (labels && still_score && lw > 0 && lh > 0 && n_labels > 0) {
+        dl = (int32_t*)arena_get(ctx, "hist.api.labels", (size_t)lw * lh * 4);
+        ds = (double*)arena_get(ctx, "hist.api.still", (size_t)n_labels * 8);
+        if (!dl || !ds) return MVS_ERR_NOMEM;
+        MVS_CUDA(ctx, cudaMemcpyAsync(dl, labels, (size_t)lw * lh * 4, cudaMemcpyHostToDevice, s));
+        MVS_CUDA(ctx, cudaMemcpyAsync(ds, still_score, (size_t)n_labels * 8, cudaMemcpyHostToDevice, s));
+    }
+    int rc = floor_hist_camera_dev(ctx, p, et, aabb, cam_center, dXs, dxy, nullptr, n, dl, lw, lh, ds, n_labels, dh, hw, hh);
+    if (rc) return rc;
+    MVS_CUDA(ctx, cudaMemcpyAsync(cam_hist, dh, sizeof(float) * (size_t)hw * hh, cudaMemcpyDeviceToHost, s));
+    MVS_CUDA(ctx, cudaStreamSynchronize(s));
+    return MVS_OK;
+}
+
+extern "C" int mvs_hist_sum(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int hh, float* hist)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!cam_hists || !hist || n_cams <= 0 || hw <= 0 || hh <= 0) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_hist_sum: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    size_t n = (size_t)hw * hh;
+    MVS_ARENA(ctx, float, din, "hist.api.cams", n * n_cams);
+    MVS_ARENA(ctx, float, dout, "hist.api.sum", n);
+    cudaStream_t s = ctx->stream;
+    MVS_CUDA(ctx, cudaMemcpyAsync(din, cam_hists, n * n_cams * 4, cudaMemcpyHostToDevice, s));
+    int rc = hist_sum_dev(ctx, din, n_cams, hw, hh, dout);
+    if (rc) return rc;
+    MVS_CUDA(ctx, cudaMemcpyAsync(hist, dout, n * 4, cudaMemcpyDeviceToHost, s));
+    MVS_CUDA(ctx, cudaStreamSynchronize(s));
+    return MVS_OK;
+}

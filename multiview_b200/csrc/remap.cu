@@ -1,0 +1,154 @@
+// a1: rectification remap, bit-exact with cv::remap(INTER_CUBIC, BORDER_CONSTANT) on 8UC3
+// (reference call: pipeline/nodes/calc_rectified.cpp:109-115).
+//
+// OpenCV's fixed-point scheme: map coordinates are rounded to 1/32 pixel, the 4x4 tap weights come
+// from a 32x32 table of Q15 integers whose entries are forced to sum to 32768, and the result is
+// (sum + 2^14) >> 15.  One thread produces one output pixel (3 channels); the 32 KB weight table and
+// the source image are read through L1/L2 (the source footprint of a tile is data dependent).
+#include "common.cuh"
+
+// Host: build the 32x32x16 weight table exactly as OpenCV's initInterTab2D(INTER_CUBIC, fixpt).
+// Compiled with -ffp-contract=off so that the float expressions round like the x86 baseline build.
+static void build_cubic_tab(int16_t* tab)
+{
+    float c[32][4];
+    const float A = -0.75f;
+    for (int i = 0; i < 32; ++i) {
+        float x = (float)i * (1.0f / 32.0f);
+        c[i][0] = ((A * (x + 1) - 5 * A) * (x + 1) + 8 * A) * (x + 1) - 4 * A;
+        c[i][1] = ((A + 2) * x - (A + 3)) * x * x + 1;
+        c[i][2] = ((A + 2) * (1 - x) - (A + 3)) * (1 - x) * (1 - x) + 1;
+        c[i][3] = 1.f - c[i][0] - c[i][1] - c[i][2];
+    }
+    for (int fy = 0; fy < 32; ++fy)
+        for (int fx = 0; fx < 32; ++fx) {
+            int16_t* w = tab + (size_t)(fy * 32 + fx) * 16;
+            int isum = 0;
+            for (int k1 = 0; k1 < 4; ++k1)
+                for (int k2 = 0; k2 < 4; ++k2) {
+                    float v = c[fy][k1] * c[fx][k2];
+                    long q = lrintf(v * 32768.0f);
+                    q = q < -32768 ? -32768 : (q > 32767 ? 32767 : q);
+                    w[k1 * 4 + k2] = (int16_t)q;
+                    isum += (int)q;
+                }
+            if (isum != 32768) {
+                // the correction goes to the largest / smallest of the four central taps
+                int diff = isum - 32768, M = 10, m = 10;
+                for (int k1 = 2; k1 < 4; ++k1)
+                    for (int k2 = 2; k2 < 4; ++k2) {
+                        int i = k1 * 4 + k2;
+                        if (w[i] < w[m])
+                            m = i;
+                        else if (w[i] > w[M])
+                            M = i;
+                    }
+                if (diff < 0)
+                    w[M] = (int16_t)(w[M] - diff);
+                else
+                    w[m] = (int16_t)(w[m] - diff);
+            }
+        }
+}
+
+static int ensure_cubic_tab(mvs_ctx* ctx)
+{
+    if (ctx->cubic_tab_dev) return MVS_OK;
+    MVS_ARENA(ctx, int16_t, tab, "remap.cubic_tab", 1024 * 16);
+    std::vector<int16_t> host(1024 * 16);
+    build_cubic_tab(host.data());
+    MVS_CUDA(ctx, cudaMemcpyAsync(tab, host.data(), host.size() * sizeof(int16_t), cudaMemcpyHostToDevice, ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host vector goes out of scope
+    ctx->cubic_tab_dev = tab;
+    return MVS_OK;
+}
+
+// cvRound(float) on x86 (cvtss2si): round-half-even; NaN and out-of-range give INT_MIN.
+__device__ __forceinline__ int cv_round_f(float v)
+{
+    return (fabsf(v) < 2147483648.0f) ? __float2int_rn(v) : (int)0x80000000;
+}
+__device__ __forceinline__ int sat16_i(int v) { return max(-32768, min(32767, v)); }
+
+__global__ void __launch_bounds__(256)
+remap_cubic_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t sstep, const float* __restrict__ mapx,
+                        const float* __restrict__ mapy, size_t mstep, int w, int h, const int16_t* __restrict__ tab,
+                        int b0, int b1, int b2, uint8_t* __restrict__ dst, size_t dstep)
+{
+    int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= w || y >= h) return;
+    float mx = *(const float*)((const char*)mapx + (size_t)y * mstep + (size_t)x * 4);
+    float my = *(const float*)((const char*)mapy + (size_t)y * mstep + (size_t)x * 4);
+    int sx = cv_round_f(mx * 32.0f), sy = cv_round_f(my * 32.0f);
+    int X = sat16_i(sx >> 5) - 1, Y = sat16_i(sy >> 5) - 1;
+    const int4* wp = (const int4*)(tab + (size_t)(((sy & 31) << 5) + (sx & 31)) * 16);
+    int4 wa = __ldg(wp), wb = __ldg(wp + 1);
+    int wraw[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+    int s0 = 0, s1 = 0, s2 = 0;
+    uint8_t* d = dst + (size_t)y * dstep + (size_t)x * 3;
+    if (X >= sw || X + 4 <= 0 || Y >= sh || Y + 4 <= 0) {
+        d[0] = (uint8_t)b0; d[1] = (uint8_t)b1; d[2] = (uint8_t)b2;
+        return;
+    }
+    bool inside = X >= 0 && X + 3 < sw && Y >= 0 && Y + 3 < sh;
+#pragma unroll
+    for (int k1 = 0; k1 < 4; ++k1) {
+        int yy = Y + k1;
+        const uint8_t* row = src + (size_t)yy * sstep;
+#pragma unroll
+        for (int k2 = 0; k2 < 4; ++k2) {
+            int wr = wraw[k1 * 2 + (k2 >> 1)];
+            int wt = (k2 & 1) ? (wr >> 16) : (int)(short)(wr & 0xffff);
+            int xx = X + k2;
+            int v0 = b0, v1 = b1, v2 = b2;
+            if (inside || (yy >= 0 && yy < sh && xx >= 0 && xx < sw)) {
+                const uint8_t* p = row + (size_t)xx * 3;
+                v0 = __ldg(p); v1 = __ldg(p + 1); v2 = __ldg(p + 2);
+            }
+            s0 += wt * v0; s1 += wt * v1; s2 += wt * v2;
+        }
+    }
+    d[0] = (uint8_t)max(0, min(255, (s0 + (1 << 14)) >> 15));
+    d[1] = (uint8_t)max(0, min(255, (s1 + (1 << 14)) >> 15));
+    d[2] = (uint8_t)max(0, min(255, (s2 + (1 << 14)) >> 15));
+}
+
+int remap_bgr8_dev(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
+                   const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border[3], uint8_t* dst,
+                   size_t dstep)
+{
+    if (interp != MVS_INTER_CUBIC)
+        return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "remap: only INTER_CUBIC (the reference default) is implemented");
+    int rc = ensure_cubic_tab(ctx);
+    if (rc) return rc;
+    dim3 grid(cdiv(w, 32), cdiv(h, 8));
+    remap_cubic_bgr8_kernel<<<grid, 256, 0, ctx->stream>>>(src, sw, sh, sstep, mapx, mapy, mstep, w, h,
+                                                           ctx->cubic_tab_dev, border[0], border[1], border[2], dst, dstep);
+    MVS_LAUNCH_CHECK(ctx, "remap_cubic_bgr8_kernel");
+    return MVS_OK;
+}
+
+extern "C" int mvs_remap_bgr8(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
+                              const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border_bgr[3],
+                              uint8_t* dst, size_t dstep)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!src || !mapx || !mapy || !dst || !border_bgr || sw <= 0 || sh <= 0 || w <= 0 || h <= 0 ||
+        sstep < (size_t)sw * 3 || mstep < (size_t)w * 4 || dstep < (size_t)w * 3)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_remap_bgr8: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    MVS_ARENA(ctx, uint8_t, dsrc, "remap.src", (size_t)sh * sw * 3);
+    MVS_ARENA(ctx, float, dmx, "remap.mapx", (size_t)h * w);
+    MVS_ARENA(ctx, float, dmy, "remap.mapy", (size_t)h * w);
+    MVS_ARENA(ctx, uint8_t, ddst, "remap.dst", (size_t)h * w * 3);
+    cudaStream_t s = ctx->stream;
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(dsrc, (size_t)sw * 3, src, sstep, (size_t)sw * 3, sh, cudaMemcpyHostToDevice, s));
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(dmx, (size_t)w * 4, mapx, mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(dmy, (size_t)w * 4, mapy, mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+    int rc = remap_bgr8_dev(ctx, dsrc, sw, sh, (size_t)sw * 3, dmx, dmy, (size_t)w * 4, w, h, interp, border_bgr, ddst,
+                            (size_t)w * 3);
+    if (rc) return rc;
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(dst, dstep, ddst, (size_t)w * 3, (size_t)w * 3, h, cudaMemcpyDeviceToHost, s));
+    MVS_CUDA(ctx, cudaStreamSynchronize(s));
+    return MVS_OK;
+}

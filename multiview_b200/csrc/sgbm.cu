@@ -1,0 +1,133 @@
+// SGBM chain glue: cost volume -> aggregation -> WTA/LR -> median/speckle, and the host-buffer entry points
+// that replace cv::StereoSGBM::compute / Disparity::calculate (strategies/stereosgbm_disp.cpp:84-156,
+// cost-functions/disparity/disparity.cpp:68-182).
+#include "common.cuh"
+
+// unpadded copy [h][w1][D] <- device volume [h][w1][Dp]
+__global__ void unpad_kernel(const int16_t* __restrict__ src, size_t npix, int D, int Dp, int16_t* __restrict__ dst)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix * (size_t)D) return;
+    size_t p = i / D;
+    int d = (int)(i - p * D);
+    dst[i] = src[p * Dp + d];
+}
+
+int sgbm_compute16_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
+                       int16_t* disp16, int16_t* raw16_tap)
+{
+    SgbmGeom g;
+    int rc = sgbm_geom(ctx, p, w, h, &g);
+    if (rc) return rc;
+    MVS_ARENA(ctx, int16_t, C, "sgbm.C", g.cells());
+    MVS_ARENA(ctx, int16_t, S, "sgbm.S", g.cells());
+    int16_t* raw = raw16_tap;
+    if (!raw) {
+        raw = (int16_t*)arena_get(ctx, "sgbm.raw", sizeof(int16_t) * (size_t)w * h);
+        if (!raw) return MVS_ERR_NOMEM;
+    }
+    stage_begin(ctx, "cost");
+    rc = sgbm_cost_volume_dev(ctx, g, l, r, C);
+    stage_end(ctx, "cost");
+    if (rc) return rc;
+    stage_begin(ctx, "aggregate");
+    rc = sgbm_aggregate_dev(ctx, g, C, S);
+    stage_end(ctx, "aggregate");
+    if (rc) return rc;
+    stage_begin(ctx, "wta");
+    rc = sgbm_wta_dev(ctx, g, S, raw);
+    stage_end(ctx, "wta");
+    if (rc) return rc;
+    stage_begin(ctx, "post");
+    rc = sgbm_post_dev(ctx, g, p, raw, disp16);
+    stage_end(ctx, "post");
+    return rc;
+}
+
+static int upload_pair(mvs_ctx* ctx, const uint8_t* l, const uint8_t* r, int channels, int w, int h, size_t step,
+                       uint8_t** dl, uint8_t** dr)
+{
+    size_t rowb = (size_t)w * channels;
+    *dl = (uint8_t*)arena_get(ctx, "sgbm.api.l", rowb * h);
+    *dr = (uint8_t*)arena_get(ctx, "sgbm.api.r", rowb * h);
+    if (!*dl || !*dr) return MVS_ERR_NOMEM;
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(*dl, rowb, l, step, rowb, h, cudaMemcpyHostToDevice, ctx->stream));
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(*dr, rowb, r, step, rowb, h, cudaMemcpyHostToDevice, ctx->stream));
+    return MVS_OK;
+}
+
+extern "C" int mvs_sgbm_compute16(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w,
+                                  int h, size_t step, int16_t* disp16, size_t dstep)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!p || !l || !r || !disp16 || w <= 0 || h <= 0 || step < (size_t)w || dstep < (size_t)w * 2)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_sgbm_compute16: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint8_t *dl, *dr;
+    int rc = upload_pair(ctx, l, r, 1, w, h, step, &dl, &dr);
+    if (rc) return rc;
+    MVS_ARENA(ctx, int16_t, dd, "sgbm.api.disp16", (size_t)w * h);
+    rc = sgbm_compute16_dev(ctx, p, dl, dr, w, h, dd, nullptr);
+    if (rc) return rc;
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(disp16, dstep, dd, (size_t)w * 2, (size_t)w * 2, h, cudaMemcpyDeviceToHost, ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MVS_OK;
+}
+
+extern "C" int mvs_disparity_sgbm(mvs_ctx* ctx, const mvs_sgbm_params* p, double presmooth_sigma, const uint8_t* l,
+                                  const uint8_t* r, int channels, int w, int h, size_t step, float* out, size_t ostep)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!p || !l || !r || !out || w <= 0 || h <= 0 || (channels != 1 && channels != 3) ||
+        step < (size_t)w * channels || ostep < (size_t)w * 4)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_disparity_sgbm: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint8_t *dl, *dr;
+    int rc = upload_pair(ctx, l, r, channels, w, h, step, &dl, &dr);
+    if (rc) return rc;
+    MVS_ARENA(ctx, uint8_t, g0, "sgbm.api.grey0", (size_t)w * h);
+    MVS_ARENA(ctx, uint8_t, g1, "sgbm.api.grey1", (size_t)w * h);
+    MVS_ARENA(ctx, int16_t, dd, "sgbm.api.disp16", (size_t)w * h);
+    MVS_ARENA(ctx, float, df, "sgbm.api.dispf", (size_t)w * h);
+    rc = presmooth_dev(ctx, "l", dl, channels, w, h, (size_t)w * channels, presmooth_sigma, g0, (size_t)w);
+    if (!rc) rc = presmooth_dev(ctx, "r", dr, channels, w, h, (size_t)w * channels, presmooth_sigma, g1, (size_t)w);
+    if (!rc) rc = sgbm_compute16_dev(ctx, p, g0, g1, w, h, dd, nullptr);
+    if (!rc) rc = disp_to_float_dev(ctx, dd, w, h, df);
+    if (rc) return rc;
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(out, ostep, df, (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MVS_OK;
+}
+
+extern "C" int mvs_sgbm_volumes(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
+                                size_t step, int16_t* C, int16_t* S, int16_t* raw_disp16)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!p || !l || !r || w <= 0 || h <= 0 || step < (size_t)w) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_sgbm_volumes: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    SgbmGeom g;
+    int rc = sgbm_geom(ctx, p, w, h, &g);
+    if (rc) return rc;
+    uint8_t *dl, *dr;
+    rc = upload_pair(ctx, l, r, 1, w, h, step, &dl, &dr);
+    if (rc) return rc;
+    MVS_ARENA(ctx, int16_t, dd, "sgbm.api.disp16", (size_t)w * h);
+    MVS_ARENA(ctx, int16_t, draw, "sgbm.api.raw16", (size_t)w * h);
+    rc = sgbm_compute16_dev(ctx, p, dl, dr, w, h, dd, draw);
+    if (rc) return rc;
+    size_t npix = (size_t)g.H * g.W1;
+    MVS_ARENA(ctx, int16_t, tmp, "sgbm.api.unpad", npix * g.D);
+    const char* names[2] = {"sgbm.C", "sgbm.S"};
+    int16_t* outs[2] = {C, S};
+    for (int k = 0; k < 2; ++k) {
+        if (!outs[k]) continue;
+        const int16_t* src = (const int16_t*)arena_get(ctx, names[k], g.cells() * 2);
+        unpad_kernel<<<cdiv(npix * g.D, 256), 256, 0, ctx->stream>>>(src, npix, g.D, g.Dp, tmp);
+        MVS_LAUNCH_CHECK(ctx, "unpad_kernel");
+        MVS_CUDA(ctx, cudaMemcpyAsync(outs[k], tmp, npix * g.D * 2, cudaMemcpyDeviceToHost, ctx->stream));
+        MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    if (raw_disp16) MVS_CUDA(ctx, cudaMemcpyAsync(raw_disp16, draw, (size_t)w * h * 2, cudaMemcpyDeviceToHost, ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MVS_OK;
+}

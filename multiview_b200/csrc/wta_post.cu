@@ -1,0 +1,212 @@
+// a3 (v)-(vii) and a4: winner-take-all with uniqueness, parabola sub-pixel, right-view consistency,
+// 3x3 median, speckle filter and float conversion (reference call sites
+// cost-functions/disparity/strategies/stereosgbm_disp.cpp:121-125 and :141-150).
+#include "common.cuh"
+
+// ---- WTA: one warp per pixel ---------------------------------------------------------------------------------
+// disp2 (the right-view disparity) is a per-row argmin with "first writer in descending x wins ties":
+// realised as atomicMin on key = minS << 16 | (0xFFFF - x), from which the winning d follows as
+// x + minX1 - x2 - minD... (x2 = x + minX1 - d - minD), so no second array is needed.
+template <int NW>
+__global__ void __launch_bounds__(256)
+wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key)
+{
+    __shared__ uint16_t sh[8][NW * 64];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    long long pix = (long long)blockIdx.x * 8 + wib;
+    if (pix >= (long long)g.W1 * g.H) return;
+    int y = (int)(pix / g.W1), x = (int)(pix - (long long)y * g.W1);
+    const uint32_t* Sp = S + (size_t)pix * (NW * 32) + lane * NW;
+    uint32_t w[NW];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) w[j] = Sp[j];
+    // first argmin: min over (S << 16 | d)
+    uint32_t key = 0xffffffffu;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+        uint32_t d0 = (uint32_t)(lane * NW + j) * 2;
+        key = min(key, ((w[j] & 0xffffu) << 16) | d0);
+        key = min(key, (w[j] & 0xffff0000u) | (d0 + 1));
+        ((uint32_t*)sh[wib])[lane * NW + j] = w[j];
+    }
+    key = __reduce_min_sync(0xffffffffu, key);
+    __syncwarp();
+    int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
+    if (minS >= 32767) return;  // every cost saturated: the reference leaves / writes INV here
+    // uniqueness: reject if some d outside best+-1 has S*(100-ur) < minS*100
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+        int d0 = (lane * NW + j) * 2;
+        int s0 = (int)(w[j] & 0xffffu), s1 = (int)(w[j] >> 16);
+        bad |= (d0 < g.D) && (s0 * (100 - g.ur) < minS * 100) && (abs(best - d0) > 1);
+        bad |= (d0 + 1 < g.D) && (s1 * (100 - g.ur) < minS * 100) && (abs(best - d0 - 1) > 1);
+    }
+    if (__any_sync(0xffffffffu, bad)) return;
+    if (lane == 0) {
+        int x2 = x + g.minX1 - best - g.minD;
+        atomicMin(disp2key + (size_t)y * g.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+        int d = best;
+        if (0 < d && d < g.D - 1) {
+            int sm = sh[wib][d - 1], sp = sh[wib][d + 1];
+            int den = max(sm + sp - 2 * minS, 1);
+            d = d * 16 + ((sm - sp) * 16 + den) / (den * 2);
+        } else
+            d *= 16;
+        raw[(size_t)y * g.W + x + g.minX1] = (int16_t)(d + g.minD * 16);
+    }
+}
+
+__global__ void wta_init_kernel(int16_t* raw, uint32_t* disp2key, size_t n, int inv)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    raw[i] = (int16_t)inv;
+    disp2key[i] = 0x7fffffffu;
+}
+
+// left-right check (A.2), in place on raw
+__global__ void lr_check_kernel(int16_t* __restrict__ raw, const uint32_t* __restrict__ disp2key, SgbmGeom g)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x + g.minX1, y = blockIdx.y;
+    if (x >= g.minX1 + g.W1) return;
+    int d1 = raw[(size_t)y * g.W + x];
+    if (d1 == g.INV) return;
+    int dl = d1 >> 4, dh = (d1 + 15) >> 4;
+    int xl = x - dl, xh = x - dh;
+    const uint32_t* row = disp2key + (size_t)y * g.W;
+    auto disp2 = [&](int xx) -> int {
+        uint32_t k = row[xx];
+        if (k == 0x7fffffffu) return g.INV;  // never written: keeps INVALID_DISP_SCALED like the reference
+        int xw = 0xffff - (int)(k & 0xffffu);
+        return xw + g.minX1 - xx;  // = d + minD of the winning left pixel
+    };
+    bool fl = false, fh = false;
+    if (0 <= xl && xl < g.W) { int v = disp2(xl); fl = v >= g.minD && abs(v - dl) > g.d12; }
+    if (0 <= xh && xh < g.W) { int v = disp2(xh); fh = v >= g.minD && abs(v - dh) > g.d12; }
+    if (fl && fh) raw[(size_t)y * g.W + x] = (int16_t)g.INV;
+}
+
+// ---- 3x3 median on s16, replicate border (cv::medianBlur) ---------------------------------------------
+__device__ __forceinline__ void cswap(int& a, int& b) { int t = min(a, b); b = max(a, b); a = t; }
+__global__ void median3_kernel(const int16_t* __restrict__ src, int W, int H, int16_t* __restrict__ dst)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    int v[9];
+#pragma unroll
+    for (int dy = -1; dy <= 1; ++dy) {
+        const int16_t* r = src + (size_t)min(max(y + dy, 0), H - 1) * W;
+#pragma unroll
+        for (int dx = -1; dx <= 1; ++dx) v[(dy + 1) * 3 + dx + 1] = r[min(max(x + dx, 0), W - 1)];
+    }
+    // 19-exchange median-of-9 network
+    cswap(v[1], v[2]); cswap(v[4], v[5]); cswap(v[7], v[8]); cswap(v[0], v[1]); cswap(v[3], v[4]); cswap(v[6], v[7]);
+    cswap(v[1], v[2]); cswap(v[4], v[5]); cswap(v[7], v[8]); cswap(v[0], v[3]); cswap(v[5], v[8]); cswap(v[4], v[7]);
+    cswap(v[3], v[6]); cswap(v[1], v[4]); cswap(v[2], v[5]); cswap(v[4], v[7]); cswap(v[4], v[2]); cswap(v[6], v[4]);
+    cswap(v[4], v[2]);
+    dst[(size_t)y * W + x] = (int16_t)v[4];
+}
+
+// ---- speckle filter (cv::filterSpeckles): 4-connected components via lock-free union-find ------------------
+__device__ __forceinline__ int uf_find(const int* L, int i)
+{
+    int p = L[i];
+    while (p != i) { i = p; p = L[i]; }
+    return i;
+}
+__device__ __forceinline__ void uf_union(int* L, int a, int b)
+{
+    for (int guard = 0; guard < (1 << 24); ++guard) {
+        a = uf_find(L, a);
+        b = uf_find(L, b);
+        if (a == b) return;
+        if (a < b) { int t = a; a = b; b = t; }  // hook the larger root under the smaller
+        int old = atomicMin(L + a, b);
+        if (old == a) return;
+        a = old;
+    }
+}
+__global__ void speckle_init_kernel(int* L, int* cnt, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { L[i] = (int)i; cnt[i] = 0; }
+}
+__global__ void speckle_union_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= W) return;
+    int i = y * W + x, v = img[i];
+    if (v == newVal) return;
+    if (x + 1 < W) { int r = img[i + 1]; if (r != newVal && abs(r - v) <= maxDiff) uf_union(L, i, i + 1); }
+    if (y + 1 < H) { int r = img[i + W]; if (r != newVal && abs(r - v) <= maxDiff) uf_union(L, i, i + W); }
+}
+__global__ void speckle_count_kernel(const int16_t* __restrict__ img, size_t n, int newVal, int* L, int* cnt)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || img[i] == newVal) return;
+    int r = uf_find(L, (int)i);
+    L[i] = r;  // flatten (roots never change after the union kernel)
+    atomicAdd(cnt + r, 1);
+}
+__global__ void speckle_apply_kernel(int16_t* img, size_t n, int newVal, int maxSize, const int* L, const int* cnt)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || img[i] == newVal) return;
+    if (cnt[L[i]] <= maxSize) img[i] = (int16_t)newVal;
+}
+
+__global__ void disp_to_float_kernel(const int16_t* __restrict__ d, size_t n, float* __restrict__ out)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float v = fabsf((float)d[i]) / 16.0f;
+    out[i] = v > 150.0f ? 0.0f : v;
+}
+
+int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16)
+{
+    cudaStream_t s = ctx->stream;
+    size_t n = (size_t)g.W * g.H;
+    MVS_ARENA(ctx, uint32_t, d2, "sgbm.disp2key", n);
+    wta_init_kernel<<<cdiv(n, 256), 256, 0, s>>>(raw16, d2, n, g.INV);
+    int blocks = cdiv((long long)g.W1 * g.H, 8);
+    switch (g.Dp / 64) {
+    case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
+    case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
+    case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
+    case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
+    default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
+    }
+    MVS_LAUNCH_CHECK(ctx, "wta_kernel");
+    lr_check_kernel<<<dim3(cdiv(g.W1, 128), g.H), 128, 0, s>>>(raw16, d2, g);
+    MVS_LAUNCH_CHECK(ctx, "lr_check_kernel");
+    return MVS_OK;
+}
+
+int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, const int16_t* raw16, int16_t* disp16)
+{
+    cudaStream_t s = ctx->stream;
+    size_t n = (size_t)g.W * g.H;
+    median3_kernel<<<dim3(cdiv(g.W, 128), g.H), 128, 0, s>>>(raw16, g.W, g.H, disp16);
+    MVS_LAUNCH_CHECK(ctx, "median3_kernel");
+    if (p->speckle_win > 0) {
+        MVS_ARENA(ctx, int, L, "sgbm.speckle.label", n);
+        MVS_ARENA(ctx, int, cnt, "sgbm.speckle.count", n);
+        int maxDiff = 16 * p->speckle_range;
+        speckle_init_kernel<<<cdiv(n, 256), 256, 0, s>>>(L, cnt, n);
+        speckle_union_kernel<<<dim3(cdiv(g.W, 128), g.H), 128, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L);
+        speckle_count_kernel<<<cdiv(n, 256), 256, 0, s>>>(disp16, n, g.INV, L, cnt);
+        speckle_apply_kernel<<<cdiv(n, 256), 256, 0, s>>>(disp16, n, g.INV, p->speckle_win, L, cnt);
+        MVS_LAUNCH_CHECK(ctx, "speckle kernels");
+    }
+    return MVS_OK;
+}
+
+int disp_to_float_dev(mvs_ctx* ctx, const int16_t* d16, int w, int h, float* out)
+{
+    size_t n = (size_t)w * h;
+    disp_to_float_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(d16, n, out);
+    MVS_LAUNCH_CHECK(ctx, "disp_to_float_kernel");
+    return MVS_OK;
+}

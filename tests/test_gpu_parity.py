@@ -1,0 +1,203 @@
+"""GPU parity tests: every stage of the CUDA path, called through the C ABI, against the CPU oracle.
+
+Bit-exact for integer/byte/index results; point coordinates within 1e-4 relative (north_star)."""
+import numpy as np
+import pytest
+
+import oracle
+from multiview_b200 import api, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(W, H, D, seed, noise=False):
+    if noise:
+        rng = np.random.default_rng(seed)
+        return rng.integers(0, 256, (H, W), dtype=np.uint8), rng.integers(0, 256, (H, W), dtype=np.uint8)
+    l, r = synth.rectified_pair(W, H, D, seed)
+    return oracle.bgr2gray(l), oracle.bgr2gray(r)
+
+
+def _sp(D, mode, block=13, p1=22, p2=1000, ur=3, d12=596, sw=600, sr=250, cap=54, minD=1):
+    return api.StereoSGBMParams(block, d12, minD, D, sw, sr, cap, ur, mode, p1, p2)
+
+
+def _op(sp):
+    return oracle.SgbmParams(sp.sg_SAD_window_size, sp.sg_12_max_diff, sp.sg_min_disparity,
+                                                     sp.sg_num_disparities, sp.sg_speckle_window_size, sp.sg_speckle_range,
+                                                     sp.sg_prefilter_cap, sp.sg_uniqueness_ratio, sp.sg_mode, sp.sg_p1, sp.sg_p2)
+
+
+def test_remap_cubic_bit_exact(ctx):
+    rng = np.random.default_rng(7)
+    for (sw, sh, w, h) in [(128, 96, 128, 96), (200, 150, 160, 120), (64, 48, 80, 60)]:
+        src = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+        mx, my = synth.radial_maps(w, h, 0.3, (1.5, -2.25))
+        mx = (mx * sw / w + rng.normal(0, 0.3, (h, w))).astype(np.float32)
+        my = (my * sh / h + rng.normal(0, 0.3, (h, w))).astype(np.float32)
+        mx[0, 0] = 1e9
+        my[0, 1] = -1e9
+        mx[1, 1] = np.nan
+        got = api.calc_rectified(src, mx, my, ctx=ctx)
+        want = oracle.remap_cubic_bgr8(src, mx, my)
+        assert np.array_equal(got, want), f"remap mismatch {(got != want).sum()} px"
+
+
+def test_presmooth_bit_exact(ctx):
+    rng = np.random.default_rng(8)
+    for (w, h) in [(131, 97), (20, 12), (640, 48)]:
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        for sigma in (2.15, 1.0, 5.0):
+            assert np.array_equal(api.presmooth(img, sigma, ctx=ctx), oracle.presmooth(img, sigma))
+        assert np.array_equal(api.presmooth(img[..., 0].copy(), 2.15, ctx=ctx), oracle.presmooth(img[..., 0].copy(), 2.15))
+        assert np.array_equal(api.presmooth(img, 0.0, ctx=ctx), oracle.bgr2gray(img))
+
+
+@pytest.mark.parametrize("mode", [1, 0, 3])
+@pytest.mark.parametrize("W,H,D", [(72, 40, 16), (200, 64, 64), (240, 50, 96), (300, 48, 128), (420, 36, 256)])
+def test_sgbm_volumes_and_disparity(ctx, mode, W, H, D):
+    for noise in (False, True):
+        L, R = _pair(W, H, D, 100 + D + mode, noise)
+        sp = _sp(D, mode)
+        t = oracle.sgbm_compute(_op(sp), L, R, taps=True)
+        Cg, Sg, rawg = api.StereoSGBMDisparity.volumes(sp, L, R, ctx=ctx)
+        assert np.array_equal(Cg, t["C"]), f"C mismatch {(Cg != t['C']).sum()}"
+        assert np.array_equal(Sg, t["S"]), f"S mismatch {(Sg != t['S']).sum()}"
+        assert np.array_equal(rawg, t["raw"]), f"raw disparity mismatch {(rawg != t['raw']).sum()}"
+        d16 = api.StereoSGBMDisparity.compute16(sp, L, R, ctx=ctx)
+        assert np.array_equal(d16, t["disp"]), f"disp16 mismatch {(d16 != t['disp']).sum()}"
+
+
+@pytest.mark.parametrize("params", [
+    dict(block=3, p1=8, p2=32, ur=0, d12=1, sw=0, sr=0),
+    dict(block=5, p1=8, p2=32, ur=10, d12=2, sw=0, sr=0),
+    dict(block=9, p1=22, p2=1000, ur=3, d12=596, sw=0, sr=0),
+    dict(block=13, p1=22, p2=1000, ur=25, d12=1, sw=50, sr=2),
+    dict(block=11, p1=22, p2=4000, ur=3, d12=596, sw=0, sr=0),
+    dict(block=7, p1=0, p2=0, ur=-1, d12=0, sw=100, sr=1, cap=10),
+    dict(block=5, p1=10, p2=120, ur=5, d12=1, sw=0, sr=0, minD=0),
+    dict(block=5, p1=10, p2=120, ur=5, d12=1, sw=20, sr=1, minD=3),
+])
+def test_sgbm_parameter_matrix(ctx, params):
+    for mode in (1, 0, 3):
+        for noise in (False, True):
+            L, R = _pair(160, 56, 32, 5 + mode, noise)
+            sp = _sp(32, mode, **params)
+            want = oracle.sgbm_compute(_op(sp), L, R)
+            got = api.StereoSGBMDisparity.compute16(sp, L, R, ctx=ctx)
+            assert np.array_equal(got, want), f"mode {mode} noise {noise}: {(got != want).sum()} px differ"
+
+
+def test_disparity_calculate_float(ctx):
+    cam = synth.make_camera(320, 200, 64, config=9)
+    rect = [oracle.remap_cubic_bgr8(cam["sensor"][i], cam["mapx"][i], cam["mapy"][i]) for i in range(2)]
+    p = api.DisparityParams(stereosgbm_params=_sp(64, 1))
+    got = api.Disparity.calculate(p, True, rect[0], rect[1], ctx=ctx)
+    want = oracle.disp_to_float(oracle.sgbm_compute(_op(p.stereosgbm_params), oracle.presmooth(rect[0]), oracle.presmooth(rect[1])))
+    assert got.dtype == np.float32 and np.array_equal(got, want)
+    assert (got > 0).mean() > 0.3
+
+
+def test_unsupported_parameters_fail_loudly(ctx):
+    L, R = _pair(160, 56, 32, 1)
+    for bad in (dict(block=21), dict(p2=30000), dict(block=4)):
+        with pytest.raises(api.MvsError):
+            api.StereoSGBMDisparity.compute16(_sp(32, 1, **bad), L, R, ctx=ctx)
+    with pytest.raises(api.MvsError):
+        api.StereoSGBMDisparity.compute16(_sp(48, 1), L[:, :40].copy(), R[:, :40].copy(), ctx=ctx)  # too narrow
+    with pytest.raises(api.MvsError):
+        api.StereoSGBMDisparity.compute16(_sp(32, 2), L, R, ctx=ctx)  # MODE_SGBM_3WAY not on the path
+
+
+def _cloud_inputs(w=320, h=200, D=64, seed=3):
+    rng = np.random.default_rng(seed)
+    disp = rng.uniform(2.0, 0.8 * D, (h, w)).astype(np.float32)
+    disp[rng.random((h, w)) < 0.3] = 0.0
+    disp[0, :5] = [np.nan, np.inf, -np.inf, -3.5, 0.0]
+    K = synth.intrinsics(w, h)
+    return disp, synth.bcam_quaternion(), synth.BCAM_T, synth.BCAM_BASELINE, K
+
+
+def test_point_cloud_parity(ctx):
+    disp, q, t, bl, K = _cloud_inputs()
+    ob = oracle.bcam_init(q, t, bl, K)
+    want = oracle.point_cloud(ob, disp)
+    bc = api.BinocularCamera.from_c(ob)  # identical 24 doubles on both sides
+    pc = api.PointCloud().init(disp, True, bc, ctx=ctx)
+    assert pc.N() == want["N"]
+    assert np.array_equal(pc.xy, want["xy"]) and np.array_equal(pc.lookup, want["lookup"])
+    rel = np.abs(pc.Xs - want["Xs"]).max() / np.abs(want["Xs"]).max()
+    assert rel <= 1e-4, rel  # north_star tolerance; the no-FMA build is expected to give 0
+    assert np.allclose(pc.C, want["C"], rtol=1e-4, atol=0)
+    # host-side BinocularCamera.init (numpy) agrees with the oracle's restatement
+    bc2 = api.BinocularCamera().init(q, t, bl, K)
+    assert np.allclose(bc2.KRR_inv[1], bc.KRR_inv[1], rtol=1e-9, atol=1e-12)
+    # empty cloud: N == 0, centroid NaN like the reference's 0/0
+    z = api.PointCloud().init(np.zeros((8, 8), np.float32), True, bc, ctx=ctx)
+    assert z.N() == 0 and np.isnan(z.C).all() and (z.lookup == -1).all()
+
+
+def test_floor_histogram_parity(ctx):
+    disp, q, t, bl, K = _cloud_inputs()
+    ob = oracle.bcam_init(q, t, bl, K)
+    want_pc = oracle.point_cloud(ob, disp)
+    aabb = synth.HIST_AABB
+    n_cams = 3
+    ets = [synth.camera_extrinsics(c, n_cams) for c in range(n_cams)]
+    pcs = []
+    for c in range(n_cams):
+        pc = api.PointCloud()
+        pc.Xs, pc.xy = want_pc["Xs"] * (1.0 + 0.1 * c), want_pc["xy"]
+        pcs.append(pc)
+    rng = np.random.default_rng(4)
+    labels = rng.integers(-1, 50, disp.shape).astype(np.int32)
+    still = rng.random(40)
+    for weighting, use_still in [(api.WGT_NONE, False), (api.WGT_NORM, False), (api.WGT_QUADRANCE, True), (api.WGT_NORM, True)]:
+        p = api.FloorHistogramParams(weighting=weighting, apply_slic_still_weights=use_still)
+        fh = api.FloorHistogram()
+        api.FloorHistogram.calculate(p, aabb, n_cams, ets, pcs, [e[:3] for e in ets], fh,
+                                     slic_lookups=[labels] * n_cams if use_still else None,
+                                     still_scores=[still] * n_cams if use_still else None, ctx=ctx)
+        hp = oracle.HistParams(p.hist_sz, p.hist_min_z, p.hist_max_z, weighting, int(use_still))
+        want = [oracle.floor_hist_camera(hp, ets[c], aabb, ets[c][:3], pcs[c].Xs, pcs[c].xy,
+                                         labels if use_still else None, still if use_still else None) for c in range(n_cams)]
+        for c in range(n_cams):
+            assert (want[c] > 0).sum() > 10
+            if weighting == api.WGT_NONE and not use_still:
+                assert np.array_equal(fh.camera_hists[c], want[c])  # counts: bit-exact
+            else:
+                assert np.allclose(fh.camera_hists[c], want[c], rtol=1e-5, atol=1e-3)
+        wsum = oracle.hist_sum(np.stack(want))
+        if weighting == api.WGT_NONE and not use_still:
+            assert np.array_equal(fh.hist, wsum)
+        else:
+            assert np.allclose(fh.hist, wsum, rtol=1e-5, atol=1e-3)
+
+
+def test_frame_path_matches_stagewise_oracle(ctx):
+    W, H, D = 384, 240, 64
+    cam = synth.make_camera(W, H, D, config=2, cam=1, n_cams=4)
+    sp = _sp(D, 1)
+    hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
+    desc = api.make_frame_desc(cam, sp, hp, synth.HIST_AABB)
+    res = api.frame_run(ctx, 0, desc)
+    out = api.frame_fetch(ctx, 0, W, H, res.hw, res.hh)
+    rect = [oracle.remap_cubic_bgr8(cam["sensor"][i], cam["mapx"][i], cam["mapy"][i]) for i in range(2)]
+    want_d = oracle.disp_to_float(oracle.sgbm_compute(_op(sp), oracle.presmooth(rect[0]), oracle.presmooth(rect[1])))
+    assert np.array_equal(out["disp"], want_d)
+    ob = oracle.bcam_init(cam["q"], cam["t"], cam["baseline"], cam["K"])
+    # same calibration doubles on both sides: take them from the descriptor the GPU used
+    ob2 = oracle.Bcam()
+    for i in range(2):
+        for k in range(9):
+            ob2.krr_inv[i][k] = desc.bcam.krr_inv[i][k]
+        for k in range(3):
+            ob2.c[i][k] = desc.bcam.c[i][k]
+    wpc = oracle.point_cloud(ob2, want_d)
+    assert out["N"] == wpc["N"] and np.array_equal(out["xy"], wpc["xy"]) and np.array_equal(out["lookup"], wpc["lookup"])
+    assert np.abs(out["Xs"] - wpc["Xs"]).max() <= 1e-4 * np.abs(wpc["Xs"]).max()
+    ohp = oracle.HistParams(hp.hist_sz, hp.hist_min_z, hp.hist_max_z, 0, 0)
+    wh = oracle.floor_hist_camera(ohp, cam["et"], synth.HIST_AABB, cam["et"][:3], wpc["Xs"], wpc["xy"])
+    assert np.array_equal(out["cam_hist"], wh) and wh.sum() > 100
+    # oracle's own calibration restatement agrees with the host-side numpy one to rounding
+    assert np.allclose(np.array(ob.krr_inv[1][:]), np.array(ob2.krr_inv[1][:]), rtol=1e-9, atol=1e-12)

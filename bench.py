@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py -- stereo frames/s of the hot path (rectify + SGM + cloud + floor_hist) on N B200s.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K --warmup W   # reference CPU path (cv2 + C port)
+
+A step is one pass of the hot path over one batch of synthetic camera-frames (default: the
+BASELINE.json configs[1] shape, 1920x1080, 256 disparities, MODE_HH 8-path).  Work shards by camera:
+every rank processes its own cameras, the per-step floor histograms are summed with NCCL.
+Rank 0 prints ONE JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {  # name -> (W, H, D)
+    "c1": (896, 672, 128),
+    "c2": (1920, 1080, 256),
+    "vga64": (640, 480, 64),
+    "720p128": (1280, 720, 128),
+    "1440p256": (2560, 1440, 256),
+    "4k256": (3840, 2160, 256),
+}
+METRIC = "stereo frames/s (rectify+SGM+cloud+floor_hist)"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+class _CAI:
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"data": (int(ptr), False), "shape": tuple(shape), "typestr": typestr, "version": 2}
+
+
+def sgbm_cells(W, H, D, minD=1):
+    return H * (W - minD - D) * D
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def cpu_frame(cam, D, mode, aabb, threads=None):
+    """The reference's CPU path for one camera-frame: cv2 (its OpenCV calls) for a1-a4, the C port for a6-a10."""
+    import oracle
+    from oracle import cv2ref
+
+    rect = [cv2ref.remap_cubic_bgr8(cam["sensor"][i], cam["mapx"][i], cam["mapy"][i]) for i in range(2)]
+    p = oracle.SgbmParams.reference_defaults(D, mode)
+    disp = cv2ref.disparity_calculate(p, rect[0], rect[1], 2.15)
+    b = oracle.bcam_init(cam["q"], cam["t"], cam["baseline"], cam["K"])
+    pc = oracle.point_cloud(b, disp)
+    hp = oracle.HistParams(0.10, 0.5, 2.0, 0, 0)
+    hist = oracle.floor_hist_camera(hp, cam["et"], aabb, cam["et"][:3], pc["Xs"], pc["xy"])
+    return disp, pc["N"], hist
+
+
+def crop_cam(cam, rows):
+    c = dict(cam)
+    c["sensor"] = [np.ascontiguousarray(s[:rows]) for s in cam["sensor"]]
+    c["mapx"] = [np.ascontiguousarray(m[:rows]) for m in cam["mapx"]]
+    c["mapy"] = [np.ascontiguousarray(m[:rows]) for m in cam["mapy"]]
+    c["H"] = rows
+    return c
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from concurrent.futures import ThreadPoolExecutor
+
+    from multiview_b200 import synth
+    from oracle import cv2ref
+
+    W, H, D = WORKLOADS[args.workload]
+    cores = os.cpu_count() or 1
+    # cv2's MODE_HH / MODE_SGBM are single-threaded inside OpenCV, so the multi-core baseline is one
+    # camera-frame per thread (cv2 releases the GIL), as the reference's thread pool runs cameras in parallel.
+    par = max(1, min(cores, args.ref_threads, int(psutil_avail_gb() // (6.0 * W * H * D / (1920 * 1080 * 256) + 0.5)) or 1))
+    cv2ref.set_threads(1 if par > 1 else cores)
+    cams = [synth.make_camera(W, H, D, config=2, cam=i % 2, frame=0, n_cams=2) for i in range(min(par, 2))]
+    rows = H
+    t0 = time.perf_counter()
+    cpu_frame(crop_cam(cams[0], min(H, 160)), D, args.mode, synth.HIST_AABB)
+    est = (time.perf_counter() - t0) * H / min(H, 160)
+    budget = 200.0 / max(args.steps + args.warmup, 1)
+    if est * 1.3 > budget:
+        rows = int(max(128, min(H, H * budget / (est * 1.3)))) // 8 * 8
+    work = [crop_cam(cams[i % len(cams)], rows) for i in range(par)]
+
+    def step():
+        with ThreadPoolExecutor(par) as ex:
+            list(ex.map(lambda c: cpu_frame(c, D, args.mode, synth.HIST_AABB), work))
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    frames = par * args.steps * rows / H
+    val = frames / dt
+    sample = (f"{par} camera-frame(s) per step in parallel threads, each {W}x{rows} of {W}x{H} rows (throughput scaled by "
+              f"rows/H), D={D}, mode={args.mode}; cv2 {cv2ref._cv2().__version__} remap+cvtColor+2xGaussianBlur+StereoSGBM "
+              f"(the reference's OpenCV calls, IPP off) + C port of PointCloud::init / floor_hist")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1000 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u16", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {W}x{H} stereo pair, {D} disparities, mode {args.mode}, full disp_map+cloud+floor_hist",
+                       "batch_per_step": par},
+            "gpix_disp_per_s": val * W * H * D / 1e9,
+            "cpu_baseline": {"value": val, "unit": "frames/s", "cores": par, "kind": "reference", "sample": sample,
+                             "host_cores": cores},
+            "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def psutil_avail_gb():
+    try:
+        import psutil
+
+        return psutil.virtual_memory().available / 2**30
+    except Exception:
+        return 16.0
+
+
+# ------------------------------------------------------------------------------------------------ CUDA arm
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    from multiview_b200 import api, synth
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    W, H, D = WORKLOADS[args.workload]
+    B = args.batch
+    ctx = api.Context(local_rank)
+    stream = torch.cuda.ExternalStream(ctx.lib.mvs_stream(ctx.h), device=dev)
+    sp = api.StereoSGBMParams(sg_num_disparities=D, sg_mode=args.mode)
+    hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
+    n_cams = world * B
+    cams = [synth.make_camera(W, H, D, config=2, cam=rank * B + b, frame=0, n_cams=n_cams) for b in range(min(B, args.distinct))]
+
+    # pinned host copies (e2e) and device-resident copies (value)
+    host, devt, descs_dev, descs_host = [], [], [], []
+    for cam in cams:
+        hc = dict(cam)
+        hc["sensor"] = [torch.from_numpy(s).pin_memory() for s in cam["sensor"]]
+        dt = {"sensor": [t.to(dev) for t in hc["sensor"]],
+              "mapx": [torch.from_numpy(m).to(dev) for m in cam["mapx"]], "mapy": [torch.from_numpy(m).to(dev) for m in cam["mapy"]]}
+        host.append(hc)
+        devt.append(dt)
+        ptrs = {k: [t.data_ptr() for t in v] for k, v in dt.items()}
+        descs_dev.append(api.make_frame_desc(cam, sp, hp, synth.HIST_AABB, on_device=True, dev_ptrs=ptrs))
+    torch.cuda.synchronize()
+    hw, hh = api.hist_dims(synth.HIST_AABB, hp.hist_sz)
+
+    def hist_reduce():
+        ptr, w_, h_ = C.c_void_p(), C.c_int(), C.c_int()
+        ctx.check(ctx.lib.mvs_frame_hist_sum(ctx.h, B, C.byref(ptr), C.byref(w_), C.byref(h_)), "mvs_frame_hist_sum")
+        t = torch.as_tensor(_CAI(ptr.value, (hh, hw), "<f4"), device=dev)
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.all_reduce(t)  # counts: exact in fp32 in any order
+        return t
+
+    def step_dev():
+        for b in range(B):
+            api.frame_run(ctx, b, descs_dev[b % len(descs_dev)])
+        return hist_reduce()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: inputs resident in HBM --------------------------------------------------------------------
+    for _ in range(args.warmup):
+        step_dev()
+    barrier()
+    l0 = ctx.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clk:
+        e0.record(stream)
+        for _ in range(args.steps):
+            hist_t = step_dev()
+        e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ctx.launch_count() - l0
+    tmax = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms = float(tmax.item())
+    frames = world * B * args.steps
+    value = frames / (ms / 1000.0)
+    hist_total = float(hist_t.sum().item())
+
+    # ---- per-stage device times (CUDA events inside the library, on the launching stream) -----------------
+    stages = ["rectify", "presmooth", "cost", "aggregate", "wta", "post", "cloud", "hist"]
+    acc = {s: [] for s in stages}
+    for _ in range(max(3, min(args.steps, 10))):
+        api.frame_run(ctx, 0, descs_dev[0])
+        ctx.sync()
+        for s in stages:
+            acc[s].append(ctx.stage_ms(s))
+    stage_ms = {s: float(np.mean(v)) for s, v in acc.items()}
+    cells = sgbm_cells(W, H, D)
+    peak, peak_src = peaks()
+    agg_bytes = 8.0 * cells  # read C + write S forward, read C + read S backward
+    achieved = agg_bytes / (stage_ms["aggregate"] / 1000.0) / 1e9
+    roofline = {"bound": "hbm", "kernel": "SGM aggregation stage (all launches of sgbm_aggregate_dev)", "achieved": achieved,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "algorithmic_bytes_per_frame": agg_bytes, "ms_per_frame": stage_ms["aggregate"], "peak_source": peak_src,
+                "frac_of_8TBs_nominal": achieved / 8000.0}
+
+    # ---- e2e: host buffers in, host results out, through the C ABI ----------------------------------------------
+    descs_host = []
+    for hc in host:
+        d = api.make_frame_desc({**hc, "sensor": [t.numpy() for t in hc["sensor"]]}, sp, hp, synth.HIST_AABB)
+        descs_host.append(d)
+    # rectification maps are per-camera constants (get_xy_mapping is computed once per video and cached by the DAG,
+    # get_xy_mapping.cpp:59), so they stay on the device; sensor images are the per-frame input.
+    for b, d in enumerate(descs_host):
+        for i in range(2):
+            d.mapx[i] = devt[b]["mapx"][i].data_ptr()
+            d.mapy[i] = devt[b]["mapy"][i].data_ptr()
+    out_disp = [torch.empty((H, W), dtype=torch.float32).pin_memory() for _ in range(B)]
+    out_hist = [torch.empty((hh, hw), dtype=torch.float32).pin_memory() for _ in range(B)]
+    out_cen = np.empty(3)
+    nout = C.c_int32()
+
+    def step_e2e():
+        for b in range(B):
+            d = descs_host[b % len(descs_host)]
+            dd = api.FrameDesc.from_buffer_copy(d)  # host (pinned) sensor pointers, device-resident maps
+            dd.inputs_on_device, dd.maps_on_device = 0, 1
+            api.frame_run(ctx, b, dd)
+            ctx.check(ctx.lib.mvs_frame_fetch(ctx.h, b, C.c_void_p(out_disp[b].data_ptr()), W * 4, None, None, None, C.byref(nout),
+                                              C.c_void_p(out_cen.ctypes.data), C.c_void_p(out_hist[b].data_ptr())), "mvs_frame_fetch")
+        hist_reduce()
+        torch.cuda.synchronize()
+
+    for _ in range(min(args.warmup, 3)):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t2 = torch.tensor([e2e_s], device=dev)
+    if world > 1:
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+    e2e_val = frames / float(t2.item())
+    h2d = B * 2 * H * W * 3
+    d2h = B * (H * W * 4 + hh * hw * 4 + 4 + 24)
+
+    line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16",
+            "data": "synthetic",
+            "config": {"workload": f"{args.workload}: {W}x{H} stereo pair, {D} disparities, mode {args.mode} "
+                                   f"({'8-path MODE_HH' if args.mode == 1 else 'mode ' + str(args.mode)}), full disp_map+cloud+floor_hist",
+                       "batch_per_gpu": B, "parallelism": f"camera-sharded x{world}, NCCL all-reduce of floor histograms",
+                       "l2": f"no flush: each cost volume is {cells * 2 / 1e6:.0f} MB > 126 MB L2"},
+            "gpix_disp_per_s": value * W * H * D / 1e9,
+            "roofline": roofline, "stage_ms": stage_ms, "gpu_launches": int(launches),
+            "e2e": {"value": e2e_val, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "note": "sensor images H2D from pinned memory + float disparity, floor histogram, N, centroid D2H every frame; "
+                            "the point cloud stays on the device (its consumer floor_hist runs there)"},
+            "clocks": clk.summary(), "hist_hits": hist_total}
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import cv2ref
+
+        cores = os.cpu_count() or 1
+        cv2ref.set_threads(cores)
+        rows = min(H, args.cpu_rows)
+        c = crop_cam(cams[0], rows)
+        t0 = time.perf_counter()
+        cpu_frame(c, D, args.mode, synth.HIST_AABB)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = {"value": (rows / H) / dt, "unit": "frames/s", "cores": cores, "kind": "reference",
+                                "sample": f"one camera-frame, first {rows} of {H} rows ({W}x{rows}, D={D}, mode {args.mode}), scaled by rows/H; "
+                                          f"cv2 {cv2ref._cv2().__version__} with setNumThreads({cores}) (StereoSGBM MODE_HH itself is "
+                                          f"single-threaded inside OpenCV) + C port of cloud/hist; `--impl reference` runs one frame per core",
+                                "seconds": dt}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--mode", type=int, default=1, help="StereoSGBM mode: 1 = MODE_HH (8-path, headline), 3 = HH4, 0 = SGBM")
+    ap.add_argument("--batch", type=int, default=2, help="camera-frames per GPU per step")
+    ap.add_argument("--distinct", type=int, default=2, help="distinct synthetic camera-frames generated per rank")
+    ap.add_argument("--ref-threads", type=int, default=16)
+    ap.add_argument("--cpu-rows", type=int, default=1080)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -51,12 +51,13 @@ const char* mvs_last_error(const mvs_ctx* ctx); /* never NULL */
 int mvs_sync(mvs_ctx* ctx);                     /* wait for the context's stream */
 void* mvs_stream(mvs_ctx* ctx);                 /* the cudaStream_t, for callers that enqueue their own work */
 const char* mvs_version(void);
+long long mvs_launch_count(const mvs_ctx* ctx); /* kernels launched through this context so far */
 
 /* -- a1: rectification -----------------------------------------------------------------------------
  * Replaces cv::remap(in, rectified, mapx, mapy, interp, BORDER_CONSTANT, Scalar(255,255,255)) in
  * calc_rectified::Task::execute, pipeline/nodes/calc_rectified.cpp:109-115.
- * src: BGR 8UC3 sw x sh; mapx/mapy: CV_32FC1 w x h; dst: BGR 8UC3 w x h.  Bit-exact for INTER_CUBIC,
- * INTER_LINEAR and INTER_NEAREST. */
+ * src: BGR 8UC3 sw x sh; mapx/mapy: CV_32FC1 w x h; dst: BGR 8UC3 w x h.  Bit-exact for INTER_CUBIC (the
+ * reference default, calc_rectified.hpp:34); other interpolation modes return MVS_ERR_UNSUPPORTED. */
 int mvs_remap_bgr8(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
                    const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border_bgr[3],
                    uint8_t* dst, size_t dstep);
@@ -151,7 +152,9 @@ typedef struct {
     const float* mapy[2];
     int sw, sh, w, h;
     size_t sstep, mstep;
-    int inputs_on_device; /* 0: host pointers (copied in), 1: device pointers (used in place) */
+    int inputs_on_device; /* sensor images: 0 = host pointers (copied in), 1 = device pointers (used in place) */
+    int maps_on_device;   /* mapx/mapy: same meaning; the maps are per-camera constants (get_xy_mapping.cpp:59 computes
+                             them once per video), so a caller uploads them once and passes device pointers */
     mvs_sgbm_params sgbm;
     double presmooth_sigma;
     mvs_bcam bcam;

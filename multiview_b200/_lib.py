@@ -30,7 +30,7 @@ class HistParams(C.Structure):
 class FrameDesc(C.Structure):
     _fields_ = [("sensor", c_void_p * 2), ("mapx", c_void_p * 2), ("mapy", c_void_p * 2),
                 ("sw", c_int), ("sh", c_int), ("w", c_int), ("h", c_int),
-                ("sstep", c_size_t), ("mstep", c_size_t), ("inputs_on_device", c_int),
+                ("sstep", c_size_t), ("mstep", c_size_t), ("inputs_on_device", c_int), ("maps_on_device", c_int),
                 ("sgbm", SgbmParams), ("presmooth_sigma", c_double), ("bcam", Bcam), ("hist", HistParams),
                 ("et", c_double * 8), ("aabb", c_double * 4), ("cam_center", c_double * 3)]
 
@@ -49,6 +49,7 @@ SIGNATURES = {
     "mvs_sync": (c_int, [c_void_p]),
     "mvs_stream": (c_void_p, [c_void_p]),
     "mvs_version": (C.c_char_p, []),
+    "mvs_launch_count": (C.c_longlong, [c_void_p]),
     "mvs_remap_bgr8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p, c_void_p, c_size_t, c_int, c_int,
                                c_int, c_void_p, c_void_p, c_size_t]),
     "mvs_presmooth": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_size_t, c_double, c_void_p, c_size_t]),

@@ -65,6 +65,9 @@ class Context:
     def sync(self):
         self.check(self.lib.mvs_sync(self.h), "mvs_sync")
 
+    def launch_count(self) -> int:
+        return int(self.lib.mvs_launch_count(self.h))
+
     def stage_ms(self, stage: str) -> float:
         return float(self.lib.mvs_stage_ms(self.h, stage.encode()))
 
@@ -390,6 +393,7 @@ def make_frame_desc(cam: dict, sgbm: StereoSGBMParams, hist: FloorHistogramParam
     d.sw, d.sh, d.w, d.h = w, h, w, h
     d.sstep, d.mstep = w * 3, w * 4
     d.inputs_on_device = int(on_device)
+    d.maps_on_device = int(on_device)
     d.sgbm = sgbm.to_c()
     d.presmooth_sigma = sigma
     d.bcam = BinocularCamera().init(cam["q"], cam["t"], cam["baseline"], cam["K"]).to_c()

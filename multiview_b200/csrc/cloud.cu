@@ -216,7 +216,7 @@ int point_cloud_dev(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, int w
     pc_scan_kernel<<<1, 1024, 0, s>>>(counts, nb, offsets, n_dev);
     pc_emit_kernel<<<nb, PC_BLOCK, 0, s>>>(disp, w, n, *bcam, left_is_ref, offsets, Xs, xy, lookup, partial);
     pc_centroid_kernel<<<1, 256, 0, s>>>(partial, nb, n_dev, centroid_dev);
-    MVS_LAUNCH_CHECK(ctx, "point cloud kernels");
+    MVS_LAUNCH_CHECK_N(ctx, "point cloud kernels", 4);
     return MVS_OK;
 }
 

@@ -40,6 +40,7 @@ struct mvs_ctx {
     FrameSlot slots[MVS_MAX_SLOTS];
     int16_t* cubic_tab_dev = nullptr;  // 32*32*16 Q15 bicubic weights
     int sm_count = 148;
+    long long launches = 0;  // kernels launched through this context (bench.py reports it)
 };
 
 int mvs_fail(mvs_ctx* ctx, int code, const char* fmt, ...);
@@ -55,12 +56,15 @@ void stage_end(mvs_ctx* ctx, const char* stage);
                             __FILE__, __LINE__);                                                    \
     } while (0)
 
-#define MVS_LAUNCH_CHECK(ctx, name)                                                                 \
+// n = number of kernel launches covered by this check
+#define MVS_LAUNCH_CHECK_N(ctx, name, n)                                                            \
     do {                                                                                            \
+        (ctx)->launches += (n);                                                                     \
         cudaError_t e__ = cudaGetLastError();                                                       \
         if (e__ != cudaSuccess)                                                                     \
             return mvs_fail(ctx, MVS_ERR_CUDA, "launch of %s failed: %s", name, cudaGetErrorString(e__)); \
     } while (0)
+#define MVS_LAUNCH_CHECK(ctx, name) MVS_LAUNCH_CHECK_N(ctx, name, 1)
 
 #define MVS_ARENA(ctx, T, var, name, count)                                   \
     T* var = (T*)arena_get(ctx, name, sizeof(T) * (size_t)(count));          \

@@ -156,7 +156,7 @@ int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, cons
     dim3 pg(cdiv(g.W, 128), g.H);
     prefilter_kernel<<<pg, 128, 0, s>>>(l, g.W, g.H, g.ftzero, planes);
     prefilter_kernel<<<pg, 128, 0, s>>>(r, g.W, g.H, g.ftzero, planes + 6 * plane);
-    MVS_LAUNCH_CHECK(ctx, "prefilter_kernel");
+    MVS_LAUNCH_CHECK_N(ctx, "prefilter_kernel", 2);
     dim3 cg(cdiv(g.W1, COST_TX), g.H);
     size_t smem = (size_t)(COST_TX + 2 * g.SW2) * g.Dp;
     pixcost_hsum_kernel<<<cg, 256, smem, s>>>(planes, planes + 6 * plane, g, hsum);

@@ -118,4 +118,6 @@ extern "C" int mvs_sync(mvs_ctx* ctx)
     return MVS_OK;
 }
 
+extern "C" long long mvs_launch_count(const mvs_ctx* ctx) { return ctx ? ctx->launches : -1; }
+
 extern "C" void* mvs_stream(mvs_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }

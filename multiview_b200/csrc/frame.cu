@@ -28,22 +28,28 @@ extern "C" int mvs_frame_run(mvs_ctx* ctx, int slot, const mvs_frame_desc* d, mv
 
     const uint8_t* sensor[2];
     const float *mapx[2], *mapy[2];
-    size_t sstep = d->sstep, mstep = d->mstep;
+    const size_t sstep = d->inputs_on_device ? d->sstep : (size_t)d->sw * 3;
+    const size_t mstep = d->maps_on_device ? d->mstep : (size_t)w * 4;
     for (int i = 0; i < 2; ++i) {
         if (d->inputs_on_device) {
-            sensor[i] = d->sensor[i]; mapx[i] = d->mapx[i]; mapy[i] = d->mapy[i];
+            sensor[i] = d->sensor[i];
         } else {
             uint8_t* ds = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "sensor1" : "sensor0").c_str(), (size_t)d->sh * d->sw * 3);
+            if (!ds) return MVS_ERR_NOMEM;
+            MVS_CUDA(ctx, cudaMemcpy2DAsync(ds, (size_t)d->sw * 3, d->sensor[i], d->sstep, (size_t)d->sw * 3, d->sh, cudaMemcpyHostToDevice, s));
+            sensor[i] = ds;
+        }
+        if (d->maps_on_device) {
+            mapx[i] = d->mapx[i]; mapy[i] = d->mapy[i];
+        } else {
             float* dx = (float*)arena_get(ctx, slot_name(slot, i ? "mapx1" : "mapx0").c_str(), n * 4);
             float* dy = (float*)arena_get(ctx, slot_name(slot, i ? "mapy1" : "mapy0").c_str(), n * 4);
-            if (!ds || !dx || !dy) return MVS_ERR_NOMEM;
-            MVS_CUDA(ctx, cudaMemcpy2DAsync(ds, (size_t)d->sw * 3, d->sensor[i], d->sstep, (size_t)d->sw * 3, d->sh, cudaMemcpyHostToDevice, s));
+            if (!dx || !dy) return MVS_ERR_NOMEM;
             MVS_CUDA(ctx, cudaMemcpy2DAsync(dx, (size_t)w * 4, d->mapx[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
             MVS_CUDA(ctx, cudaMemcpy2DAsync(dy, (size_t)w * 4, d->mapy[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
-            sensor[i] = ds; mapx[i] = dx; mapy[i] = dy;
+            mapx[i] = dx; mapy[i] = dy;
         }
     }
-    if (!d->inputs_on_device) { sstep = (size_t)d->sw * 3; mstep = (size_t)w * 4; }
 
     uint8_t* rect[2];
     uint8_t* grey[2];

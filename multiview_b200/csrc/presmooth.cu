@@ -125,7 +125,7 @@ int presmooth_dev(mvs_ctx* ctx, const char* tag, const uint8_t* src, int channel
     blur_v_kernel<<<grid, 128, 0, s>>>(tmp, w, h, t, grey, (size_t)w);
     blur_h_kernel<<<grid, 128, 0, s>>>(grey, (size_t)w, w, h, t, tmp);
     blur_v_kernel<<<grid, 128, 0, s>>>(tmp, w, h, t, dst, dstep);
-    MVS_LAUNCH_CHECK(ctx, "blur kernels");
+    MVS_LAUNCH_CHECK_N(ctx, "blur kernels", 4);
     return MVS_OK;
 }
 

@@ -178,7 +178,7 @@ int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw
     case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
     default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
     }
-    MVS_LAUNCH_CHECK(ctx, "wta_kernel");
+    MVS_LAUNCH_CHECK_N(ctx, "wta_kernel", 2);
     lr_check_kernel<<<dim3(cdiv(g.W1, 128), g.H), 128, 0, s>>>(raw16, d2, g);
     MVS_LAUNCH_CHECK(ctx, "lr_check_kernel");
     return MVS_OK;
@@ -198,7 +198,7 @@ int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, con
         speckle_union_kernel<<<dim3(cdiv(g.W, 128), g.H), 128, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L);
         speckle_count_kernel<<<cdiv(n, 256), 256, 0, s>>>(disp16, n, g.INV, L, cnt);
         speckle_apply_kernel<<<cdiv(n, 256), 256, 0, s>>>(disp16, n, g.INV, p->speckle_win, L, cnt);
-        MVS_LAUNCH_CHECK(ctx, "speckle kernels");
+        MVS_LAUNCH_CHECK_N(ctx, "speckle kernels", 4);
     }
     return MVS_OK;
 }

@@ -113,6 +113,27 @@ typedef struct {
 int mvs_point_cloud(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, size_t step, int w, int h,
                     int left_is_ref, double* Xs, int32_t* xy, int32_t* lookup, int32_t* n_out, double centroid[3]);
 
+/* The same point cloud for callers that must not allocate at frame time.  This entry point has no
+ * counterpart in the reference; it exists for hosts where the library may not call cudaMalloc once frames
+ * are flowing: a real-time camera loop (cudaMalloc synchronises the whole device and would stall the other
+ * streams), or an application whose own pool already owns all GPU memory (cudaMalloc would fail).
+ *   - All pointers are DEVICE pointers supplied by the caller: disp_dev (w*h floats, tightly packed), Xs_dev
+ *     (capacity w*h*3 doubles), xy_dev (capacity w*h*2 int32), lookup_dev (w*h int32), n_dev (one int32),
+ *     centroid_dev (3 doubles).  The call is asynchronous on the context's stream (mvs_sync to wait).
+ *   - It performs no cudaMalloc/cudaFree and calls nothing that allocates.  Its compaction scratch is a fixed
+ *     288 KiB device array inside the library, resident on every GPU that loads the library until exit.
+ *   - Limit: w*h <= MVS_STATIC_CLOUD_MAX_PIXELS (4096 x 2304); larger images return MVS_ERR_UNSUPPORTED and
+ *     mvs_last_error says so -- use mvs_point_cloud for those.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that
+ *     first call before starting any stream capture on that device.
+ *   - All calls on a device share the one array.  Its contents are whatever the previous call left; a call
+ *     overwrites every entry before reading it, so nothing needs clearing, but two calls whose kernels overlap
+ *     on the GPU (two contexts / streams on the same device) race on it: serialise them. */
+#define MVS_STATIC_CLOUD_MAX_PIXELS (4096 * 2304)
+int mvs_point_cloud_static_dev(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp_dev, int w, int h,
+                               int left_is_ref, double* Xs_dev, int32_t* xy_dev, int32_t* lookup_dev,
+                               int32_t* n_dev, double* centroid_dev);
+
 /* -- a9/a10: floor histogram ------------------------------------------------------------------------
  * Subset of FloorHistogram::Params used per point, cost-functions/floor-histogram.hpp:28-36. */
 typedef struct {

@@ -60,7 +60,9 @@ SIGNATURES = {
                                    c_size_t, c_void_p, c_size_t]),
     "mvs_point_cloud": (c_int, [c_void_p, C.POINTER(Bcam), c_void_p, c_size_t, c_int, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p, C.POINTER(C.c_int32), c_void_p]),
-    "mvs_hist_dims": (c_int, [c_void_p, c_float, C.POINTER(c_int), C.POINTER(c_int)]),
+    "mvs_point_cloud_static_dev": (c_int, [c_void_p, C.POINTER(Bcam), c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
+                                           c_void_p, c_void_p, c_void_p]),
+    "mvs_hist_dims": (c_int,[c_void_p, c_float, C.POINTER(c_int), C.POINTER(c_int)]),
     "mvs_floor_hist_camera": (c_int, [c_void_p, C.POINTER(HistParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                       C.c_int32, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int]),
     "mvs_hist_sum": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),

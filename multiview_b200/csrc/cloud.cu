@@ -252,3 +252,56 @@ extern "C" int mvs_point_cloud(mvs_ctx* ctx, const mvs_bcam* bcam, const float* 
     *n_out = nh;
     return MVS_OK;
 }
+
+// ---- point cloud without any allocation -------------------------------------------------------------------
+// Some hosts cannot let this library allocate device memory at frame time: a real-time camera loop where
+// cudaMalloc's implicit device-wide synchronisation would stall every other stream, or an application whose
+// own memory pool has already claimed the whole GPU so that a later cudaMalloc simply fails.  For them the
+// compaction scratch of the point-cloud kernels (per-tile counts, their prefix sums, per-tile centroid partial
+// sums) lives in the fixed device array below instead of the context arena.  Every GPU that loads the library
+// carries these MVS_STATIC_CLOUD_SCRATCH_BYTES (288 KiB) until the process exits.
+#define MVS_STATIC_CLOUD_MAX_TILES ((MVS_STATIC_CLOUD_MAX_PIXELS + PC_TILE - 1) / PC_TILE)
+#define MVS_STATIC_CLOUD_SCRATCH_BYTES (MVS_STATIC_CLOUD_MAX_TILES * (2 * sizeof(int) + 3 * sizeof(double)))
+static __device__ __align__(256) unsigned char g_cloud_scratch[MVS_STATIC_CLOUD_SCRATCH_BYTES];
+
+#define MVS_MAX_DEVICES 64
+static unsigned char* g_cloud_scratch_addr[MVS_MAX_DEVICES];  // device address of g_cloud_scratch, per device
+
+extern "C" int mvs_point_cloud_static_dev(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp_dev, int w, int h,
+                                          int left_is_ref, double* Xs_dev, int32_t* xy_dev, int32_t* lookup_dev,
+                                          int32_t* n_dev, double* centroid_dev)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!bcam || !disp_dev || !Xs_dev || !xy_dev || !lookup_dev || !n_dev || !centroid_dev || w <= 0 || h <= 0)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_point_cloud_static_dev: bad argument");
+    const size_t n = (size_t)w * h;
+    if (n > (size_t)MVS_STATIC_CLOUD_MAX_PIXELS)
+        return mvs_fail(ctx, MVS_ERR_UNSUPPORTED,
+                        "mvs_point_cloud_static_dev: %d x %d = %zu pixels exceeds the fixed scratch (at most %d pixels); "
+                        "use mvs_point_cloud, which sizes its scratch from the context arena",
+                        w, h, n, (int)MVS_STATIC_CLOUD_MAX_PIXELS);
+    if (ctx->device < 0 || ctx->device >= MVS_MAX_DEVICES)
+        return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "mvs_point_cloud_static_dev: device index %d not supported", ctx->device);
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    // In host code `g_cloud_scratch` is only a handle for the symbol, not a device address: ask the runtime for
+    // the address once per device, with that device current (done on the first call for the device).
+    unsigned char* base = g_cloud_scratch_addr[ctx->device];
+    if (!base) {
+        MVS_CUDA(ctx, cudaGetSymbolAddress((void**)&base, g_cloud_scratch));
+        if (!base) return mvs_fail(ctx, MVS_ERR_CUDA, "mvs_point_cloud_static_dev: cudaGetSymbolAddress returned null");
+        g_cloud_scratch_addr[ctx->device] = base;
+    }
+    const int nb = cdiv(n, PC_TILE);
+    int* counts = (int*)base;
+    int* offsets = counts + MVS_STATIC_CLOUD_MAX_TILES;
+    double* partial = (double*)(offsets + MVS_STATIC_CLOUD_MAX_TILES);
+    // Nothing in the scratch has to start at zero: each of the nb entries a call reads is written earlier in
+    // the same call (counts by pc_count, offsets by pc_scan, partial by pc_emit), so leftovers are never seen.
+    cudaStream_t s = ctx->stream;
+    pc_count_kernel<<<nb, PC_BLOCK, 0, s>>>(disp_dev, n, counts);
+    pc_scan_kernel<<<1, 1024, 0, s>>>(counts, nb, offsets, n_dev);
+    pc_emit_kernel<<<nb, PC_BLOCK, 0, s>>>(disp_dev, w, n, *bcam, left_is_ref, offsets, Xs_dev, xy_dev, lookup_dev, partial);
+    pc_centroid_kernel<<<1, 256, 0, s>>>(partial, nb, n_dev, centroid_dev);
+    MVS_LAUNCH_CHECK_N(ctx, "point cloud kernels (static scratch)", 4);
+    return MVS_OK;
+}

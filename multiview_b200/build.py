@@ -24,6 +24,7 @@ UNITS = {
     "presmooth.cu": [],
     "cost.cu": [],
     "aggregate.cu": [],
+    "aggregate_wave.cu": [],
     "wta_post.cu": [],
     "sgbm.cu": [],
     "frame.cu": [],

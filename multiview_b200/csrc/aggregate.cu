@@ -9,6 +9,8 @@
 // disparity vector, each lane 2*NW consecutive disparities packed two per 32-bit register (u16x2).
 // Neighbouring disparities come from byte permutes inside the lane and one shuffle per side; the
 // minimum over d is one packed min per register plus a warp REDUX.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 #define SENT 0x7FFFu
@@ -152,7 +154,7 @@ static void launch_path(cudaStream_t s, const SgbmGeom& g, const int16_t* C, int
                                                           dy, first);
 }
 
-int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S)
+int sgbm_aggregate_paths_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S)
 {
     // direction sets (A.2/A.3); forward directions first, as the reference does
     static const int dirs_hh[8][2] = {{1, 0}, {1, 1}, {0, 1}, {-1, 1}, {-1, 0}, {1, -1}, {0, -1}, {-1, -1}};
@@ -173,4 +175,11 @@ int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_
         MVS_LAUNCH_CHECK(ctx, "path_kernel");
     }
     return MVS_OK;
+}
+
+// MVS_AGG=paths selects the per-direction kernels above (kept for A/B checks of the fused sweeps).
+int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S)
+{
+    static const bool use_paths = [] { const char* e = getenv("MVS_AGG"); return e && !strcmp(e, "paths"); }();
+    return use_paths ? sgbm_aggregate_paths_dev(ctx, g, C, S) : sgbm_aggregate_wave_dev(ctx, g, C, S);
 }

@@ -40,6 +40,7 @@ struct mvs_ctx {
     FrameSlot slots[MVS_MAX_SLOTS];
     int16_t* cubic_tab_dev = nullptr;  // 32*32*16 Q15 bicubic weights
     int sm_count = 148;
+    bool wave_err_cleared = false;
     long long launches = 0;  // kernels launched through this context (bench.py reports it)
 };
 
@@ -102,6 +103,9 @@ int hist_sum_dev(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int h
 
 // stage kernels of the SGBM chain (cost.cu, aggregate.cu, wta_post.cu)
 int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, const uint8_t* r, int16_t* C);
-int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);
+int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);       // fused wavefront sweeps
+int sgbm_aggregate_paths_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S); // one kernel per direction (debug/A-B)
+int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);
+int sgbm_aggregate_wave_status(mvs_ctx* ctx);
 int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16);
 int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, const int16_t* raw16, int16_t* disp16);

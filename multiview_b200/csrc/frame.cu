@@ -125,7 +125,7 @@ extern "C" int mvs_frame_fetch(mvs_ctx* ctx, int slot, float* disp, size_t dstep
     if (nh > 0 && xy) MVS_CUDA(ctx, cudaMemcpyAsync(xy, arena_get(ctx, slot_name(slot, "xy").c_str(), n * 8), (size_t)nh * 8, cudaMemcpyDeviceToHost, s));
     MVS_CUDA(ctx, cudaStreamSynchronize(s));
     if (n_out) *n_out = nh;
-    return MVS_OK;
+    return sgbm_aggregate_wave_status(ctx);
 }
 
 extern "C" int mvs_frame_hist_sum(mvs_ctx* ctx, int n_slots, float** hist_dev, int* hw, int* hh)

@@ -71,7 +71,7 @@ extern "C" int mvs_sgbm_compute16(mvs_ctx* ctx, const mvs_sgbm_params* p, const 
     if (rc) return rc;
     MVS_CUDA(ctx, cudaMemcpy2DAsync(disp16, dstep, dd, (size_t)w * 2, (size_t)w * 2, h, cudaMemcpyDeviceToHost, ctx->stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return MVS_OK;
+    return sgbm_aggregate_wave_status(ctx);
 }
 
 extern "C" int mvs_disparity_sgbm(mvs_ctx* ctx, const mvs_sgbm_params* p, double presmooth_sigma, const uint8_t* l,
@@ -96,7 +96,7 @@ extern "C" int mvs_disparity_sgbm(mvs_ctx* ctx, const mvs_sgbm_params* p, double
     if (rc) return rc;
     MVS_CUDA(ctx, cudaMemcpy2DAsync(out, ostep, df, (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ctx->stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return MVS_OK;
+    return sgbm_aggregate_wave_status(ctx);
 }
 
 extern "C" int mvs_sgbm_volumes(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
@@ -129,5 +129,5 @@ extern "C" int mvs_sgbm_volumes(mvs_ctx* ctx, const mvs_sgbm_params* p, const ui
     }
     if (raw_disp16) MVS_CUDA(ctx, cudaMemcpyAsync(raw_disp16, draw, (size_t)w * h * 2, cudaMemcpyDeviceToHost, ctx->stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return MVS_OK;
+    return sgbm_aggregate_wave_status(ctx);
 }

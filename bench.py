@@ -219,9 +219,10 @@ def run_ours(args, rank, world, local_rank):
                 dist.all_reduce(t)  # counts: exact in fp32 in any order
         return t
 
+    batch_dev = (api.FrameDesc * B)(*[descs_dev[b % len(descs_dev)] for b in range(B)])
+
     def step_dev():
-        for b in range(B):
-            api.frame_run(ctx, b, descs_dev[b % len(descs_dev)])
+        api.frame_run_batch(ctx, 0, batch_dev)  # one step = the B camera-frames of this rank, one batched call
         return hist_reduce()
 
     def barrier():
@@ -253,22 +254,35 @@ def run_ours(args, rank, world, local_rank):
     hist_total = float(hist_t.sum().item())
 
     # ---- per-stage device times (CUDA events inside the library, on the launching stream) -----------------
-    stages = ["rectify", "presmooth", "cost", "aggregate", "wta", "post", "cloud", "hist"]
-    acc = {s: [] for s in stages}
+    # (a) the batched step, as timed above: stage time / B = per camera-frame; the aggregation stage is 2 launches
+    #     (forward + backward sweep) covering all B frames, so this is its per-launch duration inside the step
+    stages = ["rectify", "presmooth", "cost", "aggregate", "wta", "cloud", "hist"]
+    acc = {s_: [] for s_ in stages}
     for _ in range(max(3, min(args.steps, 10))):
+        api.frame_run_batch(ctx, 0, batch_dev)
+        ctx.sync()
+        for s_ in stages:
+            acc[s_].append(ctx.stage_ms(s_))
+    stage_ms = {s_: float(np.mean(v)) / B for s_, v in acc.items()}
+    stage_ms["wta+post"] = stage_ms.pop("wta")
+    # (b) one camera-frame alone (latency mode)
+    acc1 = {s_: [] for s_ in stages + ["post"]}
+    for _ in range(3):
         api.frame_run(ctx, 0, descs_dev[0])
         ctx.sync()
-        for s in stages:
-            acc[s].append(ctx.stage_ms(s))
-    stage_ms = {s: float(np.mean(v)) for s, v in acc.items()}
+        for s_ in acc1:
+            acc1[s_].append(ctx.stage_ms(s_))
+    stage_ms_single = {s_: float(np.mean(v)) for s_, v in acc1.items()}
     cells = sgbm_cells(W, H, D)
     peak, peak_src = peaks()
     agg_bytes = 8.0 * cells  # read C + write S forward, read C + read S backward
     achieved = agg_bytes / (stage_ms["aggregate"] / 1000.0) / 1e9
-    roofline = {"bound": "hbm", "kernel": "SGM aggregation stage (all launches of sgbm_aggregate_dev)", "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    roofline = {"bound": "hbm", "kernel": f"wave_kernel: SGM aggregation, forward + backward sweep over the batch of {B} frames",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "algorithmic_bytes_per_frame": agg_bytes, "ms_per_frame": stage_ms["aggregate"], "peak_source": peak_src,
-                "frac_of_8TBs_nominal": achieved / 8000.0}
+                "frac_of_8TBs_nominal": achieved / 8000.0,
+                "single_frame": {"ms": stage_ms_single["aggregate"],
+                                 "frac": agg_bytes / (stage_ms_single["aggregate"] / 1000.0) / 1e9 / peak}}
 
     # ---- e2e: host buffers in, host results out, through the C ABI ----------------------------------------------
     descs_host = []
@@ -286,12 +300,13 @@ def run_ours(args, rank, world, local_rank):
     out_cen = np.empty(3)
     nout = C.c_int32()
 
+    batch_host = (api.FrameDesc * B)(*[descs_host[b % len(descs_host)] for b in range(B)])
+    for b in range(B):
+        batch_host[b].inputs_on_device, batch_host[b].maps_on_device = 0, 1  # host (pinned) sensor images, resident maps
+
     def step_e2e():
+        api.frame_run_batch(ctx, 0, batch_host)
         for b in range(B):
-            d = descs_host[b % len(descs_host)]
-            dd = api.FrameDesc.from_buffer_copy(d)  # host (pinned) sensor pointers, device-resident maps
-            dd.inputs_on_device, dd.maps_on_device = 0, 1
-            api.frame_run(ctx, b, dd)
             ctx.check(ctx.lib.mvs_frame_fetch(ctx.h, b, C.c_void_p(out_disp[b].data_ptr()), W * 4, None, None, None, C.byref(nout),
                                               C.c_void_p(out_cen.ctypes.data), C.c_void_p(out_hist[b].data_ptr())), "mvs_frame_fetch")
         hist_reduce()
@@ -320,7 +335,7 @@ def run_ours(args, rank, world, local_rank):
                        "batch_per_gpu": B, "parallelism": f"camera-sharded x{world}, NCCL all-reduce of floor histograms",
                        "l2": f"no flush: each cost volume is {cells * 2 / 1e6:.0f} MB > 126 MB L2"},
             "gpix_disp_per_s": value * W * H * D / 1e9,
-            "roofline": roofline, "stage_ms": stage_ms, "gpu_launches": int(launches),
+            "roofline": roofline, "stage_ms": stage_ms, "stage_ms_single_frame": stage_ms_single, "gpu_launches": int(launches),
             "e2e": {"value": e2e_val, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "note": "sensor images H2D from pinned memory + float disparity, floor histogram, N, centroid D2H every frame; "
                             "the point cloud stays on the device (its consumer floor_hist runs there)"},
@@ -355,7 +370,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", type=int, default=1, help="StereoSGBM mode: 1 = MODE_HH (8-path, headline), 3 = HH4, 0 = SGBM")
-    ap.add_argument("--batch", type=int, default=2, help="camera-frames per GPU per step")
+    ap.add_argument("--batch", type=int, default=4, help="camera-frames per GPU per step (<= 16)")
     ap.add_argument("--distinct", type=int, default=2, help="distinct synthetic camera-frames generated per rank")
     ap.add_argument("--ref-threads", type=int, default=16)
     ap.add_argument("--cpu-rows", type=int, default=1080)

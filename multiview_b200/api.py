@@ -413,6 +413,15 @@ def frame_run(ctx: Context, slot: int, desc: FrameDesc) -> FrameResult:
     return res
 
 
+def frame_run_batch(ctx: Context, first_slot: int, descs) -> list:
+    """The camera-frames of one step together (mvs_frame_run_batch); descs is a sequence of FrameDesc."""
+    n = len(descs)
+    arr = descs if isinstance(descs, C.Array) else (FrameDesc * n)(*descs)
+    res = (FrameResult * n)()
+    ctx.check(ctx.lib.mvs_frame_run_batch(ctx.h, first_slot, arr, n, res), "mvs_frame_run_batch")
+    return list(res)
+
+
 def frame_fetch(ctx: Context, slot: int, w: int, h: int, hw: int, hh: int, want_cloud=True):
     disp = np.empty((h, w), np.float32)
     lookup = np.empty((h, w), np.int32)

@@ -178,8 +178,18 @@ int sgbm_aggregate_paths_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, 
 }
 
 // MVS_AGG=paths selects the per-direction kernels above (kept for A/B checks of the fused sweeps).
-int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S)
+int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S)
 {
     static const bool use_paths = [] { const char* e = getenv("MVS_AGG"); return e && !strcmp(e, "paths"); }();
-    return use_paths ? sgbm_aggregate_paths_dev(ctx, g, C, S) : sgbm_aggregate_wave_dev(ctx, g, C, S);
+    if (!use_paths) return sgbm_aggregate_wave_batch_dev(ctx, g, F, C, S);
+    for (int f = 0; f < F; ++f) {
+        int rc = sgbm_aggregate_paths_dev(ctx, g, C[f], S[f]);
+        if (rc) return rc;
+    }
+    return MVS_OK;
+}
+
+int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S)
+{
+    return sgbm_aggregate_batch_dev(ctx, g, 1, &C, &S);
 }

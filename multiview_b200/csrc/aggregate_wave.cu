@@ -24,16 +24,21 @@
 #define WAVE_SPIN_LIMIT (1 << 20)
 #define WAVE_CTL_PAD 16
 
-struct WaveParams {
+// A launch sweeps a batch of F camera-frames of equal geometry: tickets interleave the frames (frame = ticket % F,
+// band = ticket / F) so that all frames advance together and their wavefronts fill the machine.
+struct WaveFrame {
     const uint32_t* C;
     const uint32_t* Sin;   // backward sweep: S after the forward sweep (nullptr in the forward sweep)
     uint32_t* Sout;
     uint32_t* bndL;        // [nbands][W1][3][wpp] boundary path costs
     uint32_t* bndMin;      // [nbands][W1][2]      boundary minima (3 x u16 + pad)
-    int* progress;         // [nbands] pixels finished by the band's last row
-    int* ticket;           // band counter
+};
+struct WaveParams {
+    WaveFrame f[MVS_MAX_BATCH];
+    int* progress;         // [F][nbands] pixels finished by each band's last row
+    int* ticket;           // work counter
     int* error;            // set when a bounded wait expires
-    int W1, H, D, P1, P2, nbands, flip;
+    int W1, H, D, P1, P2, nbands, flip, F;
 };
 
 __device__ __forceinline__ uint32_t wdup16(uint32_t v) { return v | (v << 16); }
@@ -55,6 +60,8 @@ __device__ __forceinline__ void cp_async(void* smem, const void* gmem)
     else if (BYTES == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
     else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
 }
+#define WAVE_L2_AHEAD 8
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -153,16 +160,18 @@ wave_kernel(WaveParams p)
         __syncthreads();
         if (threadIdx.x == 0) s_band = atomicAdd(p.ticket, 1);
         __syncthreads();
-        const int band = s_band;
-        if (band >= p.nbands) break;
+        if (s_band >= p.nbands * p.F) break;
+        const int band = s_band / p.F, fi = s_band - band * p.F;
+        const WaveFrame& fr = p.f[fi];
         const int ys0 = band * WAVE_R;  // first sweep row of the band
         const int rows = min(WAVE_R, p.H - ys0);
         const bool first_band = band == 0, last_band = band == p.nbands - 1;
-        const uint32_t* bL = p.bndL + (size_t)(first_band ? 0 : band - 1) * W1 * 3 * RG::WPP;  // written by the previous band
-        const uint32_t* bM = p.bndMin + (size_t)(first_band ? 0 : band - 1) * W1 * 2;
-        uint32_t* oL = p.bndL + (size_t)band * W1 * 3 * RG::WPP;
-        uint32_t* oM = p.bndMin + (size_t)band * W1 * 2;
-        const int* prev_progress = p.progress + (first_band ? 0 : band - 1);
+        const uint32_t* bL = fr.bndL + (size_t)(first_band ? 0 : band - 1) * W1 * 3 * RG::WPP;  // written by the previous band
+        const uint32_t* bM = fr.bndMin + (size_t)(first_band ? 0 : band - 1) * W1 * 2;
+        uint32_t* oL = fr.bndL + (size_t)band * W1 * 3 * RG::WPP;
+        uint32_t* oM = fr.bndMin + (size_t)band * W1 * 2;
+        int* my_progress = p.progress + (size_t)fi * p.nbands + band;
+        const int* prev_progress = my_progress - (first_band ? 0 : 1);
         const bool fetch = helper && VERT && !first_band;
         int seen = 0;  // helper: cached progress of the previous band
         bool failed = false;
@@ -218,8 +227,8 @@ wave_kernel(WaveParams p)
             const int x0 = p.flip ? W1 - 1 : 0;
             off = ((long long)y * W1 + x0) * RG::WPP + lane * NW;
             stride = p.flip ? -(long long)RG::WPP : (long long)RG::WPP;
-            ldw<NW>(p.C + off, Cw);
-            if (p.Sin) ldw<NW>(p.Sin + off, Sw);
+            ldw<NW>(fr.C + off, Cw);
+            if (fr.Sin) ldw<NW>(fr.Sin + off, Sw);
         }
         const int nsteps = W1 + 2 * (rows - 1);
         __syncthreads();
@@ -233,9 +242,13 @@ wave_kernel(WaveParams p)
                 if (x >= 0 && x < W1) {
                     uint32_t Cn[NW], Sn[NW];
                     const bool more = x + 1 < W1;
+                    if (x + WAVE_L2_AHEAD < W1) {  // pull the volumes into L2 well ahead of the register prefetch
+                        prefetch_l2(fr.C + off + WAVE_L2_AHEAD * stride);
+                        if (fr.Sin) prefetch_l2(fr.Sin + off + WAVE_L2_AHEAD * stride);
+                    }
                     if (more) {  // next pixel's C (and S) before the dependent chain
-                        ldw<NW>(p.C + off + stride, Cn);
-                        if (p.Sin) ldw<NW>(p.Sin + off + stride, Sn);
+                        ldw<NW>(fr.C + off + stride, Cn);
+                        if (fr.Sin) ldw<NW>(fr.Sin + off + stride, Sn);
                     }
                     uint32_t acc[NW], Lo[NW];
                     if (DIRMASK & 1) {  // direction 0: predecessor (x-1, y), kept in registers
@@ -282,12 +295,12 @@ wave_kernel(WaveParams p)
                     }
                     uint32_t So[NW];
 #pragma unroll
-                    for (int j = 0; j < NW; ++j) So[j] = p.Sin ? __viaddmin_u16x2(Sw[j], acc[j], SENT2) : acc[j];
-                    stw<NW>(p.Sout + off, So);
+                    for (int j = 0; j < NW; ++j) So[j] = fr.Sin ? __viaddmin_u16x2(Sw[j], acc[j], SENT2) : acc[j];
+                    stw<NW>(fr.Sout + off, So);
                     if (VERT && r + 1 == rows && !last_band && (((x + 1) % WAVE_PUBLISH) == 0 || x + 1 == W1)) {
                         __threadfence();
                         __syncwarp();
-                        if (lane == 0) st_release(p.progress + band, x + 1);
+                        if (lane == 0) st_release(my_progress, x + 1);
                     }
                     off += stride;
                     if (more) {
@@ -310,7 +323,7 @@ static int launch_wave(mvs_ctx* ctx, const WaveParams& p)
     int per_sm = 1;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_kernel<NW, DIRMASK, PAD>, WAVE_THREADS, smem);
     if (per_sm < 1) per_sm = 1;
-    int grid = min(p.nbands, ctx->sm_count * per_sm);
+    int grid = min(p.nbands * p.F, ctx->sm_count * per_sm);
     wave_kernel<NW, DIRMASK, PAD><<<grid, WAVE_THREADS, smem, ctx->stream>>>(p);
     MVS_LAUNCH_CHECK(ctx, "wave_kernel");
     return MVS_OK;
@@ -329,13 +342,15 @@ static int launch_wave_nw(mvs_ctx* ctx, const SgbmGeom& g, const WaveParams& p)
     return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "aggregate: Dp=%d", g.Dp);
 }
 
-int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S)
+int sgbm_aggregate_wave_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S)
 {
+    if (F < 1 || F > MVS_MAX_BATCH) return mvs_fail(ctx, MVS_ERR_ARG, "aggregate: batch of %d frames (1..%d)", F, MVS_MAX_BATCH);
     const int nbands = cdiv(g.H, WAVE_R);
     const size_t wpp = (size_t)g.Dp / 2;
-    const int ctl_pass = nbands + 2 * WAVE_CTL_PAD;
-    MVS_ARENA(ctx, uint32_t, bndL, "sgbm.wave.bndL", (size_t)nbands * g.W1 * 3 * wpp);
-    MVS_ARENA(ctx, uint32_t, bndMin, "sgbm.wave.bndMin", (size_t)nbands * g.W1 * 2);
+    const int ctl_pass = F * nbands + 2 * WAVE_CTL_PAD;
+    const size_t bndL_sz = (size_t)nbands * g.W1 * 3 * wpp, bndM_sz = (size_t)nbands * g.W1 * 2;
+    MVS_ARENA(ctx, uint32_t, bndL, "sgbm.wave.bndL", bndL_sz * F);
+    MVS_ARENA(ctx, uint32_t, bndMin, "sgbm.wave.bndMin", bndM_sz * F);
     MVS_ARENA(ctx, int, ctl, "sgbm.wave.ctl", (size_t)2 * ctl_pass);
     MVS_ARENA(ctx, int, err, "sgbm.wave.err", 1);
     if (!ctx->wave_err_cleared) {
@@ -343,20 +358,31 @@ int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, i
         ctx->wave_err_cleared = true;
     }
     WaveParams p;
-    p.C = (const uint32_t*)C; p.bndL = bndL; p.bndMin = bndMin; p.error = err;
+    memset(&p, 0, sizeof(p));
+    p.error = err; p.F = F;
     p.W1 = g.W1; p.H = g.H; p.D = g.D; p.P1 = g.P1; p.P2 = g.P2; p.nbands = nbands;
     MVS_CUDA(ctx, cudaMemsetAsync(ctl, 0, sizeof(int) * 2 * ctl_pass, ctx->stream));
     int rc;
     // forward sweep
-    p.Sin = nullptr; p.Sout = (uint32_t*)S; p.flip = 0; p.ticket = ctl; p.progress = ctl + WAVE_CTL_PAD;
+    for (int f = 0; f < F; ++f) {
+        p.f[f].C = (const uint32_t*)C[f]; p.f[f].Sin = nullptr; p.f[f].Sout = (uint32_t*)S[f];
+        p.f[f].bndL = bndL + bndL_sz * f; p.f[f].bndMin = bndMin + bndM_sz * f;
+    }
+    p.flip = 0; p.ticket = ctl; p.progress = ctl + WAVE_CTL_PAD;
     rc = g.mode == MVS_MODE_HH4 ? launch_wave_nw<0x5>(ctx, g, p) : launch_wave_nw<0xF>(ctx, g, p);
     if (rc) return rc;
     // backward sweep: the same recurrence on the image flipped in x and y
-    p.Sin = (const uint32_t*)S; p.flip = 1; p.ticket = ctl + ctl_pass; p.progress = ctl + ctl_pass + WAVE_CTL_PAD;
+    for (int f = 0; f < F; ++f) p.f[f].Sin = (const uint32_t*)S[f];
+    p.flip = 1; p.ticket = ctl + ctl_pass; p.progress = ctl + ctl_pass + WAVE_CTL_PAD;
     if (g.mode == MVS_MODE_HH) rc = launch_wave_nw<0xF>(ctx, g, p);
     else if (g.mode == MVS_MODE_HH4) rc = launch_wave_nw<0x5>(ctx, g, p);
     else rc = launch_wave_nw<0x1>(ctx, g, p);  // MODE_SGBM: only the (x+1, y) direction
     return rc;
+}
+
+int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S)
+{
+    return sgbm_aggregate_wave_batch_dev(ctx, g, 1, &C, &S);
 }
 
 // Host check of the bounded-wait flag (synchronises the stream); called by the entry points that sync anyway.

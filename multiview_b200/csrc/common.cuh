@@ -12,6 +12,7 @@
 #include "../../include/mvstereo.h"
 
 #define MVS_MAX_SLOTS 64
+#define MVS_MAX_BATCH 16  // camera-frames per batched launch
 
 // Grow-only named device buffers: allocated on first use, reused on every later frame, freed with the
 // context.  Replaces the reference's per-call cudaMalloc/cudaFree (strategies/sgm_disp.cpp:36-60,173).
@@ -107,5 +108,9 @@ int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_
 int sgbm_aggregate_paths_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S); // one kernel per direction (debug/A-B)
 int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);
 int sgbm_aggregate_wave_status(mvs_ctx* ctx);
+int sgbm_aggregate_wave_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S);
+int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S);
+int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
+                             int16_t* const* disp16, int16_t* raw16_tap /* F == 1 only */);
 int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16);
 int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, const int16_t* raw16, int16_t* disp16);

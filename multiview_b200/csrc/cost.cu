@@ -82,48 +82,90 @@ __global__ void prefilter_kernel(const uint8_t* __restrict__ img, int W, int H, 
 }
 
 // ---- per-pixel BT cost + horizontal box sum ------------------------------------------------------------------
-// One block: row y, TX output columns (W1 coordinates), all disparities.
-#define COST_TX 32
-__global__ void __launch_bounds__(256)
-pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, SgbmGeom g,
-                    uint16_t* __restrict__ hsum)
+// One block: NY rows x one tile of TX output columns (W1 coordinates) x all disparities.  A thread owns a pair of
+// disparities (u16x2) and walks along x keeping the last WIN pixel costs in a register ring, so the row box sum is
+// a sliding window (one add, one subtract per step).  The right image's six prefilter planes are staged reversed
+// in shared memory so that consecutive disparities are consecutive halfwords; a second copy shifted by one
+// halfword keeps the packed loads aligned for odd offsets.  All arithmetic is packed 16-bit with a +1024 bias so
+// that the Birchfield-Tomasi differences never go negative (plain 32-bit adds/subs then act per halfword).
+#define COST_K2 0x04000400u
+template <int WIN>
+__global__ void __launch_bounds__(128)
+pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, SgbmGeom g, uint32_t* __restrict__ hsum)
 {
-    extern __shared__ uint8_t pix[];  // [(TX + 2*SW2)][Dp]
-    const int y = blockIdx.y, x0 = blockIdx.x * COST_TX;
-    const int nx = COST_TX + 2 * g.SW2;
+    constexpr int NS = 10 * WIN;            // steps per tile (a multiple of the ring length)
+    constexpr int TX = NS - (WIN - 1);      // output columns per tile
+    constexpr int SW = WIN / 2;
+    extern __shared__ __align__(16) uint16_t sm[];
+    const int half = g.Dp >> 1;             // disparity pairs = threads per row
+    const int t = threadIdx.x % half, ry = threadIdx.x / half;
+    const int y = blockIdx.y * (blockDim.x / half) + ry;
+    const int x0 = blockIdx.x * TX;
     const size_t plane = (size_t)g.W * g.H;
-    const uint8_t* L = PL + (size_t)y * g.W;
-    const uint8_t* R = PR + (size_t)y * g.W;
-    for (int idx = threadIdx.x; idx < nx * g.Dp; idx += blockDim.x) {
-        int xi = idx / g.Dp, d = idx - xi * g.Dp;
-        int v = 0;
-        if (d < g.D) {
-            int x1 = min(max(x0 + xi - g.SW2, 0), g.W1 - 1);
-            int x = x1 + g.minX1, x2 = x - (d + g.minD);
-            int u = L[x], u0 = L[plane + x], u1 = L[2 * plane + x];
-            int vv = R[x2], v0 = R[plane + x2], v1 = R[2 * plane + x2];
-            int c0 = max(0, max(u - v1, v0 - u)), c1 = max(0, max(vv - u1, u0 - vv));
-            v = min(c0, c1);
-            u = L[3 * plane + x]; u0 = L[4 * plane + x]; u1 = L[5 * plane + x];
-            vv = R[3 * plane + x2]; v0 = R[4 * plane + x2]; v1 = R[5 * plane + x2];
-            c0 = max(0, max(u - v1, v0 - u)); c1 = max(0, max(vv - u1, u0 - vv));
-            v += min(c0, c1) >> 2;
+    // right-image planes, reversed: Rr[k] = R[xmax - k], xmax = largest image x2 any cell of the tile touches
+    const int xmax = min(x0 + TX - 1 + SW, g.W1 - 1) + g.minX1 - g.minD;
+    const int span = NS + g.Dp + 2;
+    const int rows = blockDim.x / half;
+    uint16_t* myR = sm + (size_t)ry * (12 * span);          // [plane 0..5][copy E/O][span]
+    uint32_t* myL = (uint32_t*)(sm + (size_t)rows * 12 * span) + (size_t)ry * (8 * NS);  // [step][8] pre-biased left values
+    if (y < g.H) {
+        const uint8_t* R = PR + (size_t)y * g.W;
+        for (int idx = t; idx < 6 * span; idx += half) {
+            int pl = idx / span, k = idx - pl * span;
+            int xr = min(max(xmax - k, 0), g.W - 1);
+            uint16_t v = R[pl * plane + xr];
+            myR[(pl * 2) * span + k] = v;                    // copy E
+            if (k > 0) myR[(pl * 2 + 1) * span + k - 1] = v;  // copy O: O[k] = E[k + 1]
         }
-        pix[idx] = (uint8_t)v;
+        const uint8_t* L = PL + (size_t)y * g.W;
+        for (int k = t; k < NS; k += half) {
+            int x = min(max(x0 - SW + k, 0), g.W1 - 1) + g.minX1;
+            for (int ch = 0; ch < 2; ++ch) {
+                uint32_t u = L[(3 * ch) * plane + x], u0 = L[(3 * ch + 1) * plane + x], u1 = L[(3 * ch + 2) * plane + x];
+                myL[k * 8 + ch * 4 + 0] = u * 0x10001u + COST_K2;   // u + K
+                myL[k * 8 + ch * 4 + 1] = COST_K2 - u * 0x10001u;   // K - u
+                myL[k * 8 + ch * 4 + 2] = COST_K2 - u1 * 0x10001u;  // K - hi(u)
+                myL[k * 8 + ch * 4 + 3] = u0 * 0x10001u + COST_K2;  // lo(u) + K
+            }
+        }
     }
     __syncthreads();
-    const int half = g.Dp >> 1;
-    const int win = 2 * g.SW2 + 1;
-    for (int idx = threadIdx.x; idx < COST_TX * half; idx += blockDim.x) {
-        int xo = idx / half, dp = idx - xo * half;
-        if (x0 + xo >= g.W1) continue;
-        const uint8_t* p = pix + (size_t)xo * g.Dp + 2 * dp;
-        unsigned lo = 0, hi = 0;
-        for (int k = 0; k < win; ++k) {
-            lo += p[(size_t)k * g.Dp];
-            hi += p[(size_t)k * g.Dp + 1];
+    if (y >= g.H) return;
+    uint32_t ring[WIN];
+#pragma unroll
+    for (int i = 0; i < WIN; ++i) ring[i] = 0;
+    uint32_t hs = 0;
+    const bool padlo = 2 * t >= g.D, padhi = 2 * t + 1 >= g.D;
+    uint32_t* out = hsum + ((size_t)y * g.W1) * half + t;
+#pragma unroll 1
+    for (int kb = 0; kb < NS; kb += WIN) {
+#pragma unroll
+        for (int i = 0; i < WIN; ++i) {
+            const int k = kb + i;
+            const int x = min(max(x0 - SW + k, 0), g.W1 - 1) + g.minX1;
+            // halfword index of the pair (d = 2t -> x2, d = 2t+1 -> x2 - 1) in the reversed row
+            const int k0 = xmax - (x - g.minD) + 2 * t;
+            const uint16_t* base = myR + ((k0 & 1) ? span : 0);
+            const uint32_t* pr = (const uint32_t*)(base) + (k0 >> 1);
+            const uint32_t* lv = myL + k * 8;
+            uint32_t pix = 0;
+#pragma unroll
+            for (int ch = 0; ch < 2; ++ch) {
+                const uint32_t v = pr[(ch * 3 + 0) * span], v0 = pr[(ch * 3 + 1) * span], v1 = pr[(ch * 3 + 2) * span];
+                const uint32_t uK = lv[ch * 4 + 0], Ku = lv[ch * 4 + 1], Ku1 = lv[ch * 4 + 2], u0K = lv[ch * 4 + 3];
+                // c0 + K = max(K, u - hi(v) + K, lo(v) - u + K); c1 + K = max(K, v - hi(u) + K, lo(u) - v + K)
+                uint32_t c0 = __vimax3_u16x2(uK - v1, v0 + Ku, COST_K2);
+                uint32_t c1 = __vimax3_u16x2(v + Ku1, u0K - v, COST_K2);
+                uint32_t c = __vminu2(c0, c1) - COST_K2;
+                pix += ch ? ((c >> 2) & 0x3fff3fffu) : c;
+            }
+            if (padlo) pix &= 0xffff0000u;
+            if (padhi) pix &= 0x0000ffffu;
+            hs = hs + pix - ring[i];
+            ring[i] = pix;
+            const int xo = x0 + k - (WIN - 1);
+            if (k >= WIN - 1 && xo < g.W1) out[(size_t)xo * half] = hs;
         }
-        *(uint32_t*)(hsum + ((size_t)y * g.W1 + x0 + xo) * g.Dp + 2 * dp) = lo | (hi << 16);
     }
 }
 
@@ -157,10 +199,25 @@ int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, cons
     prefilter_kernel<<<pg, 128, 0, s>>>(l, g.W, g.H, g.ftzero, planes);
     prefilter_kernel<<<pg, 128, 0, s>>>(r, g.W, g.H, g.ftzero, planes + 6 * plane);
     MVS_LAUNCH_CHECK_N(ctx, "prefilter_kernel", 2);
-    dim3 cg(cdiv(g.W1, COST_TX), g.H);
-    size_t smem = (size_t)(COST_TX + 2 * g.SW2) * g.Dp;
-    pixcost_hsum_kernel<<<cg, 256, smem, s>>>(planes, planes + 6 * plane, g, hsum);
-    MVS_LAUNCH_CHECK(ctx, "pixcost_hsum_kernel");
+    {
+        const int half = g.Dp >> 1, rows = 128 / half > 0 ? 128 / half : 1, win = 2 * g.SW2 + 1;
+        const int ns = 10 * win, tx = ns - (win - 1), span = ns + g.Dp + 2;
+        dim3 cg(cdiv(g.W1, tx), cdiv(g.H, rows));
+        size_t smem = (size_t)rows * (12 * span * sizeof(uint16_t) + 8 * ns * sizeof(uint32_t));
+        uint32_t* hs32 = (uint32_t*)hsum;
+        const uint8_t* PR = planes + 6 * plane;
+        switch (win) {
+        case 1: pixcost_hsum_kernel<1><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
+        case 3: pixcost_hsum_kernel<3><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
+        case 5: pixcost_hsum_kernel<5><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
+        case 7: pixcost_hsum_kernel<7><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
+        case 9: pixcost_hsum_kernel<9><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
+        case 11: pixcost_hsum_kernel<11><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
+        case 13: pixcost_hsum_kernel<13><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
+        default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "cost: block size %d", win);
+        }
+        MVS_LAUNCH_CHECK(ctx, "pixcost_hsum_kernel");
+    }
     size_t rowwords = (size_t)g.W1 * (g.Dp >> 1);
     dim3 vg(cdiv(rowwords, 256), cdiv(g.H, VSUM_ROWS));
     vsum_kernel<<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C);

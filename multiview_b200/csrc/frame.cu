@@ -1,6 +1,10 @@
 // Device-resident camera-frame path: rectify x2 -> grey/blur x2 -> SGBM -> float -> cloud -> floor histogram,
 // i.e. the DAG slice calc_rectified[2c],[2c+1] -> disp_init[c] -> disp_map_update[c] (pass-through) ->
 // floor_hist (per-camera part) of pipeline/frame-results.cpp:206-255, enqueued on one stream.
+//
+// mvs_frame_run_batch takes the camera-frames of one step together (the reference's thread pool runs the nodes of
+// different cameras concurrently, pipeline/pipeline-task.cpp:181-200): the stages run frame after frame, except
+// the SGM aggregation, which sweeps all frames of the batch in one launch so that its wavefronts fill the GPU.
 #include "common.cuh"
 
 static std::string slot_name(int slot, const char* what)
@@ -10,93 +14,137 @@ static std::string slot_name(int slot, const char* what)
     return buf;
 }
 
-extern "C" int mvs_frame_run(mvs_ctx* ctx, int slot, const mvs_frame_desc* d, mvs_frame_result* out)
+struct SlotBufs {
+    uint8_t *rect[2], *grey[2];
+    int16_t* disp16;
+    float* dispf;
+    double* Xs;
+    int32_t *xy, *lookup, *nd;
+    double* cen;
+    float* cam_hist;
+};
+
+extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame_desc* descs, int n_frames,
+                                   mvs_frame_result* out)
 {
     if (!ctx) return MVS_ERR_ARG;
-    if (!d || slot < 0 || slot >= MVS_MAX_SLOTS || d->w <= 0 || d->h <= 0 || d->sw <= 0 || d->sh <= 0 ||
-        !d->sensor[0] || !d->sensor[1] || !d->mapx[0] || !d->mapx[1] || !d->mapy[0] || !d->mapy[1])
-        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run: bad argument");
+    if (!descs || n_frames < 1 || n_frames > MVS_MAX_BATCH || first_slot < 0 || first_slot + n_frames > MVS_MAX_SLOTS)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: bad argument (1..%d frames, slots < %d)", MVS_MAX_BATCH, MVS_MAX_SLOTS);
+    const mvs_frame_desc& d0 = descs[0];
+    for (int f = 0; f < n_frames; ++f) {
+        const mvs_frame_desc* d = descs + f;
+        if (d->w <= 0 || d->h <= 0 || d->sw <= 0 || d->sh <= 0 || !d->sensor[0] || !d->sensor[1] || !d->mapx[0] || !d->mapx[1] ||
+            !d->mapy[0] || !d->mapy[1])
+            return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d: bad argument", f);
+        if (d->w != d0.w || d->h != d0.h || memcmp(&d->sgbm, &d0.sgbm, sizeof(mvs_sgbm_params)) || d->hist.hist_sz != d0.hist.hist_sz ||
+            memcmp(d->aabb, d0.aabb, sizeof(d0.aabb)))
+            return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d differs in size, SGBM parameters or histogram bounds", f);
+    }
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
-    const int w = d->w, h = d->h;
+    const int w = d0.w, h = d0.h;
     const size_t n = (size_t)w * h;
     int hw = 0, hh = 0;
-    if (mvs_hist_dims(d->aabb, d->hist.hist_sz, &hw, &hh)) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run: bad histogram bounds");
+    if (mvs_hist_dims(d0.aabb, d0.hist.hist_sz, &hw, &hh)) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: bad histogram bounds");
     SgbmGeom g;
-    int rc = sgbm_geom(ctx, &d->sgbm, w, h, &g);
+    int rc = sgbm_geom(ctx, &d0.sgbm, w, h, &g);
     if (rc) return rc;
-
-    const uint8_t* sensor[2];
-    const float *mapx[2], *mapy[2];
-    const size_t sstep = d->inputs_on_device ? d->sstep : (size_t)d->sw * 3;
-    const size_t mstep = d->maps_on_device ? d->mstep : (size_t)w * 4;
-    for (int i = 0; i < 2; ++i) {
-        if (d->inputs_on_device) {
-            sensor[i] = d->sensor[i];
-        } else {
-            uint8_t* ds = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "sensor1" : "sensor0").c_str(), (size_t)d->sh * d->sw * 3);
-            if (!ds) return MVS_ERR_NOMEM;
-            MVS_CUDA(ctx, cudaMemcpy2DAsync(ds, (size_t)d->sw * 3, d->sensor[i], d->sstep, (size_t)d->sw * 3, d->sh, cudaMemcpyHostToDevice, s));
-            sensor[i] = ds;
-        }
-        if (d->maps_on_device) {
-            mapx[i] = d->mapx[i]; mapy[i] = d->mapy[i];
-        } else {
-            float* dx = (float*)arena_get(ctx, slot_name(slot, i ? "mapx1" : "mapx0").c_str(), n * 4);
-            float* dy = (float*)arena_get(ctx, slot_name(slot, i ? "mapy1" : "mapy0").c_str(), n * 4);
-            if (!dx || !dy) return MVS_ERR_NOMEM;
-            MVS_CUDA(ctx, cudaMemcpy2DAsync(dx, (size_t)w * 4, d->mapx[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
-            MVS_CUDA(ctx, cudaMemcpy2DAsync(dy, (size_t)w * 4, d->mapy[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
-            mapx[i] = dx; mapy[i] = dy;
-        }
-    }
-
-    uint8_t* rect[2];
-    uint8_t* grey[2];
-    for (int i = 0; i < 2; ++i) {
-        rect[i] = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "rect1" : "rect0").c_str(), n * 3);
-        grey[i] = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "grey1" : "grey0").c_str(), n);
-        if (!rect[i] || !grey[i]) return MVS_ERR_NOMEM;
-    }
-    int16_t* disp16 = (int16_t*)arena_get(ctx, slot_name(slot, "disp16").c_str(), n * 2);
-    float* dispf = (float*)arena_get(ctx, slot_name(slot, "disp").c_str(), n * 4);
-    double* Xs = (double*)arena_get(ctx, slot_name(slot, "Xs").c_str(), n * 24);
-    int32_t* xy = (int32_t*)arena_get(ctx, slot_name(slot, "xy").c_str(), n * 8);
-    int32_t* lookup = (int32_t*)arena_get(ctx, slot_name(slot, "lookup").c_str(), n * 4);
-    int32_t* nd = (int32_t*)arena_get(ctx, slot_name(slot, "n").c_str(), 4);
-    double* cen = (double*)arena_get(ctx, slot_name(slot, "centroid").c_str(), 24);
     // per-camera histograms of all slots live in one array so that the camera sum is one kernel
     float* hists = (float*)arena_get(ctx, "slots.cam_hists", sizeof(float) * (size_t)hw * hh * MVS_MAX_SLOTS);
-    if (!disp16 || !dispf || !Xs || !xy || !lookup || !nd || !cen || !hists) return MVS_ERR_NOMEM;
-    float* cam_hist = hists + (size_t)slot * hw * hh;
+    if (!hists) return MVS_ERR_NOMEM;
+
+    SlotBufs sb[MVS_MAX_BATCH];
+    const uint8_t* sensor[MVS_MAX_BATCH][2];
+    const float *mapx[MVS_MAX_BATCH][2], *mapy[MVS_MAX_BATCH][2];
+    for (int f = 0; f < n_frames; ++f) {
+        const mvs_frame_desc* d = descs + f;
+        const int slot = first_slot + f;
+        for (int i = 0; i < 2; ++i) {
+            if (d->inputs_on_device) {
+                sensor[f][i] = d->sensor[i];
+            } else {
+                uint8_t* ds = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "sensor1" : "sensor0").c_str(), (size_t)d->sh * d->sw * 3);
+                if (!ds) return MVS_ERR_NOMEM;
+                MVS_CUDA(ctx, cudaMemcpy2DAsync(ds, (size_t)d->sw * 3, d->sensor[i], d->sstep, (size_t)d->sw * 3, d->sh, cudaMemcpyHostToDevice, s));
+                sensor[f][i] = ds;
+            }
+            if (d->maps_on_device) {
+                mapx[f][i] = d->mapx[i]; mapy[f][i] = d->mapy[i];
+            } else {
+                float* dx = (float*)arena_get(ctx, slot_name(slot, i ? "mapx1" : "mapx0").c_str(), n * 4);
+                float* dy = (float*)arena_get(ctx, slot_name(slot, i ? "mapy1" : "mapy0").c_str(), n * 4);
+                if (!dx || !dy) return MVS_ERR_NOMEM;
+                MVS_CUDA(ctx, cudaMemcpy2DAsync(dx, (size_t)w * 4, d->mapx[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+                MVS_CUDA(ctx, cudaMemcpy2DAsync(dy, (size_t)w * 4, d->mapy[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+                mapx[f][i] = dx; mapy[f][i] = dy;
+            }
+            sb[f].rect[i] = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "rect1" : "rect0").c_str(), n * 3);
+            sb[f].grey[i] = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "grey1" : "grey0").c_str(), n);
+            if (!sb[f].rect[i] || !sb[f].grey[i]) return MVS_ERR_NOMEM;
+        }
+        sb[f].disp16 = (int16_t*)arena_get(ctx, slot_name(slot, "disp16").c_str(), n * 2);
+        sb[f].dispf = (float*)arena_get(ctx, slot_name(slot, "disp").c_str(), n * 4);
+        sb[f].Xs = (double*)arena_get(ctx, slot_name(slot, "Xs").c_str(), n * 24);
+        sb[f].xy = (int32_t*)arena_get(ctx, slot_name(slot, "xy").c_str(), n * 8);
+        sb[f].lookup = (int32_t*)arena_get(ctx, slot_name(slot, "lookup").c_str(), n * 4);
+        sb[f].nd = (int32_t*)arena_get(ctx, slot_name(slot, "n").c_str(), 4);
+        sb[f].cen = (double*)arena_get(ctx, slot_name(slot, "centroid").c_str(), 24);
+        if (!sb[f].disp16 || !sb[f].dispf || !sb[f].Xs || !sb[f].xy || !sb[f].lookup || !sb[f].nd || !sb[f].cen) return MVS_ERR_NOMEM;
+        sb[f].cam_hist = hists + (size_t)slot * hw * hh;
+    }
 
     const uint8_t white[3] = {255, 255, 255};  // calc_rectified.cpp:113
     stage_begin(ctx, "rectify");
-    for (int i = 0; i < 2 && !rc; ++i)
-        rc = remap_bgr8_dev(ctx, sensor[i], d->sw, d->sh, sstep, mapx[i], mapy[i], mstep, w, h, MVS_INTER_CUBIC, white, rect[i], (size_t)w * 3);
+    for (int f = 0; f < n_frames && !rc; ++f) {
+        const mvs_frame_desc* d = descs + f;
+        const size_t sstep = d->inputs_on_device ? d->sstep : (size_t)d->sw * 3;
+        const size_t mstep = d->maps_on_device ? d->mstep : (size_t)w * 4;
+        for (int i = 0; i < 2 && !rc; ++i)
+            rc = remap_bgr8_dev(ctx, sensor[f][i], d->sw, d->sh, sstep, mapx[f][i], mapy[f][i], mstep, w, h, MVS_INTER_CUBIC, white,
+                                sb[f].rect[i], (size_t)w * 3);
+    }
     stage_end(ctx, "rectify");
     stage_begin(ctx, "presmooth");
-    for (int i = 0; i < 2 && !rc; ++i)
-        rc = presmooth_dev(ctx, i ? "r" : "l", rect[i], 3, w, h, (size_t)w * 3, d->presmooth_sigma, grey[i], (size_t)w);
+    for (int f = 0; f < n_frames && !rc; ++f)
+        for (int i = 0; i < 2 && !rc; ++i)
+            rc = presmooth_dev(ctx, i ? "r" : "l", sb[f].rect[i], 3, w, h, (size_t)w * 3, descs[f].presmooth_sigma, sb[f].grey[i], (size_t)w);
     stage_end(ctx, "presmooth");
-    if (!rc) rc = sgbm_compute16_dev(ctx, &d->sgbm, grey[0], grey[1], w, h, disp16, nullptr);
+    if (!rc) {
+        const uint8_t *l[MVS_MAX_BATCH], *r[MVS_MAX_BATCH];
+        int16_t* d16[MVS_MAX_BATCH];
+        for (int f = 0; f < n_frames; ++f) { l[f] = sb[f].grey[0]; r[f] = sb[f].grey[1]; d16[f] = sb[f].disp16; }
+        rc = sgbm_compute16_batch_dev(ctx, &d0.sgbm, n_frames, l, r, w, h, d16, nullptr);
+    }
     stage_begin(ctx, "cloud");
-    if (!rc) rc = disp_to_float_dev(ctx, disp16, w, h, dispf);
-    if (!rc) rc = point_cloud_dev(ctx, &d->bcam, dispf, w, h, 1, Xs, xy, lookup, nd, cen);
+    for (int f = 0; f < n_frames && !rc; ++f) {
+        rc = disp_to_float_dev(ctx, sb[f].disp16, w, h, sb[f].dispf);
+        if (!rc) rc = point_cloud_dev(ctx, &descs[f].bcam, sb[f].dispf, w, h, 1, sb[f].Xs, sb[f].xy, sb[f].lookup, sb[f].nd, sb[f].cen);
+    }
     stage_end(ctx, "cloud");
     stage_begin(ctx, "hist");
-    if (!rc) rc = floor_hist_camera_dev(ctx, &d->hist, d->et, d->aabb, d->cam_center, Xs, xy, nd, 0, nullptr, 0, 0, nullptr, 0, cam_hist, hw, hh);
+    for (int f = 0; f < n_frames && !rc; ++f)
+        rc = floor_hist_camera_dev(ctx, &descs[f].hist, descs[f].et, descs[f].aabb, descs[f].cam_center, sb[f].Xs, sb[f].xy, sb[f].nd, 0,
+                                   nullptr, 0, 0, nullptr, 0, sb[f].cam_hist, hw, hh);
     stage_end(ctx, "hist");
     if (rc) return rc;
 
-    FrameSlot& fs = ctx->slots[slot];
-    fs.w = w; fs.h = h; fs.hw = hw; fs.hh = hh; fs.valid = true;
-    if (out) {
-        out->rectified_dev[0] = rect[0]; out->rectified_dev[1] = rect[1];
-        out->disp16_dev = disp16; out->disp_dev = dispf; out->Xs_dev = Xs; out->xy_dev = xy; out->lookup_dev = lookup;
-        out->cam_hist_dev = cam_hist; out->n_dev = nd; out->centroid_dev = cen; out->hw = hw; out->hh = hh;
+    for (int f = 0; f < n_frames; ++f) {
+        FrameSlot& fs = ctx->slots[first_slot + f];
+        fs.w = w; fs.h = h; fs.hw = hw; fs.hh = hh; fs.valid = true;
+        if (out) {
+            mvs_frame_result* o = out + f;
+            o->rectified_dev[0] = sb[f].rect[0]; o->rectified_dev[1] = sb[f].rect[1];
+            o->disp16_dev = sb[f].disp16; o->disp_dev = sb[f].dispf; o->Xs_dev = sb[f].Xs; o->xy_dev = sb[f].xy;
+            o->lookup_dev = sb[f].lookup; o->cam_hist_dev = sb[f].cam_hist; o->n_dev = sb[f].nd; o->centroid_dev = sb[f].cen;
+            o->hw = hw; o->hh = hh;
+        }
     }
     return MVS_OK;
+}
+
+extern "C" int mvs_frame_run(mvs_ctx* ctx, int slot, const mvs_frame_desc* d, mvs_frame_result* out)
+{
+    return mvs_frame_run_batch(ctx, slot, d, 1, out);
 }
 
 extern "C" int mvs_frame_fetch(mvs_ctx* ctx, int slot, float* disp, size_t dstep, double* Xs, int32_t* xy,

@@ -13,35 +13,54 @@ __global__ void unpad_kernel(const int16_t* __restrict__ src, size_t npix, int D
     dst[i] = src[p * Dp + d];
 }
 
-int sgbm_compute16_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
-                       int16_t* disp16, int16_t* raw16_tap)
+static std::string fname(const char* base, int f)
 {
+    char buf[64];
+    snprintf(buf, sizeof(buf), "%s.%d", base, f);
+    return buf;
+}
+
+// A batch of F pairs of equal size through the SGBM chain.  The cost volumes of all frames are built first so
+// that ONE aggregation launch per sweep covers the whole batch (its wavefronts then fill the GPU).
+int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r,
+                             int w, int h, int16_t* const* disp16, int16_t* raw16_tap)
+{
+    if (F < 1 || F > MVS_MAX_BATCH) return mvs_fail(ctx, MVS_ERR_ARG, "sgbm: batch of %d frames (1..%d)", F, MVS_MAX_BATCH);
     SgbmGeom g;
     int rc = sgbm_geom(ctx, p, w, h, &g);
     if (rc) return rc;
-    MVS_ARENA(ctx, int16_t, C, "sgbm.C", g.cells());
-    MVS_ARENA(ctx, int16_t, S, "sgbm.S", g.cells());
-    int16_t* raw = raw16_tap;
-    if (!raw) {
-        raw = (int16_t*)arena_get(ctx, "sgbm.raw", sizeof(int16_t) * (size_t)w * h);
-        if (!raw) return MVS_ERR_NOMEM;
+    int16_t* C[MVS_MAX_BATCH];
+    int16_t* S[MVS_MAX_BATCH];
+    for (int f = 0; f < F; ++f) {
+        C[f] = (int16_t*)arena_get(ctx, fname("sgbm.C", f).c_str(), g.cells() * 2);
+        S[f] = (int16_t*)arena_get(ctx, fname("sgbm.S", f).c_str(), g.cells() * 2);
+        if (!C[f] || !S[f]) return MVS_ERR_NOMEM;
     }
+    int16_t* raw = (F == 1 && raw16_tap) ? raw16_tap : (int16_t*)arena_get(ctx, "sgbm.raw", sizeof(int16_t) * (size_t)w * h);
+    if (!raw) return MVS_ERR_NOMEM;
     stage_begin(ctx, "cost");
-    rc = sgbm_cost_volume_dev(ctx, g, l, r, C);
+    for (int f = 0; f < F && !rc; ++f) rc = sgbm_cost_volume_dev(ctx, g, l[f], r[f], C[f]);
     stage_end(ctx, "cost");
     if (rc) return rc;
     stage_begin(ctx, "aggregate");
-    rc = sgbm_aggregate_dev(ctx, g, C, S);
+    rc = sgbm_aggregate_batch_dev(ctx, g, F, C, S);
     stage_end(ctx, "aggregate");
     if (rc) return rc;
+    // F == 1: "wta" and "post" are timed separately; a batch times both under "wta"
     stage_begin(ctx, "wta");
-    rc = sgbm_wta_dev(ctx, g, S, raw);
-    stage_end(ctx, "wta");
-    if (rc) return rc;
-    stage_begin(ctx, "post");
-    rc = sgbm_post_dev(ctx, g, p, raw, disp16);
-    stage_end(ctx, "post");
+    for (int f = 0; f < F && !rc; ++f) {
+        rc = sgbm_wta_dev(ctx, g, S[f], raw);
+        if (F == 1) { stage_end(ctx, "wta"); stage_begin(ctx, "post"); }
+        if (!rc) rc = sgbm_post_dev(ctx, g, p, raw, disp16[f]);
+    }
+    stage_end(ctx, F == 1 ? "post" : "wta");
     return rc;
+}
+
+int sgbm_compute16_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
+                       int16_t* disp16, int16_t* raw16_tap)
+{
+    return sgbm_compute16_batch_dev(ctx, p, 1, &l, &r, w, h, &disp16, raw16_tap);
 }
 
 static int upload_pair(mvs_ctx* ctx, const uint8_t* l, const uint8_t* r, int channels, int w, int h, size_t step,
@@ -117,7 +136,7 @@ extern "C" int mvs_sgbm_volumes(mvs_ctx* ctx, const mvs_sgbm_params* p, const ui
     if (rc) return rc;
     size_t npix = (size_t)g.H * g.W1;
     MVS_ARENA(ctx, int16_t, tmp, "sgbm.api.unpad", npix * g.D);
-    const char* names[2] = {"sgbm.C", "sgbm.S"};
+    const char* names[2] = {"sgbm.C.0", "sgbm.S.0"};
     int16_t* outs[2] = {C, S};
     for (int k = 0; k < 2; ++k) {
         if (!outs[k]) continue;

@@ -108,16 +108,30 @@ __global__ void median3_kernel(const int16_t* __restrict__ src, int W, int H, in
     dst[(size_t)y * W + x] = (int16_t)v[4];
 }
 
-// ---- speckle filter (cv::filterSpeckles): 4-connected components via lock-free union-find ------------------
-__device__ __forceinline__ int uf_find(const int* L, int i)
+// ---- speckle filter (cv::filterSpeckles): 4-connected components, sizes <= maxSpeckleSize removed -----------
+// Run-based union-find: (1) every horizontal run of connected pixels is labelled with its first pixel and its
+// length is counted there (one warp per row, ballots); (2) vertically connected runs are merged with lock-free
+// unions (atomicMin hooking, path halving), skipping pixels whose left neighbour already made the same merge;
+// (3) every run adds its length to its component's root; (4) small components are erased.  Component sizes do
+// not depend on traversal order, so the result is bit-exact with the reference's flood fill.
+__device__ __forceinline__ bool sp_conn(int a, int b, int newVal, int maxDiff)
+{
+    return a != newVal && b != newVal && abs(a - b) <= maxDiff;
+}
+__device__ __forceinline__ int uf_find(int* L, int i)
 {
     int p = L[i];
-    while (p != i) { i = p; p = L[i]; }
+    while (p != i) {
+        int gp = L[p];
+        if (gp != p) L[i] = gp;  // path halving: racy, but only ever re-points a node to one of its ancestors
+        i = p;
+        p = gp;
+    }
     return i;
 }
 __device__ __forceinline__ void uf_union(int* L, int a, int b)
 {
-    for (int guard = 0; guard < (1 << 24); ++guard) {
+    for (int guard = 0; guard < (1 << 22); ++guard) {
         a = uf_find(L, a);
         b = uf_find(L, b);
         if (a == b) return;
@@ -127,33 +141,78 @@ __device__ __forceinline__ void uf_union(int* L, int a, int b)
         a = old;
     }
 }
-__global__ void speckle_init_kernel(int* L, int* cnt, size_t n)
+// one warp per row: L[i] = index of the first pixel of i's run, cnt[run start] = run length
+__global__ void __launch_bounds__(256)
+speckle_runs_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* __restrict__ L,
+                    int* __restrict__ cnt)
 {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { L[i] = (int)i; cnt[i] = 0; }
+    const int lane = threadIdx.x & 31;
+    const int y = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (y >= H) return;
+    const int16_t* row = img + (size_t)y * W;
+    int carry = -1;          // run start (x) of the previous chunk's last pixel, -1 if that pixel is invalid
+    int prev_last = newVal;  // value of the previous chunk's last pixel
+    for (int x0 = 0; x0 < W; x0 += 32) {
+        const int x = x0 + lane;
+        const int v = x < W ? row[x] : newVal;
+        int left = __shfl_up_sync(0xffffffffu, v, 1);
+        if (lane == 0) left = prev_last;
+        const bool valid = v != newVal;
+        const bool link = valid && x > 0 && sp_conn(v, left, newVal, maxDiff);
+        const unsigned starts = __ballot_sync(0xffffffffu, valid && !link);  // lanes where a run begins
+        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+        const unsigned below = starts & (0xffffffffu >> (31 - lane));        // run starts at or before this lane
+        const int start = below ? x0 + (31 - __clz(below)) : carry;
+        const int i = y * W + x;
+        if (x < W) L[i] = valid ? y * W + start : i;
+        // length of the part of each run inside this chunk, counted by the run's first lane in the chunk
+        if (valid && (!link || lane == 0)) {
+            unsigned stop = ~vmask | starts;                                  // a run ends before the next start / hole
+            stop &= (lane == 31) ? 0u : (0xffffffffu << (lane + 1));
+            const int end = stop ? __ffs(stop) - 1 : 32;
+            const int len = end - lane;
+            atomicAdd(cnt + y * W + start, len);  // cnt is zeroed before the kernel; a run may span several chunks
+        }
+        carry = __shfl_sync(0xffffffffu, valid ? start : -1, 31);
+        prev_last = __shfl_sync(0xffffffffu, v, 31);
+    }
 }
-__global__ void speckle_union_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L)
+__global__ void speckle_merge_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L)
 {
-    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y + 1;
+    if (x >= W || y >= H) return;
+    const int i = y * W + x;
+    const int v = img[i], u = img[i - W];
+    if (!sp_conn(v, u, newVal, maxDiff)) return;
+    if (x > 0) {  // the left neighbour already merges the same two runs
+        const int vl = img[i - 1], ul = img[i - W - 1];
+        if (sp_conn(v, vl, newVal, maxDiff) && sp_conn(u, ul, newVal, maxDiff) && sp_conn(vl, ul, newVal, maxDiff)) return;
+    }
+    uf_union(L, L[i], L[i - W]);
+}
+// every run start adds its run length to its component's root and then points straight at it
+__global__ void speckle_resolve_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L, int* cnt)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
     if (x >= W) return;
-    int i = y * W + x, v = img[i];
+    const int i = y * W + x;
+    const int v = img[i];
     if (v == newVal) return;
-    if (x + 1 < W) { int r = img[i + 1]; if (r != newVal && abs(r - v) <= maxDiff) uf_union(L, i, i + 1); }
-    if (y + 1 < H) { int r = img[i + W]; if (r != newVal && abs(r - v) <= maxDiff) uf_union(L, i, i + W); }
+    if (x > 0 && sp_conn(v, img[i - 1], newVal, maxDiff)) return;  // not a run start
+    int root = i;  // read-only walk: this kernel's only writes to L are final root pointers
+    for (int q = L[root]; q != root; q = L[root]) root = q;
+    if (root != i) {
+        atomicAdd(cnt + root, cnt[i]);
+        L[i] = root;
+    }
 }
-__global__ void speckle_count_kernel(const int16_t* __restrict__ img, size_t n, int newVal, int* L, int* cnt)
+__global__ void speckle_apply_kernel(int16_t* img, size_t n, int newVal, int maxSize, const int* __restrict__ L,
+                                     const int* __restrict__ cnt)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || img[i] == newVal) return;
-    int r = uf_find(L, (int)i);
-    L[i] = r;  // flatten (roots never change after the union kernel)
-    atomicAdd(cnt + r, 1);
-}
-__global__ void speckle_apply_kernel(int16_t* img, size_t n, int newVal, int maxSize, const int* L, const int* cnt)
-{
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n || img[i] == newVal) return;
-    if (cnt[L[i]] <= maxSize) img[i] = (int16_t)newVal;
+    const int root = L[L[i]];  // pixel -> run start -> component root (flattened by the resolve kernel)
+    if (cnt[root] <= maxSize) img[i] = (int16_t)newVal;
 }
 
 __global__ void disp_to_float_kernel(const int16_t* __restrict__ d, size_t n, float* __restrict__ out)
@@ -194,9 +253,10 @@ int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, con
         MVS_ARENA(ctx, int, L, "sgbm.speckle.label", n);
         MVS_ARENA(ctx, int, cnt, "sgbm.speckle.count", n);
         int maxDiff = 16 * p->speckle_range;
-        speckle_init_kernel<<<cdiv(n, 256), 256, 0, s>>>(L, cnt, n);
-        speckle_union_kernel<<<dim3(cdiv(g.W, 128), g.H), 128, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L);
-        speckle_count_kernel<<<cdiv(n, 256), 256, 0, s>>>(disp16, n, g.INV, L, cnt);
+        MVS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int) * n, s));
+        speckle_runs_kernel<<<cdiv(g.H, 8), 256, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L, cnt);
+        if (g.H > 1) speckle_merge_kernel<<<dim3(cdiv(g.W, 128), g.H - 1), 128, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L);
+        speckle_resolve_kernel<<<dim3(cdiv(g.W, 128), g.H), 128, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L, cnt);
         speckle_apply_kernel<<<cdiv(n, 256), 256, 0, s>>>(disp16, n, g.INV, p->speckle_win, L, cnt);
         MVS_LAUNCH_CHECK_N(ctx, "speckle kernels", 4);
     }

@@ -201,3 +201,26 @@ def test_frame_path_matches_stagewise_oracle(ctx):
     assert np.array_equal(out["cam_hist"], wh) and wh.sum() > 100
     # oracle's own calibration restatement agrees with the host-side numpy one to rounding
     assert np.allclose(np.array(ob.krr_inv[1][:]), np.array(ob2.krr_inv[1][:]), rtol=1e-9, atol=1e-12)
+
+
+def test_frame_batch_equals_single_frames(ctx):
+    """mvs_frame_run_batch (one aggregation launch for all frames) gives exactly what per-frame calls give."""
+    W, H, D = 352, 150, 64
+    sp = _sp(D, 1)
+    hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
+    cams = [synth.make_camera(W, H, D, config=3, cam=c, n_cams=5) for c in range(5)]
+    descs = [api.make_frame_desc(c, sp, hp, synth.HIST_AABB) for c in cams]
+    single = []
+    for i, d in enumerate(descs):
+        res = api.frame_run(ctx, 10 + i, d)
+        single.append(api.frame_fetch(ctx, 10 + i, W, H, res.hw, res.hh))
+    res = api.frame_run_batch(ctx, 0, descs)
+    for i in range(len(descs)):
+        out = api.frame_fetch(ctx, i, W, H, res[i].hw, res[i].hh)
+        assert np.array_equal(out["disp"], single[i]["disp"]) and (out["disp"] > 0).mean() > 0.3
+        assert out["N"] == single[i]["N"] and np.array_equal(out["xy"], single[i]["xy"])
+        assert np.array_equal(out["Xs"], single[i]["Xs"]) and np.array_equal(out["cam_hist"], single[i]["cam_hist"])
+    # and the first one against the oracle
+    rect = [oracle.remap_cubic_bgr8(cams[0]["sensor"][i], cams[0]["mapx"][i], cams[0]["mapy"][i]) for i in range(2)]
+    want = oracle.disp_to_float(oracle.sgbm_compute(_op(sp), oracle.presmooth(rect[0]), oracle.presmooth(rect[1])))
+    assert np.array_equal(single[0]["disp"], want)

@@ -24,7 +24,7 @@ UNITS = {
     "presmooth.cu": [],
     "cost.cu": [],
     "aggregate.cu": [],
-    "aggregate_wave.cu": [],
+    "aggregate_wave.cu": ([f"-DWAVE_R={os.environ['MVS_WAVE_R']}"] if os.environ.get("MVS_WAVE_R") else []),
     "wta_post.cu": [],
     "sgbm.cu": [],
     "frame.cu": [],

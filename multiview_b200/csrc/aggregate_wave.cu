@@ -8,30 +8,36 @@
 // t = x + 2y are independent (a wavefront).  A CTA owns a band of R consecutive rows; warp r walks row r of the
 // band, two pixels behind warp r-1, one pixel per step, all warps meeting at one __syncthreads per step.
 //   * the disparity vector of a pixel is spread over the warp's 32 lanes (2*NW disparities per lane, u16x2);
-//   * L0 stays in registers; L1/L2/L3 of the row above come from a shared-memory ring written by warp r-1
-//     (sentinel words at both ends give the d-1 / d+1 neighbours of lanes 0 and 31 without branches);
-//   * bands are chained through global memory: the last warp of a band streams its L1/L2/L3 rows to a
-//     boundary buffer and publishes its progress; a helper warp of the next band waits for that progress and
-//     copies the boundary row into the ring with cp.async a few pixels ahead of its consumers;
-//   * bands are handed out by an atomic ticket in dependency order, so the band a CTA waits for is always
-//     running or finished (no co-residency assumption); every wait is bounded and raises an error flag.
+//   * L0 stays in registers; L1/L2/L3 of the row above come from a shared-memory ring written by warp r-1.
+//     A ring slot is {min(L) x2, -, -, SENT | L[0..D) | SENT, -, -, -}: the sentinel words give the d-1 / d+1
+//     neighbours of lanes 0 and 31 without branches and the minimum travels with the data;
+//   * image borders need no branches either: the slots "x = -1" and "x = W1" are filled with zeros (Lr = 0,
+//     minLr = 0 outside the image, as the reference initialises its Lr buffers);
+//   * bands are chained through global memory: the last warp of a band streams its slots to a boundary buffer and
+//     publishes its progress; a helper warp of the next band waits for that progress and copies the boundary row
+//     into the ring with cp.async a few pixels ahead of its consumers;
+//   * a launch covers a batch of frames; (frame, band) items are handed out by an atomic ticket in dependency
+//     order, so the band a CTA waits for is always running or finished (no co-residency assumption); every wait
+//     is bounded and raises an error flag instead of hanging.
 #include "common.cuh"
 
 #define SENT2 0x7FFF7FFFu
+#ifndef WAVE_R
 #define WAVE_R 16            // rows (compute warps) per band
+#endif
 #define WAVE_THREADS ((WAVE_R + 1) * 32)
+#ifndef WAVE_PUBLISH
 #define WAVE_PUBLISH 8       // progress is published every this many pixels
+#endif
 #define WAVE_SPIN_LIMIT (1 << 20)
 #define WAVE_CTL_PAD 16
+#define WAVE_L2_AHEAD 8
 
-// A launch sweeps a batch of F camera-frames of equal geometry: tickets interleave the frames (frame = ticket % F,
-// band = ticket / F) so that all frames advance together and their wavefronts fill the machine.
 struct WaveFrame {
     const uint32_t* C;
     const uint32_t* Sin;   // backward sweep: S after the forward sweep (nullptr in the forward sweep)
     uint32_t* Sout;
-    uint32_t* bndL;        // [nbands][W1][3][wpp] boundary path costs
-    uint32_t* bndMin;      // [nbands][W1][2]      boundary minima (3 x u16 + pad)
+    uint32_t* bnd;         // [nbands][W1][3][4 + wpp] boundary slots (header + path costs)
 };
 struct WaveParams {
     WaveFrame f[MVS_MAX_BATCH];
@@ -52,15 +58,10 @@ __device__ __forceinline__ void st_release(int* p, int v)
 {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-template <int BYTES>
-__device__ __forceinline__ void cp_async(void* smem, const void* gmem)
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gmem)
 {
-    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    if (BYTES == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
-    else if (BYTES == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
-    else asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
 }
-#define WAVE_L2_AHEAD 8
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -89,6 +90,7 @@ __device__ __forceinline__ void stw(uint32_t* p, const uint32_t (&w)[NW])
 
 // One path step.  a[] = Lp (this lane's words), left/right = neighbouring words (they supply d-1 of the lane's
 // first and d+1 of its last disparity), minLp2 = min(Lp) in both halves.  Writes L to out[], returns min_d L.
+// Written so that the packed mins go to the integer pipe and the plain adds may go to the FMA pipe (IMAD).
 template <int NW, bool PAD>
 __device__ __forceinline__ uint32_t step_dir(const uint32_t (&a)[NW], uint32_t left, uint32_t right, uint32_t minLp2,
                                              const uint32_t (&Cw)[NW], uint32_t P1x2, uint32_t P2x2,
@@ -100,9 +102,9 @@ __device__ __forceinline__ uint32_t step_dir(const uint32_t (&a)[NW], uint32_t l
     for (int j = 0; j < NW; ++j) {
         uint32_t lo = __byte_perm(j == 0 ? left : a[j == 0 ? 0 : j - 1], a[j], 0x5432);            // Lp[d-1]
         uint32_t hi = __byte_perm(a[j], j == NW - 1 ? right : a[j == NW - 1 ? j : j + 1], 0x5432);  // Lp[d+1]
-        uint32_t t = __viaddmin_u16x2(__vminu2(lo, hi), P1x2, a[j]);
-        t = __vminu2(t, delta);
-        uint32_t l = Cw[j] + t - minLp2;  // per half: t >= minLp and C + (t - minLp) <= 32767, no borrow / carry
+        uint32_t x = __vminu2(lo, hi) + P1x2;           // halves stay below 2^16: a plain add
+        uint32_t t = __vimin3_u16x2(x, a[j], delta);
+        uint32_t l = t + (Cw[j] - minLp2);              // per half: t >= minLp and C + (t - minLp) <= 32767
         if (PAD) l = (l & ~padmask[j]) | (SENT2 & padmask[j]);
         out[j] = l;
         m = __vminu2(m, l);
@@ -111,41 +113,50 @@ __device__ __forceinline__ uint32_t step_dir(const uint32_t (&a)[NW], uint32_t l
     return __reduce_min_sync(0xffffffffu, mm);
 }
 
-// Shared-memory ring geometry (32-bit words).  A slot holds one pixel's path costs with 4 pad words on each
-// side; pad word 3 and pad word SLOT-4 are the d = -1 / d = D sentinels.
+// Shared-memory geometry (32-bit words).
 template <int NW>
 struct Ring {
     static constexpr int WPP = NW * 32;        // words per pixel
-    static constexpr int SLOT = WPP + 8;
-    static constexpr int ROW_SLOTS = 10;       // compute rows: L1 x4, L2 x4, L3 x2
-    static constexpr int HELP_SLOTS = 24;      // helper row: 3 directions x 8
-    static constexpr int NSLOTS = WAVE_R * ROW_SLOTS + HELP_SLOTS;
+    static constexpr int SLOT = WPP + 8;       // header(4) + data + tail(4)
+    static constexpr int BSLOT = WPP + 4;      // boundary-buffer slot in global memory: header + data
+    static constexpr int ROW_SLOTS = 10;       // rows written by compute warps: L1 x4, L2 x4, L3 x2
+    static constexpr int HELP_SLOTS = 24;      // row above the band (helper): 3 directions x 8
+    static constexpr int NSLOTS = HELP_SLOTS + WAVE_R * ROW_SLOTS;
     static constexpr int WORDS = NSLOTS * SLOT;
-    // ring row rr in [0, R] (0 = row above the band, filled by the helper), direction 1..3, pixel x
-    __device__ static __forceinline__ int slot(int rr, int dir, int x)
-    {
-        if (rr == 0) return (dir - 1) * 8 + (x & 7);
-        int base = HELP_SLOTS + (rr - 1) * ROW_SLOTS;
-        return dir == 1 ? base + (x & 3) : (dir == 2 ? base + 4 + (x & 3) : base + 8 + (x & 1));
-    }
+    static constexpr int STAGE = 4;            // cp.async stages of the per-warp C (and S) stream
+    static constexpr int STREAM_WORDS = WAVE_R * STAGE * WPP;
 };
 
-template <int NW, int DIRMASK, bool PAD>
+template <int NW>
+__device__ __forceinline__ void cp_async_lane(uint32_t smem_addr, const uint32_t* g)
+{
+    if (NW == 4) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
+    else if (NW == 2) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_addr), "l"(g) : "memory");
+    else {
+#pragma unroll
+        for (int j = 0; j < NW; ++j)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_addr + 4 * j), "l"(g + j) : "memory");
+    }
+}
+
+template <int NW, int DIRMASK, bool PAD, bool BWD>
 __global__ void __launch_bounds__(WAVE_THREADS, 1)
 wave_kernel(WaveParams p)
 {
     using RG = Ring<NW>;
     constexpr bool VERT = (DIRMASK & 0xE) != 0;
     extern __shared__ __align__(16) uint32_t ring[];
-    __shared__ uint16_t mins[WAVE_R + 1][3][8];          // [ring row][dir-1][x & 7]; row 0 unused (see hmins)
-    __shared__ __align__(8) uint16_t hmins[8][4];        // helper row minima: [x & 7][dir-1]
-    __shared__ int s_band;
+    uint32_t* cstream = ring + RG::WORDS;                  // [warp][stage][WPP] cost stream
+    uint32_t* sstream = cstream + RG::STREAM_WORDS;        // [warp][stage][WPP] S-in stream (backward sweep only)
+    __shared__ int s_item;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const bool helper = wid == WAVE_R;
+    const int r = wid;
     const int W1 = p.W1;
     const uint32_t P1x2 = wdup16((uint32_t)p.P1), P2x2 = wdup16((uint32_t)p.P2);
+    const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
 
-    for (int s = threadIdx.x; s < RG::NSLOTS; s += blockDim.x) {  // sentinels: written once
+    for (int s = threadIdx.x; s < RG::NSLOTS; s += blockDim.x) {  // sentinels: written once, never overwritten
         ring[s * RG::SLOT + 3] = SENT2;
         ring[s * RG::SLOT + RG::SLOT - 4] = SENT2;
     }
@@ -155,28 +166,36 @@ wave_kernel(WaveParams p)
         int d0 = (lane * NW + j) * 2;
         padmask[j] = (d0 >= p.D ? 0xffffu : 0u) | (d0 + 1 >= p.D ? 0xffff0000u : 0u);
     }
+    // ring rows: what this warp reads (the row above) and what it writes (for the row below)
+    const int rd_slot0 = r == 0 ? 0 : RG::HELP_SLOTS + (r - 1) * RG::ROW_SLOTS;
+    const int rm1 = r == 0 ? 7 : 3, rm2 = rm1, rm3 = r == 0 ? 7 : 1;
+    const int lw = 4 + lane * NW;  // this lane's first data word inside a slot
+    const int rb1 = rd_slot0 * RG::SLOT + lw, rb2 = (rd_slot0 + (r == 0 ? 8 : 4)) * RG::SLOT + lw,
+              rb3 = (rd_slot0 + (r == 0 ? 16 : 8)) * RG::SLOT + lw;
+    const int wr_slot0 = RG::HELP_SLOTS + r * RG::ROW_SLOTS;
+    const int wb1 = wr_slot0 * RG::SLOT + lw, wb2 = (wr_slot0 + 4) * RG::SLOT + lw, wb3 = (wr_slot0 + 8) * RG::SLOT + lw;
+    const int my_stream = (r * RG::STAGE) * RG::WPP + lane * NW;  // this lane's words in stage 0 of the warp's streams
 
     for (;;) {
         __syncthreads();
-        if (threadIdx.x == 0) s_band = atomicAdd(p.ticket, 1);
+        if (threadIdx.x == 0) s_item = atomicAdd(p.ticket, 1);
         __syncthreads();
-        if (s_band >= p.nbands * p.F) break;
-        const int band = s_band / p.F, fi = s_band - band * p.F;
+        if (s_item >= p.nbands * p.F) break;
+        const int band = s_item / p.F, fi = s_item - band * p.F;
         const WaveFrame& fr = p.f[fi];
         const int ys0 = band * WAVE_R;  // first sweep row of the band
         const int rows = min(WAVE_R, p.H - ys0);
         const bool first_band = band == 0, last_band = band == p.nbands - 1;
-        const uint32_t* bL = fr.bndL + (size_t)(first_band ? 0 : band - 1) * W1 * 3 * RG::WPP;  // written by the previous band
-        const uint32_t* bM = fr.bndMin + (size_t)(first_band ? 0 : band - 1) * W1 * 2;
-        uint32_t* oL = fr.bndL + (size_t)band * W1 * 3 * RG::WPP;
-        uint32_t* oM = fr.bndMin + (size_t)band * W1 * 2;
+        const uint32_t* bin = fr.bnd + (size_t)(first_band ? 0 : band - 1) * W1 * 3 * RG::BSLOT;  // written by the previous band
+        uint32_t* bout = fr.bnd + (size_t)band * W1 * 3 * RG::BSLOT;
         int* my_progress = p.progress + (size_t)fi * p.nbands + band;
         const int* prev_progress = my_progress - (first_band ? 0 : 1);
         const bool fetch = helper && VERT && !first_band;
         int seen = 0;  // helper: cached progress of the previous band
         bool failed = false;
 
-        // helper: request boundary pixel xp (one cp.async group per call, possibly empty)
+        // helper: bring boundary pixel xp into ring row 0 (one cp.async group per call, possibly empty);
+        // xp == W1 is the zero slot behind the last pixel
         auto helper_issue = [&](int xp) {
             if (xp < W1) {
                 const int need = xp + 1;
@@ -190,23 +209,36 @@ wave_kernel(WaveParams p)
                         __nanosleep(32);
                     }
                 }
+                const uint32_t* src = bin + (size_t)xp * 3 * RG::BSLOT;
 #pragma unroll
                 for (int dir = 1; dir <= 3; ++dir) {
                     if (!(DIRMASK & (1 << dir))) continue;
-                    uint32_t* dst = ring + RG::slot(0, dir, xp) * RG::SLOT + 4 + lane * NW;
-                    const uint32_t* src = bL + ((size_t)xp * 3 + (dir - 1)) * RG::WPP + lane * NW;
-                    cp_async<NW == 4 ? 16 : (NW == 2 ? 8 : 4)>(dst, src);
-                    if (NW == 3) { cp_async<4>(dst + 1, src + 1); cp_async<4>(dst + 2, src + 2); }
+                    const uint32_t dst = ring_s + (((dir - 1) * 8 + (xp & 7)) * RG::SLOT) * 4;
+                    const uint32_t* sp = src + (dir - 1) * RG::BSLOT;
+                    if (lane < RG::WPP / 4) cp_async16(dst + (lane + 1) * 16, sp + (lane + 1) * 4);
+                    if (lane == 0) cp_async16(dst, sp);  // header: {min, -, -, SENT}
                 }
-                if (lane == 0) cp_async<8>(&hmins[xp & 7][0], bM + (size_t)xp * 2);
+            } else if (xp == W1) {
+#pragma unroll
+                for (int dir = 1; dir <= 3; ++dir) {
+                    uint32_t* dst = ring + ((dir - 1) * 8 + (xp & 7)) * RG::SLOT;
+                    for (int k = lane; k < RG::WPP; k += 32) dst[4 + k] = 0;
+                    if (lane == 0) dst[0] = 0;
+                }
             }
             cp_async_commit();
         };
 
         if (helper && VERT && first_band) {  // the row above the image: Lr = 0, minLr = 0
-            for (int s = 0; s < RG::HELP_SLOTS; ++s)
+            for (int s = 0; s < RG::HELP_SLOTS; ++s) {
                 for (int k = lane; k < RG::WPP; k += 32) ring[s * RG::SLOT + 4 + k] = 0;
-            if (lane < 32) ((uint16_t*)hmins)[lane] = 0;
+                if (lane == 0) ring[s * RG::SLOT] = 0;
+            }
+        }
+        if (!helper && VERT) {  // "x = -1" slot of the row this warp reads (direction 1 at x = 0)
+            uint32_t* z = ring + (rb1 - lw) + (-1 & rm1) * RG::SLOT;
+            for (int k = lane; k < RG::WPP; k += 32) z[4 + k] = 0;
+            if (lane == 0) z[0] = 0;
         }
         if (fetch) {
             for (int xp = 0; xp < 4; ++xp) helper_issue(xp);
@@ -214,23 +246,33 @@ wave_kernel(WaveParams p)
         }
 
         // per-warp state of a compute row
-        const int r = wid;
         const bool active_row = !helper && r < rows;
-        uint32_t L0[NW], Cw[NW], Sw[NW];
+        const bool to_ring = r + 1 < rows, to_global = VERT && r + 1 == rows && !last_band;
+        uint32_t L0[NW];
 #pragma unroll
-        for (int j = 0; j < NW; ++j) { L0[j] = 0; Sw[j] = 0; Cw[j] = 0; }
+        for (int j = 0; j < NW; ++j) L0[j] = 0;
         uint32_t minL0 = 0;
-        long long off = 0, stride = 0;
+        uint32_t gbase = 0;  // word offset of this lane's words of the row's first pixel in the volumes (< 2^32 words)
+        int gstride = 0;
+        const uint32_t cs_s = ring_s + (RG::WORDS + my_stream) * 4, ss_s = cs_s + RG::STREAM_WORDS * 4;
+        auto stream_issue = [&](int xq) {  // request pixel xq of this row into stage xq % STAGE (one group, maybe empty)
+            if (xq < W1) {
+                const uint32_t o = gbase + (uint32_t)(xq * gstride);
+                cp_async_lane<NW>(cs_s + (xq & (RG::STAGE - 1)) * (RG::WPP * 4), fr.C + o);
+                if (BWD) cp_async_lane<NW>(ss_s + (xq & (RG::STAGE - 1)) * (RG::WPP * 4), fr.Sin + o);
+            }
+            cp_async_commit();
+        };
         if (active_row) {
             const int ys = ys0 + r;
-            const int y = p.flip ? p.H - 1 - ys : ys;
-            const int x0 = p.flip ? W1 - 1 : 0;
-            off = ((long long)y * W1 + x0) * RG::WPP + lane * NW;
-            stride = p.flip ? -(long long)RG::WPP : (long long)RG::WPP;
-            ldw<NW>(fr.C + off, Cw);
-            if (fr.Sin) ldw<NW>(fr.Sin + off, Sw);
+            const int y = BWD ? p.H - 1 - ys : ys;
+            const int x0 = BWD ? W1 - 1 : 0;
+            gbase = (uint32_t)(((size_t)y * W1 + x0) * RG::WPP + lane * NW);
+            gstride = BWD ? -RG::WPP : RG::WPP;
+            for (int xq = 0; xq < RG::STAGE - 1; ++xq) stream_issue(xq);
         }
-        const int nsteps = W1 + 2 * (rows - 1);
+        uint32_t* gout = bout + lw;  // this lane's data words of boundary pixel 0, direction 1
+        const int nsteps = W1 + 2 * (rows - 1) + 1;
         __syncthreads();
 
         for (int t = 0; t < nsteps; ++t) {
@@ -240,22 +282,19 @@ wave_kernel(WaveParams p)
             } else if (active_row) {
                 const int x = t - 2 * r;
                 if (x >= 0 && x < W1) {
-                    uint32_t Cn[NW], Sn[NW];
-                    const bool more = x + 1 < W1;
-                    if (x + WAVE_L2_AHEAD < W1) {  // pull the volumes into L2 well ahead of the register prefetch
-                        prefetch_l2(fr.C + off + WAVE_L2_AHEAD * stride);
-                        if (fr.Sin) prefetch_l2(fr.Sin + off + WAVE_L2_AHEAD * stride);
-                    }
-                    if (more) {  // next pixel's C (and S) before the dependent chain
-                        ldw<NW>(fr.C + off + stride, Cn);
-                        if (fr.Sin) ldw<NW>(fr.Sin + off + stride, Sn);
-                    }
-                    uint32_t acc[NW], Lo[NW];
+                    stream_issue(x + RG::STAGE - 1);
+                    cp_async_wait<RG::STAGE - 1>();  // this lane's words of pixel x have landed (own copies only)
+                    uint32_t Cw[NW], Sw[NW];
+                    ldw<NW>(cstream + my_stream + (x & (RG::STAGE - 1)) * RG::WPP, Cw);
+                    if (BWD) ldw<NW>(sstream + my_stream + (x & (RG::STAGE - 1)) * RG::WPP, Sw);
+                    uint32_t acc[NW], Lo1[NW], Lo2[NW], Lo3[NW];
+                    uint32_t mn1 = 0, mn2 = 0, mn3 = 0;
                     if (DIRMASK & 1) {  // direction 0: predecessor (x-1, y), kept in registers
                         uint32_t left = __shfl_up_sync(0xffffffffu, L0[NW - 1], 1);
                         uint32_t right = __shfl_down_sync(0xffffffffu, L0[0], 1);
                         if (lane == 0) left = SENT2;
                         if (lane == 31) right = SENT2;
+                        uint32_t Lo[NW];
                         uint32_t mn = step_dir<NW, PAD>(L0, left, right, minL0, Cw, P1x2, P2x2, padmask, Lo);
 #pragma unroll
                         for (int j = 0; j < NW; ++j) { L0[j] = Lo[j]; acc[j] = Lo[j]; }
@@ -264,80 +303,112 @@ wave_kernel(WaveParams p)
 #pragma unroll
                         for (int j = 0; j < NW; ++j) acc[j] = 0;
                     }
+                    if (DIRMASK & 2) {  // direction 1: predecessor (x-1, y-1)
+                        const uint32_t* sl = ring + rb1 + ((x - 1) & rm1) * RG::SLOT;
+                        uint32_t a[NW];
+                        ldw<NW>(sl, a);
+                        mn1 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo1);
 #pragma unroll
-                    for (int dir = 1; dir <= 3; ++dir) {  // predecessors in the row above, from the ring
-                        if (!(DIRMASK & (1 << dir))) continue;
-                        const int xp = dir == 1 ? x - 1 : (dir == 2 ? x : x + 1);
-                        uint32_t a[NW], left, right, mp;
-                        if (xp >= 0 && xp < W1) {
-                            const uint32_t* sl = ring + RG::slot(r, dir, xp) * RG::SLOT + 4 + lane * NW;
-                            ldw<NW>(sl, a);
-                            left = sl[-1];
-                            right = sl[NW];
-                            mp = wdup16(r == 0 ? (uint32_t)hmins[xp & 7][dir - 1] : (uint32_t)mins[r][dir - 1][xp & 7]);
-                        } else {  // predecessor outside the image: Lr = 0, minLr = 0
+                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo1[j], SENT2);
+                    }
+                    if (DIRMASK & 4) {  // direction 2: predecessor (x, y-1)
+                        const uint32_t* sl = ring + rb2 + (x & rm2) * RG::SLOT;
+                        uint32_t a[NW];
+                        ldw<NW>(sl, a);
+                        mn2 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo2);
 #pragma unroll
-                            for (int j = 0; j < NW; ++j) a[j] = 0;
-                            left = lane == 0 ? SENT2 : 0u;
-                            right = lane == 31 ? SENT2 : 0u;
-                            mp = 0;
+                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo2[j], SENT2);
+                    }
+                    if (DIRMASK & 8) {  // direction 3: predecessor (x+1, y-1)
+                        const uint32_t* sl = ring + rb3 + ((x + 1) & rm3) * RG::SLOT;
+                        uint32_t a[NW];
+                        ldw<NW>(sl, a);
+                        mn3 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo3);
+#pragma unroll
+                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo3[j], SENT2);
+                    }
+                    // S = min(S_in + sum L, 32767)
+                    if (BWD) {
+#pragma unroll
+                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(Sw[j], acc[j], SENT2);
+                    }
+                    stw<NW>(fr.Sout + (gbase + (uint32_t)(x * gstride)), acc);
+                    if (to_ring) {  // for the row below
+                        if (DIRMASK & 2) {
+                            uint32_t* d = ring + wb1 + (x & 3) * RG::SLOT;
+                            stw<NW>(d, Lo1);
+                            if (lane == 0) d[-4] = wdup16(mn1);
                         }
-                        uint32_t mn = step_dir<NW, PAD>(a, left, right, mp, Cw, P1x2, P2x2, padmask, Lo);
-                        if (r + 1 < rows) {  // for the row below
-                            stw<NW>(ring + RG::slot(r + 1, dir, x) * RG::SLOT + 4 + lane * NW, Lo);
-                            if (lane == 0) mins[r + 1][dir - 1][x & 7] = (uint16_t)mn;
-                        } else if (!last_band) {  // for the next band
-                            stw<NW>(oL + ((size_t)x * 3 + (dir - 1)) * RG::WPP + lane * NW, Lo);
-                            if (lane == 0) ((uint16_t*)(oM + (size_t)x * 2))[dir - 1] = (uint16_t)mn;
+                        if (DIRMASK & 4) {
+                            uint32_t* d = ring + wb2 + (x & 3) * RG::SLOT;
+                            stw<NW>(d, Lo2);
+                            if (lane == 0) d[-4] = wdup16(mn2);
                         }
-#pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo[j], SENT2);
+                        if (DIRMASK & 8) {
+                            uint32_t* d = ring + wb3 + (x & 1) * RG::SLOT;
+                            stw<NW>(d, Lo3);
+                            if (lane == 0) d[-4] = wdup16(mn3);
+                        }
+                    } else if (to_global) {  // for the next band
+                        if (DIRMASK & 2) {
+                            stw<NW>(gout, Lo1);
+                            if (lane == 0) *(uint4*)(gout - lw) = make_uint4(wdup16(mn1), 0u, 0u, SENT2);
+                        }
+                        if (DIRMASK & 4) {
+                            stw<NW>(gout + RG::BSLOT, Lo2);
+                            if (lane == 0) *(uint4*)(gout - lw + RG::BSLOT) = make_uint4(wdup16(mn2), 0u, 0u, SENT2);
+                        }
+                        if (DIRMASK & 8) {
+                            stw<NW>(gout + 2 * RG::BSLOT, Lo3);
+                            if (lane == 0) *(uint4*)(gout - lw + 2 * RG::BSLOT) = make_uint4(wdup16(mn3), 0u, 0u, SENT2);
+                        }
+                        gout += 3 * RG::BSLOT;
+                        if (((x + 1) % WAVE_PUBLISH) == 0 || x + 1 == W1) {
+                            // the warp barrier orders every lane's boundary stores before lane 0's release store
+                            // (release is cumulative over what the warp barrier made visible to lane 0)
+                            __syncwarp();
+                            if (lane == 0) st_release(my_progress, x + 1);
+                        }
                     }
-                    uint32_t So[NW];
-#pragma unroll
-                    for (int j = 0; j < NW; ++j) So[j] = fr.Sin ? __viaddmin_u16x2(Sw[j], acc[j], SENT2) : acc[j];
-                    stw<NW>(fr.Sout + off, So);
-                    if (VERT && r + 1 == rows && !last_band && (((x + 1) % WAVE_PUBLISH) == 0 || x + 1 == W1)) {
-                        __threadfence();
-                        __syncwarp();
-                        if (lane == 0) st_release(my_progress, x + 1);
-                    }
-                    off += stride;
-                    if (more) {
-#pragma unroll
-                        for (int j = 0; j < NW; ++j) { Cw[j] = Cn[j]; Sw[j] = Sn[j]; }
-                    }
+                } else if (x == W1 && to_ring && (DIRMASK & 8)) {
+                    // zero slot "x = W1" for direction 3 of the row below (its predecessor is outside the image)
+                    uint32_t* d = ring + wb3 + (x & 1) * RG::SLOT;
+                    for (int k = lane; k < RG::WPP; k += 32) d[k - lw + 4] = 0;
+                    if (lane == 0) d[-4] = 0;
                 }
             }
             __syncthreads();
         }
-        if (fetch) cp_async_wait<0>();
+        cp_async_wait<0>();
     }
 }
 
-template <int NW, int DIRMASK, bool PAD>
+template <int NW, int DIRMASK, bool PAD, bool BWD>
 static int launch_wave(mvs_ctx* ctx, const WaveParams& p)
 {
-    const int smem = Ring<NW>::WORDS * 4;
-    MVS_CUDA(ctx, cudaFuncSetAttribute(wave_kernel<NW, DIRMASK, PAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    int per_sm = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, wave_kernel<NW, DIRMASK, PAD>, WAVE_THREADS, smem);
-    if (per_sm < 1) per_sm = 1;
+    const int smem = (Ring<NW>::WORDS + (BWD ? 2 : 1) * Ring<NW>::STREAM_WORDS) * 4;
+    static int per_sm = 0;  // per instantiation
+    if (!per_sm) {
+        MVS_CUDA(ctx, cudaFuncSetAttribute(wave_kernel<NW, DIRMASK, PAD, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        int n = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wave_kernel<NW, DIRMASK, PAD, BWD>, WAVE_THREADS, smem);
+        per_sm = n < 1 ? 1 : n;
+    }
     int grid = min(p.nbands * p.F, ctx->sm_count * per_sm);
-    wave_kernel<NW, DIRMASK, PAD><<<grid, WAVE_THREADS, smem, ctx->stream>>>(p);
+    wave_kernel<NW, DIRMASK, PAD, BWD><<<grid, WAVE_THREADS, smem, ctx->stream>>>(p);
     MVS_LAUNCH_CHECK(ctx, "wave_kernel");
     return MVS_OK;
 }
 
-template <int DIRMASK>
+template <int DIRMASK, bool BWD>
 static int launch_wave_nw(mvs_ctx* ctx, const SgbmGeom& g, const WaveParams& p)
 {
     bool pad = g.Dp != g.D;
     switch (g.Dp / 64) {
-    case 1: return pad ? launch_wave<1, DIRMASK, true>(ctx, p) : launch_wave<1, DIRMASK, false>(ctx, p);
-    case 2: return pad ? launch_wave<2, DIRMASK, true>(ctx, p) : launch_wave<2, DIRMASK, false>(ctx, p);
-    case 3: return pad ? launch_wave<3, DIRMASK, true>(ctx, p) : launch_wave<3, DIRMASK, false>(ctx, p);
-    case 4: return pad ? launch_wave<4, DIRMASK, true>(ctx, p) : launch_wave<4, DIRMASK, false>(ctx, p);
+    case 1: return pad ? launch_wave<1, DIRMASK, true, BWD>(ctx, p) : launch_wave<1, DIRMASK, false, BWD>(ctx, p);
+    case 2: return pad ? launch_wave<2, DIRMASK, true, BWD>(ctx, p) : launch_wave<2, DIRMASK, false, BWD>(ctx, p);
+    case 3: return pad ? launch_wave<3, DIRMASK, true, BWD>(ctx, p) : launch_wave<3, DIRMASK, false, BWD>(ctx, p);
+    case 4: return pad ? launch_wave<4, DIRMASK, true, BWD>(ctx, p) : launch_wave<4, DIRMASK, false, BWD>(ctx, p);
     }
     return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "aggregate: Dp=%d", g.Dp);
 }
@@ -348,9 +419,8 @@ int sgbm_aggregate_wave_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const 
     const int nbands = cdiv(g.H, WAVE_R);
     const size_t wpp = (size_t)g.Dp / 2;
     const int ctl_pass = F * nbands + 2 * WAVE_CTL_PAD;
-    const size_t bndL_sz = (size_t)nbands * g.W1 * 3 * wpp, bndM_sz = (size_t)nbands * g.W1 * 2;
-    MVS_ARENA(ctx, uint32_t, bndL, "sgbm.wave.bndL", bndL_sz * F);
-    MVS_ARENA(ctx, uint32_t, bndMin, "sgbm.wave.bndMin", bndM_sz * F);
+    const size_t bnd_sz = (size_t)nbands * g.W1 * 3 * (wpp + 4);
+    MVS_ARENA(ctx, uint32_t, bnd, "sgbm.wave.bnd", bnd_sz * F);
     MVS_ARENA(ctx, int, ctl, "sgbm.wave.ctl", (size_t)2 * ctl_pass);
     MVS_ARENA(ctx, int, err, "sgbm.wave.err", 1);
     if (!ctx->wave_err_cleared) {
@@ -366,17 +436,17 @@ int sgbm_aggregate_wave_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const 
     // forward sweep
     for (int f = 0; f < F; ++f) {
         p.f[f].C = (const uint32_t*)C[f]; p.f[f].Sin = nullptr; p.f[f].Sout = (uint32_t*)S[f];
-        p.f[f].bndL = bndL + bndL_sz * f; p.f[f].bndMin = bndMin + bndM_sz * f;
+        p.f[f].bnd = bnd + bnd_sz * f;
     }
     p.flip = 0; p.ticket = ctl; p.progress = ctl + WAVE_CTL_PAD;
-    rc = g.mode == MVS_MODE_HH4 ? launch_wave_nw<0x5>(ctx, g, p) : launch_wave_nw<0xF>(ctx, g, p);
+    rc = g.mode == MVS_MODE_HH4 ? launch_wave_nw<0x5, false>(ctx, g, p) : launch_wave_nw<0xF, false>(ctx, g, p);
     if (rc) return rc;
     // backward sweep: the same recurrence on the image flipped in x and y
     for (int f = 0; f < F; ++f) p.f[f].Sin = (const uint32_t*)S[f];
     p.flip = 1; p.ticket = ctl + ctl_pass; p.progress = ctl + ctl_pass + WAVE_CTL_PAD;
-    if (g.mode == MVS_MODE_HH) rc = launch_wave_nw<0xF>(ctx, g, p);
-    else if (g.mode == MVS_MODE_HH4) rc = launch_wave_nw<0x5>(ctx, g, p);
-    else rc = launch_wave_nw<0x1>(ctx, g, p);  // MODE_SGBM: only the (x+1, y) direction
+    if (g.mode == MVS_MODE_HH) rc = launch_wave_nw<0xF, true>(ctx, g, p);
+    else if (g.mode == MVS_MODE_HH4) rc = launch_wave_nw<0x5, true>(ctx, g, p);
+    else rc = launch_wave_nw<0x1, true>(ctx, g, p);  // MODE_SGBM: only the (x+1, y) direction
     return rc;
 }
 

@@ -181,7 +181,7 @@ def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
 
-    from multiview_b200 import api, synth
+    from multiview_b200 import api, shard, synth
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -194,7 +194,8 @@ def run_ours(args, rank, world, local_rank):
     sp = api.StereoSGBMParams(sg_num_disparities=D, sg_mode=args.mode)
     hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
     n_cams = world * B
-    cams = [synth.make_camera(W, H, D, config=2, cam=rank * B + b, frame=0, n_cams=n_cams) for b in range(min(B, args.distinct))]
+    my_cams = shard.cameras_for_rank(n_cams, world, rank)  # camera c lives on rank c % world
+    cams = [synth.make_camera(W, H, D, config=2, cam=c, frame=0, n_cams=n_cams) for c in my_cams[:min(B, args.distinct)]]
 
     # pinned host copies (e2e) and device-resident copies (value)
     host, devt, descs_dev, descs_host = [], [], [], []
@@ -370,7 +371,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", type=int, default=1, help="StereoSGBM mode: 1 = MODE_HH (8-path, headline), 3 = HH4, 0 = SGBM")
-    ap.add_argument("--batch", type=int, default=4, help="camera-frames per GPU per step (<= 16)")
+    ap.add_argument("--batch", type=int, default=8, help="camera-frames per GPU per step (<= 16)")
     ap.add_argument("--distinct", type=int, default=2, help="distinct synthetic camera-frames generated per rank")
     ap.add_argument("--ref-threads", type=int, default=16)
     ap.add_argument("--cpu-rows", type=int, default=1080)

@@ -6,13 +6,17 @@
 //
 // Parallelisation: pixel (x,y) depends on (x-1,y) and on three pixels of row y-1, so all pixels with the same
 // t = x + 2y are independent (a wavefront).  A CTA owns a band of R consecutive rows; warp r walks row r of the
-// band, two pixels behind warp r-1, one pixel per step, all warps meeting at one __syncthreads per step.
+// band between two and four pixels behind warp r-1.
 //   * the disparity vector of a pixel is spread over the warp's 32 lanes (2*NW disparities per lane, u16x2);
 //   * L0 stays in registers; L1/L2/L3 of the row above come from a shared-memory ring written by warp r-1.
 //     A ring slot is {min(L) x2, -, -, SENT | L[0..D) | SENT, -, -, -}: the sentinel words give the d-1 / d+1
 //     neighbours of lanes 0 and 31 without branches and the minimum travels with the data;
-//   * image borders need no branches either: the slots "x = -1" and "x = W1" are filled with zeros (Lr = 0,
-//     minLr = 0 outside the image, as the reference initialises its Lr buffers);
+//   * neighbouring warps are coupled only by two shared-memory counters per ring row ("pixels written",
+//     "pixels consumed", release/acquire at CTA scope): there is no CTA-wide barrier inside a band, and the rings
+//     are two slots deeper than lock-step needs, so a warp that stalls does not stall the other fifteen;
+//   * image borders need no branches: the slots "x = -1" and "x = W1" are filled with zeros (Lr = 0, minLr = 0
+//     outside the image, as the reference initialises its Lr buffers);
+//   * C (and S in the backward sweep) stream through a per-warp cp.async pipeline three pixels ahead;
 //   * bands are chained through global memory: the last warp of a band streams its slots to a boundary buffer and
 //     publishes its progress; a helper warp of the next band waits for that progress and copies the boundary row
 //     into the ring with cp.async a few pixels ahead of its consumers;
@@ -27,11 +31,10 @@
 #endif
 #define WAVE_THREADS ((WAVE_R + 1) * 32)
 #ifndef WAVE_PUBLISH
-#define WAVE_PUBLISH 8       // progress is published every this many pixels
+#define WAVE_PUBLISH 8       // inter-band progress is published every this many pixels
 #endif
 #define WAVE_SPIN_LIMIT (1 << 20)
 #define WAVE_CTL_PAD 16
-#define WAVE_L2_AHEAD 8
 
 struct WaveFrame {
     const uint32_t* C;
@@ -58,11 +61,25 @@ __device__ __forceinline__ void st_release(int* p, int v)
 {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ int lds_relaxed(uint32_t saddr)
+{
+    int v;
+    asm volatile("ld.relaxed.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void fence_cta() { asm volatile("fence.acq_rel.cta;" ::: "memory"); }
+__device__ __forceinline__ void sts_release(uint32_t saddr, int v)
+{
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts_relaxed(uint32_t saddr, int v)
+{
+    asm volatile("st.relaxed.cta.shared.s32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
+}
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gmem)
 {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
 }
-__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -119,8 +136,11 @@ struct Ring {
     static constexpr int WPP = NW * 32;        // words per pixel
     static constexpr int SLOT = WPP + 8;       // header(4) + data + tail(4)
     static constexpr int BSLOT = WPP + 4;      // boundary-buffer slot in global memory: header + data
-    static constexpr int ROW_SLOTS = 10;       // rows written by compute warps: L1 x4, L2 x4, L3 x2
-    static constexpr int HELP_SLOTS = 24;      // row above the band (helper): 3 directions x 8
+    // rows written by compute warps: lock-step needs 4 / 3 / 2 slots for L1 / L2 / L3; two more give two pixels of slack
+    static constexpr int D12 = 6, D3 = 4;
+    static constexpr int ROW_SLOTS = 2 * D12 + D3;
+    static constexpr int HD = 8;               // row above the band (helper): 8 slots per direction
+    static constexpr int HELP_SLOTS = 3 * HD;
     static constexpr int NSLOTS = HELP_SLOTS + WAVE_R * ROW_SLOTS;
     static constexpr int WORDS = NSLOTS * SLOT;
     static constexpr int STAGE = 4;            // cp.async stages of the per-warp C (and S) stream
@@ -149,12 +169,15 @@ wave_kernel(WaveParams p)
     uint32_t* cstream = ring + RG::WORDS;                  // [warp][stage][WPP] cost stream
     uint32_t* sstream = cstream + RG::STREAM_WORDS;        // [warp][stage][WPP] S-in stream (backward sweep only)
     __shared__ int s_item;
+    __shared__ int s_done[WAVE_R + 1];   // [ring row k] pixels of ring row k written (k = 0: by the helper, else by warp k-1)
+    __shared__ int s_cons[WAVE_R + 1];   // [ring row k] pixels of ring row k consumed by warp k
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const bool helper = wid == WAVE_R;
     const int r = wid;
     const int W1 = p.W1;
     const uint32_t P1x2 = wdup16((uint32_t)p.P1), P2x2 = wdup16((uint32_t)p.P2);
     const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
+    const uint32_t done_s = (uint32_t)__cvta_generic_to_shared(s_done), cons_s = (uint32_t)__cvta_generic_to_shared(s_cons);
 
     for (int s = threadIdx.x; s < RG::NSLOTS; s += blockDim.x) {  // sentinels: written once, never overwritten
         ring[s * RG::SLOT + 3] = SENT2;
@@ -166,19 +189,19 @@ wave_kernel(WaveParams p)
         int d0 = (lane * NW + j) * 2;
         padmask[j] = (d0 >= p.D ? 0xffffu : 0u) | (d0 + 1 >= p.D ? 0xffff0000u : 0u);
     }
-    // ring rows: what this warp reads (the row above) and what it writes (for the row below)
-    const int rd_slot0 = r == 0 ? 0 : RG::HELP_SLOTS + (r - 1) * RG::ROW_SLOTS;
-    const int rm1 = r == 0 ? 7 : 3, rm2 = rm1, rm3 = r == 0 ? 7 : 1;
+    // ring rows: what this warp reads (the row above: ring row r) and what it writes (ring row r + 1)
     const int lw = 4 + lane * NW;  // this lane's first data word inside a slot
-    const int rb1 = rd_slot0 * RG::SLOT + lw, rb2 = (rd_slot0 + (r == 0 ? 8 : 4)) * RG::SLOT + lw,
-              rb3 = (rd_slot0 + (r == 0 ? 16 : 8)) * RG::SLOT + lw;
+    const int rd12 = r == 0 ? RG::HD : RG::D12, rd3 = r == 0 ? RG::HD : RG::D3;  // depths of the rings this warp reads
+    const int rd_slot0 = r == 0 ? 0 : RG::HELP_SLOTS + (r - 1) * RG::ROW_SLOTS;
+    const int rb1 = rd_slot0 * RG::SLOT + lw, rb2 = (rd_slot0 + rd12) * RG::SLOT + lw, rb3 = (rd_slot0 + 2 * rd12) * RG::SLOT + lw;
     const int wr_slot0 = RG::HELP_SLOTS + r * RG::ROW_SLOTS;
-    const int wb1 = wr_slot0 * RG::SLOT + lw, wb2 = (wr_slot0 + 4) * RG::SLOT + lw, wb3 = (wr_slot0 + 8) * RG::SLOT + lw;
+    const int wb1 = wr_slot0 * RG::SLOT + lw, wb2 = (wr_slot0 + RG::D12) * RG::SLOT + lw, wb3 = (wr_slot0 + 2 * RG::D12) * RG::SLOT + lw;
     const int my_stream = (r * RG::STAGE) * RG::WPP + lane * NW;  // this lane's words in stage 0 of the warp's streams
 
     for (;;) {
-        __syncthreads();
+        __syncthreads();  // every warp has left the previous band
         if (threadIdx.x == 0) s_item = atomicAdd(p.ticket, 1);
+        if (threadIdx.x <= WAVE_R) { s_done[threadIdx.x] = 0; s_cons[threadIdx.x] = 0; }
         __syncthreads();
         if (s_item >= p.nbands * p.F) break;
         const int band = s_item / p.F, fi = s_item - band * p.F;
@@ -190,194 +213,232 @@ wave_kernel(WaveParams p)
         uint32_t* bout = fr.bnd + (size_t)band * W1 * 3 * RG::BSLOT;
         int* my_progress = p.progress + (size_t)fi * p.nbands + band;
         const int* prev_progress = my_progress - (first_band ? 0 : 1);
-        const bool fetch = helper && VERT && !first_band;
-        int seen = 0;  // helper: cached progress of the previous band
         bool failed = false;
 
-        // helper: bring boundary pixel xp into ring row 0 (one cp.async group per call, possibly empty);
-        // xp == W1 is the zero slot behind the last pixel
-        auto helper_issue = [&](int xp) {
-            if (xp < W1) {
-                const int need = xp + 1;
-                if (seen < need && !failed) {
-                    int spins = 0;
-                    while ((seen = ld_acquire(prev_progress)) < need) {
-                        // bounded: a timeout here or anywhere else in the grid ends all waiting (results are then invalid
-                        // and the host reports an error), so a logic fault can never hang the GPU
-                        if (++spins > WAVE_SPIN_LIMIT) { atomicExch(p.error, 1); failed = true; break; }
-                        if ((spins & 1023) == 0 && *(volatile int*)p.error) { failed = true; break; }
-                        __nanosleep(32);
-                    }
-                }
-                const uint32_t* src = bin + (size_t)xp * 3 * RG::BSLOT;
-#pragma unroll
-                for (int dir = 1; dir <= 3; ++dir) {
-                    if (!(DIRMASK & (1 << dir))) continue;
-                    const uint32_t dst = ring_s + (((dir - 1) * 8 + (xp & 7)) * RG::SLOT) * 4;
-                    const uint32_t* sp = src + (dir - 1) * RG::BSLOT;
-                    if (lane < RG::WPP / 4) cp_async16(dst + (lane + 1) * 16, sp + (lane + 1) * 4);
-                    if (lane == 0) cp_async16(dst, sp);  // header: {min, -, -, SENT}
-                }
-            } else if (xp == W1) {
-#pragma unroll
-                for (int dir = 1; dir <= 3; ++dir) {
-                    uint32_t* dst = ring + ((dir - 1) * 8 + (xp & 7)) * RG::SLOT;
-                    for (int k = lane; k < RG::WPP; k += 32) dst[4 + k] = 0;
-                    if (lane == 0) dst[0] = 0;
-                }
+        // bounded wait on a shared-memory counter: every lane polls the same word (a broadcast read)
+        // `seen` caches the last value read, so a warp that runs with slack does not touch the counter at all
+        auto wait_smem = [&](uint32_t saddr, int need, int& seen) {
+            if (seen >= need || failed) return;
+            int spins = 0;
+            while ((seen = lds_relaxed(saddr)) < need) {
+                if (++spins > WAVE_SPIN_LIMIT) { atomicExch(p.error, 1); failed = true; break; }
+                if ((spins & 4095) == 0 && *(volatile int*)p.error) { failed = true; break; }
             }
-            cp_async_commit();
+            fence_cta();  // acquire: the ring accesses below stay behind the counter read
         };
 
-        if (helper && VERT && first_band) {  // the row above the image: Lr = 0, minLr = 0
+        // zero slots prepared before anybody runs: the row above the image, and "x = -1" of the row each warp reads
+        if (helper && VERT && first_band) {
             for (int s = 0; s < RG::HELP_SLOTS; ++s) {
                 for (int k = lane; k < RG::WPP; k += 32) ring[s * RG::SLOT + 4 + k] = 0;
                 if (lane == 0) ring[s * RG::SLOT] = 0;
             }
         }
-        if (!helper && VERT) {  // "x = -1" slot of the row this warp reads (direction 1 at x = 0)
-            uint32_t* z = ring + (rb1 - lw) + (-1 & rm1) * RG::SLOT;
+        if (!helper && VERT) {
+            uint32_t* z = ring + (rb1 - lw) + (rd12 - 1) * RG::SLOT;  // slot (-1 mod depth)
             for (int k = lane; k < RG::WPP; k += 32) z[4 + k] = 0;
             if (lane == 0) z[0] = 0;
         }
-        if (fetch) {
-            for (int xp = 0; xp < 4; ++xp) helper_issue(xp);
-            cp_async_wait<2>();  // pixels 0 and 1 have landed
-        }
-
-        // per-warp state of a compute row
-        const bool active_row = !helper && r < rows;
-        const bool to_ring = r + 1 < rows, to_global = VERT && r + 1 == rows && !last_band;
-        uint32_t L0[NW];
-#pragma unroll
-        for (int j = 0; j < NW; ++j) L0[j] = 0;
-        uint32_t minL0 = 0;
-        uint32_t gbase = 0;  // word offset of this lane's words of the row's first pixel in the volumes (< 2^32 words)
-        int gstride = 0;
-        const uint32_t cs_s = ring_s + (RG::WORDS + my_stream) * 4, ss_s = cs_s + RG::STREAM_WORDS * 4;
-        auto stream_issue = [&](int xq) {  // request pixel xq of this row into stage xq % STAGE (one group, maybe empty)
-            if (xq < W1) {
-                const uint32_t o = gbase + (uint32_t)(xq * gstride);
-                cp_async_lane<NW>(cs_s + (xq & (RG::STAGE - 1)) * (RG::WPP * 4), fr.C + o);
-                if (BWD) cp_async_lane<NW>(ss_s + (xq & (RG::STAGE - 1)) * (RG::WPP * 4), fr.Sin + o);
-            }
-            cp_async_commit();
-        };
-        if (active_row) {
-            const int ys = ys0 + r;
-            const int y = BWD ? p.H - 1 - ys : ys;
-            const int x0 = BWD ? W1 - 1 : 0;
-            gbase = (uint32_t)(((size_t)y * W1 + x0) * RG::WPP + lane * NW);
-            gstride = BWD ? -RG::WPP : RG::WPP;
-            for (int xq = 0; xq < RG::STAGE - 1; ++xq) stream_issue(xq);
-        }
-        uint32_t* gout = bout + lw;  // this lane's data words of boundary pixel 0, direction 1
-        const int nsteps = W1 + 2 * (rows - 1) + 1;
         __syncthreads();
 
-        for (int t = 0; t < nsteps; ++t) {
-            if (fetch) {
-                helper_issue(t + 4);
-                cp_async_wait<2>();  // pixel t+2 (requested two steps ago) is visible after the barrier below
-            } else if (active_row) {
-                const int x = t - 2 * r;
-                if (x >= 0 && x < W1) {
-                    stream_issue(x + RG::STAGE - 1);
-                    cp_async_wait<RG::STAGE - 1>();  // this lane's words of pixel x have landed (own copies only)
-                    uint32_t Cw[NW], Sw[NW];
-                    ldw<NW>(cstream + my_stream + (x & (RG::STAGE - 1)) * RG::WPP, Cw);
-                    if (BWD) ldw<NW>(sstream + my_stream + (x & (RG::STAGE - 1)) * RG::WPP, Sw);
-                    uint32_t acc[NW], Lo1[NW], Lo2[NW], Lo3[NW];
-                    uint32_t mn1 = 0, mn2 = 0, mn3 = 0;
-                    if (DIRMASK & 1) {  // direction 0: predecessor (x-1, y), kept in registers
-                        uint32_t left = __shfl_up_sync(0xffffffffu, L0[NW - 1], 1);
-                        uint32_t right = __shfl_down_sync(0xffffffffu, L0[0], 1);
-                        if (lane == 0) left = SENT2;
-                        if (lane == 31) right = SENT2;
-                        uint32_t Lo[NW];
-                        uint32_t mn = step_dir<NW, PAD>(L0, left, right, minL0, Cw, P1x2, P2x2, padmask, Lo);
+        if (helper) {
+            if (VERT) {
+                if (first_band) {
+                    if (lane == 0) sts_release(done_s, W1 + 1);  // everything above the image is zero, for good
+                } else {
+                    // boundary row of the previous band -> ring row 0, four pixels ahead of publication
+                    int seen = 0, seen_cons = 0;
+                    for (int xp = 0; xp <= W1 + 2; ++xp) {
+                        if (xp <= W1) {
+                            // slot xp % 8 last held pixel xp - 8, read by warp 0 (direction 1) at its pixel xp - 7
+                            if (xp >= 7) wait_smem(cons_s, xp - 6, seen_cons);
+                            if (xp < W1) {
+                                const int need = xp + 1;
+                                if (seen < need && !failed) {
+                                    int spins = 0;
+                                    while ((seen = ld_acquire(prev_progress)) < need) {
+                                        // bounded: a timeout here or anywhere else in the grid ends all waiting (results are
+                                        // then invalid and the host reports an error): a logic fault cannot hang the GPU
+                                        if (++spins > WAVE_SPIN_LIMIT) { atomicExch(p.error, 1); failed = true; break; }
+                                        if ((spins & 1023) == 0 && *(volatile int*)p.error) { failed = true; break; }
+                                        __nanosleep(32);
+                                    }
+                                }
+                                const uint32_t* src = bin + (size_t)xp * 3 * RG::BSLOT;
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) { L0[j] = Lo[j]; acc[j] = Lo[j]; }
-                        minL0 = wdup16(mn);
-                    } else {
+                                for (int dir = 1; dir <= 3; ++dir) {
+                                    if (!(DIRMASK & (1 << dir))) continue;
+                                    const uint32_t dst = ring_s + (((dir - 1) * RG::HD + (xp & (RG::HD - 1))) * RG::SLOT) * 4;
+                                    const uint32_t* sp = src + (dir - 1) * RG::BSLOT;
+                                    if (lane < RG::WPP / 4) cp_async16(dst + (lane + 1) * 16, sp + (lane + 1) * 4);
+                                    if (lane == 0) cp_async16(dst, sp);  // header: {min, -, -, SENT}
+                                }
+                            } else {  // xp == W1: the zero slot behind the last pixel
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = 0;
-                    }
-                    if (DIRMASK & 2) {  // direction 1: predecessor (x-1, y-1)
-                        const uint32_t* sl = ring + rb1 + ((x - 1) & rm1) * RG::SLOT;
-                        uint32_t a[NW];
-                        ldw<NW>(sl, a);
-                        mn1 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo1);
-#pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo1[j], SENT2);
-                    }
-                    if (DIRMASK & 4) {  // direction 2: predecessor (x, y-1)
-                        const uint32_t* sl = ring + rb2 + (x & rm2) * RG::SLOT;
-                        uint32_t a[NW];
-                        ldw<NW>(sl, a);
-                        mn2 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo2);
-#pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo2[j], SENT2);
-                    }
-                    if (DIRMASK & 8) {  // direction 3: predecessor (x+1, y-1)
-                        const uint32_t* sl = ring + rb3 + ((x + 1) & rm3) * RG::SLOT;
-                        uint32_t a[NW];
-                        ldw<NW>(sl, a);
-                        mn3 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo3);
-#pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo3[j], SENT2);
-                    }
-                    // S = min(S_in + sum L, 32767)
-                    if (BWD) {
-#pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(Sw[j], acc[j], SENT2);
-                    }
-                    stw<NW>(fr.Sout + (gbase + (uint32_t)(x * gstride)), acc);
-                    if (to_ring) {  // for the row below
-                        if (DIRMASK & 2) {
-                            uint32_t* d = ring + wb1 + (x & 3) * RG::SLOT;
-                            stw<NW>(d, Lo1);
-                            if (lane == 0) d[-4] = wdup16(mn1);
+                                for (int dir = 1; dir <= 3; ++dir) {
+                                    uint32_t* dst = ring + ((dir - 1) * RG::HD + (xp & (RG::HD - 1))) * RG::SLOT;
+                                    for (int k = lane; k < RG::WPP; k += 32) dst[4 + k] = 0;
+                                    if (lane == 0) dst[0] = 0;
+                                }
+                            }
                         }
-                        if (DIRMASK & 4) {
-                            uint32_t* d = ring + wb2 + (x & 3) * RG::SLOT;
-                            stw<NW>(d, Lo2);
-                            if (lane == 0) d[-4] = wdup16(mn2);
-                        }
-                        if (DIRMASK & 8) {
-                            uint32_t* d = ring + wb3 + (x & 1) * RG::SLOT;
-                            stw<NW>(d, Lo3);
-                            if (lane == 0) d[-4] = wdup16(mn3);
-                        }
-                    } else if (to_global) {  // for the next band
-                        if (DIRMASK & 2) {
-                            stw<NW>(gout, Lo1);
-                            if (lane == 0) *(uint4*)(gout - lw) = make_uint4(wdup16(mn1), 0u, 0u, SENT2);
-                        }
-                        if (DIRMASK & 4) {
-                            stw<NW>(gout + RG::BSLOT, Lo2);
-                            if (lane == 0) *(uint4*)(gout - lw + RG::BSLOT) = make_uint4(wdup16(mn2), 0u, 0u, SENT2);
-                        }
-                        if (DIRMASK & 8) {
-                            stw<NW>(gout + 2 * RG::BSLOT, Lo3);
-                            if (lane == 0) *(uint4*)(gout - lw + 2 * RG::BSLOT) = make_uint4(wdup16(mn3), 0u, 0u, SENT2);
-                        }
-                        gout += 3 * RG::BSLOT;
-                        if (((x + 1) % WAVE_PUBLISH) == 0 || x + 1 == W1) {
-                            // the warp barrier orders every lane's boundary stores before lane 0's release store
-                            // (release is cumulative over what the warp barrier made visible to lane 0)
-                            __syncwarp();
-                            if (lane == 0) st_release(my_progress, x + 1);
+                        cp_async_commit();
+                        cp_async_wait<2>();  // the group of pixel xp - 2 has landed
+                        if (xp >= 2) {
+                            __syncwarp();  // all lanes' copies are in; lane 0 publishes them
+                            if (lane == 0) sts_release(done_s, xp - 1);
                         }
                     }
-                } else if (x == W1 && to_ring && (DIRMASK & 8)) {
-                    // zero slot "x = W1" for direction 3 of the row below (its predecessor is outside the image)
-                    uint32_t* d = ring + wb3 + (x & 1) * RG::SLOT;
+                }
+            }
+        } else if (r < rows) {
+            const bool to_ring = r + 1 < rows, to_global = VERT && r + 1 == rows && !last_band;
+            const uint32_t my_done_s = done_s + 4 * r, my_cons_s = cons_s + 4 * r;          // ring row r (read)
+            const uint32_t nx_done_s = done_s + 4 * (r + 1), nx_cons_s = cons_s + 4 * (r + 1);  // ring row r+1 (written)
+            uint32_t L0[NW];
+#pragma unroll
+            for (int j = 0; j < NW; ++j) L0[j] = 0;
+            uint32_t minL0 = 0;
+            const int ys = ys0 + r;
+            const int y = BWD ? p.H - 1 - ys : ys;
+            const uint32_t gbase = (uint32_t)(((size_t)y * W1 + (BWD ? W1 - 1 : 0)) * RG::WPP + lane * NW);  // < 2^32 words
+            const int gstride = BWD ? -RG::WPP : RG::WPP;
+            const uint32_t cs_s = ring_s + (RG::WORDS + my_stream) * 4, ss_s = cs_s + RG::STREAM_WORDS * 4;
+            auto stream_issue = [&](int xq) {  // request pixel xq of this row into stage xq % STAGE (one group, maybe empty)
+                if (xq < W1) {
+                    const uint32_t o = gbase + (uint32_t)(xq * gstride);
+                    cp_async_lane<NW>(cs_s + (xq & (RG::STAGE - 1)) * (RG::WPP * 4), fr.C + o);
+                    if (BWD) cp_async_lane<NW>(ss_s + (xq & (RG::STAGE - 1)) * (RG::WPP * 4), fr.Sin + o);
+                }
+                cp_async_commit();
+            };
+            for (int xq = 0; xq < RG::STAGE - 1; ++xq) stream_issue(xq);
+            uint32_t* gout = bout + lw;  // this lane's data words of boundary pixel 0, direction 1
+            // running slot indices: reads (x-1) % rd12, x % rd12, (x+1) % rd3; writes x % D12, x % D3
+            int i1 = rd12 - 1, i2 = 0, i3 = 1 % rd3, j12 = 0, j3 = 0;
+            int seen_done = 0, seen_cons = 0;
+
+            for (int x = 0; x < W1; ++x) {
+                stream_issue(x + RG::STAGE - 1);
+                if (VERT) {
+                    wait_smem(my_done_s, min(x + 2, W1 + 1), seen_done);          // the row above is written through pixel x + 1
+                    if (to_ring && x >= 4) wait_smem(nx_cons_s, x - 4, seen_cons);  // the slots about to be overwritten were read
+                }
+                cp_async_wait<RG::STAGE - 1>();  // this lane's words of pixel x have landed (own copies only)
+                uint32_t Cw[NW], Sw[NW];
+                ldw<NW>(cstream + my_stream + (x & (RG::STAGE - 1)) * RG::WPP, Cw);
+                if (BWD) ldw<NW>(sstream + my_stream + (x & (RG::STAGE - 1)) * RG::WPP, Sw);
+                uint32_t acc[NW], Lo1[NW], Lo2[NW], Lo3[NW];
+                uint32_t mn1 = 0, mn2 = 0, mn3 = 0;
+                if (DIRMASK & 1) {  // direction 0: predecessor (x-1, y), kept in registers
+                    uint32_t left = __shfl_up_sync(0xffffffffu, L0[NW - 1], 1);
+                    uint32_t right = __shfl_down_sync(0xffffffffu, L0[0], 1);
+                    if (lane == 0) left = SENT2;
+                    if (lane == 31) right = SENT2;
+                    uint32_t Lo[NW];
+                    uint32_t mn = step_dir<NW, PAD>(L0, left, right, minL0, Cw, P1x2, P2x2, padmask, Lo);
+#pragma unroll
+                    for (int j = 0; j < NW; ++j) { L0[j] = Lo[j]; acc[j] = Lo[j]; }
+                    minL0 = wdup16(mn);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < NW; ++j) acc[j] = 0;
+                }
+                if (DIRMASK & 2) {  // direction 1: predecessor (x-1, y-1)
+                    const uint32_t* sl = ring + rb1 + i1 * RG::SLOT;
+                    uint32_t a[NW];
+                    ldw<NW>(sl, a);
+                    mn1 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo1);
+#pragma unroll
+                    for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo1[j], SENT2);
+                }
+                if (DIRMASK & 4) {  // direction 2: predecessor (x, y-1)
+                    const uint32_t* sl = ring + rb2 + i2 * RG::SLOT;
+                    uint32_t a[NW];
+                    ldw<NW>(sl, a);
+                    mn2 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo2);
+#pragma unroll
+                    for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo2[j], SENT2);
+                }
+                if (DIRMASK & 8) {  // direction 3: predecessor (x+1, y-1)
+                    const uint32_t* sl = ring + rb3 + i3 * RG::SLOT;
+                    uint32_t a[NW];
+                    ldw<NW>(sl, a);
+                    mn3 = step_dir<NW, PAD>(a, sl[-1], sl[NW], sl[-lw], Cw, P1x2, P2x2, padmask, Lo3);
+#pragma unroll
+                    for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], Lo3[j], SENT2);
+                }
+                // S = min(S_in + sum L, 32767)
+                if (BWD) {
+#pragma unroll
+                    for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(Sw[j], acc[j], SENT2);
+                }
+                stw<NW>(fr.Sout + (gbase + (uint32_t)(x * gstride)), acc);
+                if (to_ring) {  // for the row below
+                    if (DIRMASK & 2) {
+                        uint32_t* d = ring + wb1 + j12 * RG::SLOT;
+                        stw<NW>(d, Lo1);
+                        if (lane == 0) d[-4] = wdup16(mn1);
+                    }
+                    if (DIRMASK & 4) {
+                        uint32_t* d = ring + wb2 + j12 * RG::SLOT;
+                        stw<NW>(d, Lo2);
+                        if (lane == 0) d[-4] = wdup16(mn2);
+                    }
+                    if (DIRMASK & 8) {
+                        uint32_t* d = ring + wb3 + j3 * RG::SLOT;
+                        stw<NW>(d, Lo3);
+                        if (lane == 0) d[-4] = wdup16(mn3);
+                    }
+                } else if (to_global) {  // for the next band
+                    if (DIRMASK & 2) {
+                        stw<NW>(gout, Lo1);
+                        if (lane == 0) *(uint4*)(gout - lw) = make_uint4(wdup16(mn1), 0u, 0u, SENT2);
+                    }
+                    if (DIRMASK & 4) {
+                        stw<NW>(gout + RG::BSLOT, Lo2);
+                        if (lane == 0) *(uint4*)(gout - lw + RG::BSLOT) = make_uint4(wdup16(mn2), 0u, 0u, SENT2);
+                    }
+                    if (DIRMASK & 8) {
+                        stw<NW>(gout + 2 * RG::BSLOT, Lo3);
+                        if (lane == 0) *(uint4*)(gout - lw + 2 * RG::BSLOT) = make_uint4(wdup16(mn3), 0u, 0u, SENT2);
+                    }
+                    gout += 3 * RG::BSLOT;
+                    if (((x + 1) % WAVE_PUBLISH) == 0 || x + 1 == W1) {
+                        // the warp barrier orders every lane's boundary stores before lane 0's release store
+                        // (release is cumulative over what the warp barrier made visible to lane 0)
+                        __syncwarp();
+                        if (lane == 0) st_release(my_progress, x + 1);
+                    }
+                }
+                if (VERT) {
+                    // publish: ring row r+1 holds pixel x; ring row r has been read for pixel x.  The warp barrier
+                    // puts every lane's ring reads and writes before lane 0's release store.
+                    __syncwarp();
+                    if (lane == 0) {
+                        fence_cta();
+                        sts_relaxed(nx_done_s, x + 1);
+                        sts_relaxed(my_cons_s, x + 1);
+                    }
+                }
+                i1 = i1 + 1 == rd12 ? 0 : i1 + 1;
+                i2 = i2 + 1 == rd12 ? 0 : i2 + 1;
+                i3 = i3 + 1 == rd3 ? 0 : i3 + 1;
+                j12 = j12 + 1 == RG::D12 ? 0 : j12 + 1;
+                j3 = (j3 + 1) & (RG::D3 - 1);
+            }
+            if (to_ring && VERT) {
+                // zero slot "x = W1" for direction 3 of the row below (its predecessor is outside the image);
+                // "W1 + 1 pixels written" is what the row below waits for at its last pixel
+                if (DIRMASK & 8) {
+                    if (W1 >= 4) wait_smem(nx_cons_s, W1 - 4, seen_cons);
+                    uint32_t* d = ring + wb3 + j3 * RG::SLOT;
                     for (int k = lane; k < RG::WPP; k += 32) d[k - lw + 4] = 0;
                     if (lane == 0) d[-4] = 0;
                 }
+                __syncwarp();
+                if (lane == 0) sts_release(nx_done_s, W1 + 1);
             }
-            __syncthreads();
         }
         cp_async_wait<0>();
     }

@@ -285,6 +285,15 @@ def run_ours(args, rank, world, local_rank):
                 "single_frame": {"ms": stage_ms_single["aggregate"],
                                  "frac": agg_bytes / (stage_ms_single["aggregate"] / 1000.0) / 1e9 / peak}}
 
+    # DRAM traffic of the same two launches from the committed ncu --set full capture (per camera-frame, like
+    # algorithmic_bytes_per_frame); only quoted when the capture is of this workload
+    tpath = os.path.join(ROOT, "profiles", "r01_wave_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if tj.get("workload") == args.workload and args.mode == 1:
+            roofline["traffic"] = tj["traffic_bytes_per_frame"]
+            roofline["traffic_source"] = "profiles/r01_wave_traffic.json (ncu dram__bytes_read+write, batch %d)" % tj["batch"]
+
     # ---- e2e: host buffers in, host results out, through the C ABI ----------------------------------------------
     descs_host = []
     for hc in host:

@@ -223,6 +223,9 @@ wave_kernel(WaveParams p)
             while ((seen = lds_relaxed(saddr)) < need) {
                 if (++spins > WAVE_SPIN_LIMIT) { atomicExch(p.error, 1); failed = true; break; }
                 if ((spins & 4095) == 0 && *(volatile int*)p.error) { failed = true; break; }
+#ifdef WAVE_SPIN_SLEEP
+                __nanosleep(WAVE_SPIN_SLEEP);  // leave the issue slots to the warps that have work
+#endif
             }
             fence_cta();  // acquire: the ring accesses below stay behind the counter read
         };

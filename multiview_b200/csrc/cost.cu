@@ -10,6 +10,7 @@ extern "C" int mvs_sgbm_check(const mvs_sgbm_params* p, int w, int h)
     if (!p || w <= 0 || h <= 0) return MVS_ERR_ARG;
     if (p->num_disp <= 0 || p->num_disp % 16 || p->num_disp > 256) return MVS_ERR_UNSUPPORTED;
     if (p->min_disp < 0) return MVS_ERR_UNSUPPORTED;
+    if (p->uniqueness > 99) return MVS_ERR_UNSUPPORTED;  // the WTA threshold divides by (100 - uniquenessRatio)
     if (p->block < 1 || !(p->block & 1) || p->block > 13) return MVS_ERR_UNSUPPORTED;
     if (p->mode != MVS_MODE_SGBM && p->mode != MVS_MODE_HH && p->mode != MVS_MODE_HH4) return MVS_ERR_UNSUPPORTED;
     int ftzero = (p->prefilter_cap > 15 ? p->prefilter_cap : 15) | 1;
@@ -169,23 +170,39 @@ pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ 
     }
 }
 
-// ---- vertical box sum: C[y] = sum_{dy} hsum[clamp(y+dy)] ; packed u16x2, sliding along y -------------------
-#define VSUM_ROWS 24
+// ---- vertical box sum: C[y] = sum_{dy} hsum[clamp(y+dy)] ; packed u16x2, sliding along y ------------------------
+// A thread owns one packed word (x, disparity pair) of a strip of rows and keeps the WIN row sums of its window
+// in a register ring, so every row sum is read once per strip (+ WIN-1 at the strip start).
+#define VSUM_ROWS 96
+template <int WIN>
 __global__ void __launch_bounds__(256)
 vsum_kernel(const uint32_t* __restrict__ hsum, SgbmGeom g, uint32_t* __restrict__ C)
 {
+    constexpr int SH = WIN / 2;
     const size_t rowwords = (size_t)g.W1 * (g.Dp >> 1);
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= rowwords) return;
-    int y0 = blockIdx.y * VSUM_ROWS, y1 = min(y0 + VSUM_ROWS, g.H);
-    int zero_from = (g.mode == MVS_MODE_HH4) ? g.H - g.SH2 : g.H;  // OpenCV 4.13 leaves these C rows zero in HH4
+    const int y0 = blockIdx.y * VSUM_ROWS, y1 = min(y0 + VSUM_ROWS, g.H);
+    const int zero_from = (g.mode == MVS_MODE_HH4) ? g.H - g.SH2 : g.H;  // OpenCV 4.13 leaves these C rows zero in HH4
+    uint32_t ring[WIN];
     uint32_t acc = 0;
-    for (int dy = -g.SH2; dy <= g.SH2; ++dy) acc += __ldg(hsum + (size_t)min(max(y0 + dy, 0), g.H - 1) * rowwords + i);
-    for (int y = y0; y < y1; ++y) {
-        C[(size_t)y * rowwords + i] = (y >= zero_from) ? 0u : acc;
-        uint32_t sub = __ldg(hsum + (size_t)min(max(y - g.SH2, 0), g.H - 1) * rowwords + i);
-        uint32_t add = __ldg(hsum + (size_t)min(max(y + 1 + g.SH2, 0), g.H - 1) * rowwords + i);
-        acc = acc - sub + add;  // component-wise: no borrow (acc >= sub) and no carry (sums <= 29237)
+#pragma unroll
+    for (int k = 0; k < WIN; ++k) {  // ring[k] holds row clamp(y0 - SH + k)
+        ring[k] = __ldg(hsum + (size_t)min(max(y0 - SH + k, 0), g.H - 1) * rowwords + i);
+        acc += ring[k];
+    }
+    for (int yb = y0; yb < y1; yb += WIN) {
+        uint32_t add[WIN];
+#pragma unroll
+        for (int k = 0; k < WIN; ++k)  // the WIN rows entering the window during this block of steps: all loads in flight at once
+            add[k] = __ldg(hsum + (size_t)min(yb + k + 1 + SH, g.H - 1) * rowwords + i);
+#pragma unroll
+        for (int k = 0; k < WIN; ++k) {
+            const int y = yb + k;
+            if (y < y1) C[(size_t)y * rowwords + i] = (y >= zero_from) ? 0u : acc;
+            acc = acc - ring[k] + add[k];  // per half: no borrow (acc >= ring[k]) and no carry (sums <= 29237)
+            ring[k] = add[k];              // slot k held row clamp(y - SH), the one leaving the window
+        }
     }
 }
 
@@ -220,7 +237,15 @@ int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, cons
     }
     size_t rowwords = (size_t)g.W1 * (g.Dp >> 1);
     dim3 vg(cdiv(rowwords, 256), cdiv(g.H, VSUM_ROWS));
-    vsum_kernel<<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C);
+    switch (2 * g.SH2 + 1) {
+    case 1: vsum_kernel<1><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
+    case 3: vsum_kernel<3><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
+    case 5: vsum_kernel<5><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
+    case 7: vsum_kernel<7><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
+    case 9: vsum_kernel<9><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
+    case 11: vsum_kernel<11><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
+    default: vsum_kernel<13><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
+    }
     MVS_LAUNCH_CHECK(ctx, "vsum_kernel");
     return MVS_OK;
 }

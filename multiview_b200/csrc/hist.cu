@@ -25,11 +25,20 @@ __device__ __forceinline__ Q qmul(Q a, Q b)  // quaternion.hpp:205-213
     return c;
 }
 
-__global__ void __launch_bounds__(256)
+// Per point: transform to world, bin, weight.  SMEM = true: the block accumulates into a private copy of the
+// histogram in shared memory (float atomics on-chip) and adds its non-zero bins to the global one at the end.
+template <bool SMEM>
+__global__ void __launch_bounds__(512)
 floor_hist_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __restrict__ xy, const int32_t* n_dev,
                   int n_host, const int32_t* __restrict__ labels, const double* __restrict__ still,
                   float* __restrict__ hist)
 {
+    extern __shared__ float sh_hist[];
+    const int nbins = a.hw * a.hh;
+    if (SMEM) {
+        for (int k = threadIdx.x; k < nbins; k += blockDim.x) sh_hist[k] = 0.0f;
+        __syncthreads();
+    }
     const int n = n_dev ? *n_dev : n_host;
     // rotation.inverse() = conjugate().normalised()
     Q q = {a.et[3], a.et[4], a.et[5], a.et[6]};
@@ -58,7 +67,14 @@ floor_hist_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __re
             int label = ((unsigned)px < (unsigned)a.lw && (unsigned)py < (unsigned)a.lh) ? labels[(size_t)py * a.lw + px] : -1;
             if (label >= 0 && label < a.n_labels) wgt *= 1.0 + 10.0 * still[label];
         }
-        atomicAdd(hist + (size_t)by * a.hw + bx, (float)wgt);
+        atomicAdd((SMEM ? sh_hist : hist) + (size_t)by * a.hw + bx, (float)wgt);
+    }
+    if (SMEM) {
+        __syncthreads();
+        for (int k = threadIdx.x; k < nbins; k += blockDim.x) {
+            float v = sh_hist[k];
+            if (v != 0.0f) atomicAdd(hist + k, v);
+        }
     }
 }
 
@@ -93,8 +109,17 @@ int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double e
     a.weighting = p->weighting; a.use_still = p->use_still && labels && still;
     a.lw = lw; a.lh = lh; a.n_labels = n_labels; a.hw = hw; a.hh = hh;
     MVS_CUDA(ctx, cudaMemsetAsync(cam_hist, 0, sizeof(float) * (size_t)hw * hh, ctx->stream));
-    int blocks = ctx->sm_count * 8;
-    floor_hist_kernel<<<blocks, 256, 0, ctx->stream>>>(a, Xs, xy, n_dev, n_host, labels, still, cam_hist);
+    const size_t smem = sizeof(float) * (size_t)hw * hh;
+    if (smem <= 100 * 1024) {  // two blocks per SM keep a private histogram each
+        static bool configured = false;
+        if (!configured) {
+            MVS_CUDA(ctx, cudaFuncSetAttribute(floor_hist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+            configured = true;
+        }
+        floor_hist_kernel<true><<<ctx->sm_count * 2, 512, smem, ctx->stream>>>(a, Xs, xy, n_dev, n_host, labels, still, cam_hist);
+    } else {
+        floor_hist_kernel<false><<<ctx->sm_count * 4, 512, 0, ctx->stream>>>(a, Xs, xy, n_dev, n_host, labels, still, cam_hist);
+    }
     MVS_LAUNCH_CHECK(ctx, "floor_hist_kernel");
     return MVS_OK;
 }

@@ -11,44 +11,56 @@ template <int NW>
 __global__ void __launch_bounds__(256)
 wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key)
 {
-    __shared__ uint16_t sh[8][NW * 64];
+    __shared__ __align__(16) uint32_t sh[8][NW * 32];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     long long pix = (long long)blockIdx.x * 8 + wib;
     if (pix >= (long long)g.W1 * g.H) return;
     int y = (int)(pix / g.W1), x = (int)(pix - (long long)y * g.W1);
     const uint32_t* Sp = S + (size_t)pix * (NW * 32) + lane * NW;
     uint32_t w[NW];
+    if (NW == 4) { uint4 v = __ldg((const uint4*)Sp); w[0] = v.x; w[1 % NW] = v.y; w[2 % NW] = v.z; w[3 % NW] = v.w; }
+    else if (NW == 2) { uint2 v = __ldg((const uint2*)Sp); w[0] = v.x; w[1 % NW] = v.y; }
+    else {
 #pragma unroll
-    for (int j = 0; j < NW; ++j) w[j] = Sp[j];
-    // first argmin: min over (S << 16 | d)
+        for (int j = 0; j < NW; ++j) w[j] = __ldg(Sp + j);
+    }
+    // first argmin: min over (S << 16 | d); padding (d >= D) holds 32767 and never beats a real minimum below it
     uint32_t key = 0xffffffffu;
+    uint32_t* mysh = sh[wib];
 #pragma unroll
     for (int j = 0; j < NW; ++j) {
-        uint32_t d0 = (uint32_t)(lane * NW + j) * 2;
-        key = min(key, ((w[j] & 0xffffu) << 16) | d0);
-        key = min(key, (w[j] & 0xffff0000u) | (d0 + 1));
-        ((uint32_t*)sh[wib])[lane * NW + j] = w[j];
+        const uint32_t d0 = (uint32_t)(lane * NW + j) * 2;
+        key = min(key, min(w[j] * 65536u + d0, (w[j] & 0xffff0000u) | (d0 + 1)));
+        // staged copy for the uniqueness test: padding is taken out of it (0xFFFF never counts)
+        mysh[lane * NW + j] = w[j] | (d0 >= (uint32_t)g.D ? 0xffffu : 0u) | (d0 + 1 >= (uint32_t)g.D ? 0xffff0000u : 0u);
     }
     key = __reduce_min_sync(0xffffffffu, key);
-    __syncwarp();
-    int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
+    const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
     if (minS >= 32767) return;  // every cost saturated: the reference leaves / writes INV here
-    // uniqueness: reject if some d outside best+-1 has S*(100-ur) < minS*100
-    bool bad = false;
-#pragma unroll
-    for (int j = 0; j < NW; ++j) {
-        int d0 = (lane * NW + j) * 2;
-        int s0 = (int)(w[j] & 0xffffu), s1 = (int)(w[j] >> 16);
-        bad |= (d0 < g.D) && (s0 * (100 - g.ur) < minS * 100) && (abs(best - d0) > 1);
-        bad |= (d0 + 1 < g.D) && (s1 * (100 - g.ur) < minS * 100) && (abs(best - d0 - 1) > 1);
+    __syncwarp();
+    // uniqueness: reject if some d outside best-1..best+1 has S*(100-ur) < minS*100, i.e. S <= thr.
+    // Lane 0 reads the two neighbours it needs for the sub-pixel fit, blanks best-1..best+1 in the staged copy,
+    // and the warp takes one packed minimum over what is left.
+    const uint16_t* h16 = (const uint16_t*)mysh;
+    int sm = 0, sp = 0;
+    if (lane == 0) {
+        uint16_t* hw = (uint16_t*)mysh;
+        if (best > 0) { sm = h16[best - 1]; hw[best - 1] = 0xffffu; }
+        if (best < g.D - 1) { sp = h16[best + 1]; hw[best + 1] = 0xffffu; }
+        hw[best] = 0xffffu;
     }
-    if (__any_sync(0xffffffffu, bad)) return;
+    __syncwarp();
+    uint32_t m = 0xffffffffu;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) m = __vminu2(m, mysh[lane * NW + j]);
+    const uint32_t mn = __reduce_min_sync(0xffffffffu, min(m & 0xffffu, m >> 16));
+    const uint32_t thr = minS > 0 ? (uint32_t)(minS * 100 - 1) / (uint32_t)(100 - g.ur) : 0xffffffffu;  // ur <= 99 (mvs_sgbm_check)
+    if (minS > 0 && mn != 0xffffu && mn <= thr) return;
     if (lane == 0) {
         int x2 = x + g.minX1 - best - g.minD;
         atomicMin(disp2key + (size_t)y * g.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
         int d = best;
         if (0 < d && d < g.D - 1) {
-            int sm = sh[wib][d - 1], sp = sh[wib][d + 1];
             int den = max(sm + sp - 2 * minS, 1);
             d = d * 16 + ((sm - sp) * 16 + den) / (den * 2);
         } else

@@ -108,7 +108,7 @@ pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ 
     const int span = NS + g.Dp + 2;
     const int rows = blockDim.x / half;
     uint16_t* myR = sm + (size_t)ry * (12 * span);          // [plane 0..5][copy E/O][span]
-    uint32_t* myL = (uint32_t*)(sm + (size_t)rows * 12 * span) + (size_t)ry * (8 * NS);  // [step][8] pre-biased left values
+    uint32_t* myL = (uint32_t*)(sm + (((size_t)rows * 12 * span + 7) & ~(size_t)7)) + (size_t)ry * (8 * NS);  // [step][8] pre-biased left values, 16-byte aligned
     if (y < g.H) {
         const uint8_t* R = PR + (size_t)y * g.W;
         for (int idx = t; idx < 6 * span; idx += half) {
@@ -148,7 +148,8 @@ pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ 
             const int k0 = xmax - (x - g.minD) + 2 * t;
             const uint16_t* base = myR + ((k0 & 1) ? span : 0);
             const uint32_t* pr = (const uint32_t*)(base) + (k0 >> 1);
-            const uint32_t* lv = myL + k * 8;
+            const uint4 lva = *(const uint4*)(myL + k * 8), lvb = *(const uint4*)(myL + k * 8 + 4);  // two broadcast 16-byte reads
+            const uint32_t lv[8] = {lva.x, lva.y, lva.z, lva.w, lvb.x, lvb.y, lvb.z, lvb.w};
             uint32_t pix = 0;
 #pragma unroll
             for (int ch = 0; ch < 2; ++ch) {
@@ -220,7 +221,7 @@ int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, cons
         const int half = g.Dp >> 1, rows = 128 / half > 0 ? 128 / half : 1, win = 2 * g.SW2 + 1;
         const int ns = 10 * win, tx = ns - (win - 1), span = ns + g.Dp + 2;
         dim3 cg(cdiv(g.W1, tx), cdiv(g.H, rows));
-        size_t smem = (size_t)rows * (12 * span * sizeof(uint16_t) + 8 * ns * sizeof(uint32_t));
+        size_t smem = (size_t)rows * (12 * span * sizeof(uint16_t) + 8 * ns * sizeof(uint32_t)) + 16;
         uint32_t* hs32 = (uint32_t*)hsum;
         const uint8_t* PR = planes + 6 * plane;
         switch (win) {

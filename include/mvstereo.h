@@ -210,14 +210,17 @@ int mvs_frame_run(mvs_ctx* ctx, int slot, const mvs_frame_desc* desc, mvs_frame_
  * (pipeline/pipeline-task.cpp:181-200).  descs / out are arrays of n_frames elements (out may be NULL). */
 int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame_desc* descs, int n_frames, mvs_frame_result* out);
 
-/* Copy results of a slot to host buffers (any may be NULL).  Synchronises the stream. */
+/* Copy results of a slot to host buffers (any may be NULL) and wait for them.  The copies run on the context's
+ * copy stream behind the slot's last kernel, so a batch enqueued on OTHER slots keeps the GPU busy meanwhile:
+ * alternate two slot ranges (run batch k+1, then fetch batch k) to hide the PCIe transfers behind the kernels.
+ * Host-pointer inputs of mvs_frame_run(_batch) are uploaded on the same copy stream. */
 int mvs_frame_fetch(mvs_ctx* ctx, int slot, float* disp, size_t dstep, double* Xs, int32_t* xy, int32_t* lookup,
                     int32_t* n_out, double centroid[3], float* cam_hist);
 
-/* Sum the per-camera histograms of slots [0, n_slots) in slot order into a device buffer owned by the
+/* Sum the per-camera histograms of slots [first_slot, first_slot + n_slots) in slot order into a device buffer owned by the
  * context (floor-histogram.cpp:296-300); returns its device address (hw*hh floats).  This buffer is what
  * a multi-GPU caller hands to ncclAllReduce / ncclAllGather. */
-int mvs_frame_hist_sum(mvs_ctx* ctx, int n_slots, float** hist_dev, int* hw, int* hh);
+int mvs_frame_hist_sum(mvs_ctx* ctx, int first_slot, int n_slots, float** hist_dev, int* hw, int* hh);
 
 /* -- test taps (kernel-level parity; not used by the reference-facing path) ---------------------------
  * Run cost volume + aggregation for grey images and copy the 16-bit volumes back ([h][w1][num_disp]).

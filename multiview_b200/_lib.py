@@ -70,7 +70,7 @@ SIGNATURES = {
     "mvs_frame_run_batch": (c_int, [c_void_p, c_int, C.POINTER(FrameDesc), c_int, C.POINTER(FrameResult)]),
     "mvs_frame_fetch": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, C.POINTER(C.c_int32),
                                 c_void_p, c_void_p]),
-    "mvs_frame_hist_sum": (c_int, [c_void_p, c_int, C.POINTER(c_void_p), C.POINTER(c_int), C.POINTER(c_int)]),
+    "mvs_frame_hist_sum": (c_int, [c_void_p, c_int, c_int, C.POINTER(c_void_p), C.POINTER(c_int), C.POINTER(c_int)]),
     "mvs_sgbm_volumes": (c_int, [c_void_p, C.POINTER(SgbmParams), c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p,
                                  c_void_p, c_void_p]),
     "mvs_stage_ms": (c_float, [c_void_p, C.c_char_p]),

@@ -520,15 +520,16 @@ int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, i
 }
 
 // Host check of the bounded-wait flag (synchronises the stream); called by the entry points that sync anyway.
-int sgbm_aggregate_wave_status(mvs_ctx* ctx)
+int sgbm_aggregate_wave_status(mvs_ctx* ctx, cudaStream_t stream)
 {
     auto it = ctx->arena.bufs.find("sgbm.wave.err");
     if (it == ctx->arena.bufs.end() || !it->second.p) return MVS_OK;
+    if (!stream) stream = ctx->stream;
     int h = 0;
-    MVS_CUDA(ctx, cudaMemcpyAsync(&h, it->second.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    MVS_CUDA(ctx, cudaMemcpyAsync(&h, it->second.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(stream));
     if (h) {
-        cudaMemsetAsync(it->second.p, 0, sizeof(int), ctx->stream);
+        cudaMemsetAsync(it->second.p, 0, sizeof(int), stream);
         return mvs_fail(ctx, MVS_ERR_CUDA, "aggregation: a bounded inter-band wait expired (results invalid)");
     }
     return MVS_OK;

@@ -35,6 +35,14 @@ struct FrameSlot {
 struct mvs_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    // Host<->device copies of the frame path run on their own stream so that the upload of the next batch and the
+    // download of the previous one overlap the kernels of the current one (ordered by the events below).
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_h2d = nullptr;                       // uploads of the batch being enqueued are complete
+    cudaEvent_t ev_slot_done[MVS_MAX_SLOTS] = {};       // last kernel that touched the slot's buffers
+    bool slot_done_recorded[MVS_MAX_SLOTS] = {};
+    cudaEvent_t ev_slot_fetched[MVS_MAX_SLOTS] = {};    // last download of the slot's results
+    bool slot_fetch_recorded[MVS_MAX_SLOTS] = {};
     Arena arena;
     char err[512];
     std::map<std::string, StageTimer> timers;
@@ -107,7 +115,7 @@ int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, cons
 int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);       // fused wavefront sweeps
 int sgbm_aggregate_paths_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S); // one kernel per direction (debug/A-B)
 int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);
-int sgbm_aggregate_wave_status(mvs_ctx* ctx);
+int sgbm_aggregate_wave_status(mvs_ctx* ctx, cudaStream_t stream = nullptr);  // nullptr: the compute stream
 int sgbm_aggregate_wave_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S);
 int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S);
 int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,

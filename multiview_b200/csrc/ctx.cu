@@ -85,8 +85,14 @@ extern "C" int mvs_ctx_create(int device, mvs_ctx** out)
     if (!ctx) return MVS_ERR_NOMEM;
     ctx->device = device;
     ctx->err[0] = 0;
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
-        delete ctx;
+    bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_h2d, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < MVS_MAX_SLOTS; ++i)
+        ok = cudaEventCreateWithFlags(&ctx->ev_slot_done[i], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->ev_slot_fetched[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+        mvs_ctx_destroy(ctx);
         return MVS_ERR_CUDA;
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
@@ -98,14 +104,21 @@ extern "C" void mvs_ctx_destroy(mvs_ctx* ctx)
 {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
     for (auto& kv : ctx->arena.bufs)
         if (kv.second.p) cudaFree(kv.second.p);
     for (auto& kv : ctx->timers) {
         if (kv.second.beg) cudaEventDestroy(kv.second.beg);
         if (kv.second.end) cudaEventDestroy(kv.second.end);
     }
-    cudaStreamDestroy(ctx->stream);
+    if (ctx->ev_h2d) cudaEventDestroy(ctx->ev_h2d);
+    for (int i = 0; i < MVS_MAX_SLOTS; ++i)
+        if (ctx->ev_slot_done[i]) cudaEventDestroy(ctx->ev_slot_done[i]);
+    for (int i = 0; i < MVS_MAX_SLOTS; ++i)
+        if (ctx->ev_slot_fetched[i]) cudaEventDestroy(ctx->ev_slot_fetched[i]);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
@@ -115,6 +128,7 @@ extern "C" int mvs_sync(mvs_ctx* ctx)
 {
     if (!ctx) return MVS_ERR_ARG;
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
     return MVS_OK;
 }
 

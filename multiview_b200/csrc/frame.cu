@@ -56,16 +56,23 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     SlotBufs sb[MVS_MAX_BATCH];
     const uint8_t* sensor[MVS_MAX_BATCH][2];
     const float *mapx[MVS_MAX_BATCH][2], *mapy[MVS_MAX_BATCH][2];
+    cudaStream_t cs = ctx->copy_stream;  // uploads go here; the compute stream waits for them once, below
+    bool any_upload = false;
     for (int f = 0; f < n_frames; ++f) {
         const mvs_frame_desc* d = descs + f;
         const int slot = first_slot + f;
+        if ((!d->inputs_on_device || !d->maps_on_device)) {
+            any_upload = true;
+            // the slot's input buffers may still be read by the kernels of the previous frame that used this slot
+            if (ctx->slot_done_recorded[slot]) MVS_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_slot_done[slot], 0));
+        }
         for (int i = 0; i < 2; ++i) {
             if (d->inputs_on_device) {
                 sensor[f][i] = d->sensor[i];
             } else {
                 uint8_t* ds = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "sensor1" : "sensor0").c_str(), (size_t)d->sh * d->sw * 3);
                 if (!ds) return MVS_ERR_NOMEM;
-                MVS_CUDA(ctx, cudaMemcpy2DAsync(ds, (size_t)d->sw * 3, d->sensor[i], d->sstep, (size_t)d->sw * 3, d->sh, cudaMemcpyHostToDevice, s));
+                MVS_CUDA(ctx, cudaMemcpy2DAsync(ds, (size_t)d->sw * 3, d->sensor[i], d->sstep, (size_t)d->sw * 3, d->sh, cudaMemcpyHostToDevice, cs));
                 sensor[f][i] = ds;
             }
             if (d->maps_on_device) {
@@ -74,8 +81,8 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
                 float* dx = (float*)arena_get(ctx, slot_name(slot, i ? "mapx1" : "mapx0").c_str(), n * 4);
                 float* dy = (float*)arena_get(ctx, slot_name(slot, i ? "mapy1" : "mapy0").c_str(), n * 4);
                 if (!dx || !dy) return MVS_ERR_NOMEM;
-                MVS_CUDA(ctx, cudaMemcpy2DAsync(dx, (size_t)w * 4, d->mapx[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
-                MVS_CUDA(ctx, cudaMemcpy2DAsync(dy, (size_t)w * 4, d->mapy[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+                MVS_CUDA(ctx, cudaMemcpy2DAsync(dx, (size_t)w * 4, d->mapx[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, cs));
+                MVS_CUDA(ctx, cudaMemcpy2DAsync(dy, (size_t)w * 4, d->mapy[i], d->mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, cs));
                 mapx[f][i] = dx; mapy[f][i] = dy;
             }
             sb[f].rect[i] = (uint8_t*)arena_get(ctx, slot_name(slot, i ? "rect1" : "rect0").c_str(), n * 3);
@@ -92,6 +99,14 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         if (!sb[f].disp16 || !sb[f].dispf || !sb[f].Xs || !sb[f].xy || !sb[f].lookup || !sb[f].nd || !sb[f].cen) return MVS_ERR_NOMEM;
         sb[f].cam_hist = hists + (size_t)slot * hw * hh;
     }
+
+    if (any_upload) {
+        MVS_CUDA(ctx, cudaEventRecord(ctx->ev_h2d, cs));
+        MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_h2d, 0));
+    }
+    // results of these slots may still be on their way to the host (mvs_frame_fetch copies on the copy stream)
+    for (int f = 0; f < n_frames; ++f)
+        if (ctx->slot_fetch_recorded[first_slot + f]) MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_slot_fetched[first_slot + f], 0));
 
     const uint8_t white[3] = {255, 255, 255};  // calc_rectified.cpp:113
     stage_begin(ctx, "rectify");
@@ -129,6 +144,8 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     if (rc) return rc;
 
     for (int f = 0; f < n_frames; ++f) {
+        MVS_CUDA(ctx, cudaEventRecord(ctx->ev_slot_done[first_slot + f], s));
+        ctx->slot_done_recorded[first_slot + f] = true;
         FrameSlot& fs = ctx->slots[first_slot + f];
         fs.w = w; fs.h = h; fs.hw = hw; fs.hh = hh; fs.valid = true;
         if (out) {
@@ -154,7 +171,9 @@ extern "C" int mvs_frame_fetch(mvs_ctx* ctx, int slot, float* disp, size_t dstep
     if (slot < 0 || slot >= MVS_MAX_SLOTS || !ctx->slots[slot].valid) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_fetch: empty slot");
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
     const FrameSlot& fs = ctx->slots[slot];
-    cudaStream_t s = ctx->stream;
+    // download on the copy stream, behind the slot's last kernel: the compute stream is free to run the next batch
+    cudaStream_t s = ctx->copy_stream;
+    if (ctx->slot_done_recorded[slot]) MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_slot_done[slot], 0));
     size_t n = (size_t)fs.w * fs.h;
     int32_t nh = 0;
     MVS_CUDA(ctx, cudaMemcpyAsync(&nh, arena_get(ctx, slot_name(slot, "n").c_str(), 4), 4, cudaMemcpyDeviceToHost, s));
@@ -171,23 +190,29 @@ extern "C" int mvs_frame_fetch(mvs_ctx* ctx, int slot, float* disp, size_t dstep
     MVS_CUDA(ctx, cudaStreamSynchronize(s));
     if (nh > 0 && Xs) MVS_CUDA(ctx, cudaMemcpyAsync(Xs, arena_get(ctx, slot_name(slot, "Xs").c_str(), n * 24), (size_t)nh * 24, cudaMemcpyDeviceToHost, s));
     if (nh > 0 && xy) MVS_CUDA(ctx, cudaMemcpyAsync(xy, arena_get(ctx, slot_name(slot, "xy").c_str(), n * 8), (size_t)nh * 8, cudaMemcpyDeviceToHost, s));
+    MVS_CUDA(ctx, cudaEventRecord(ctx->ev_slot_fetched[slot], s));
+    ctx->slot_fetch_recorded[slot] = true;
     MVS_CUDA(ctx, cudaStreamSynchronize(s));
     if (n_out) *n_out = nh;
-    return sgbm_aggregate_wave_status(ctx);
+    return sgbm_aggregate_wave_status(ctx, s);  // read behind the slot's kernels, without waiting for later batches
 }
 
-extern "C" int mvs_frame_hist_sum(mvs_ctx* ctx, int n_slots, float** hist_dev, int* hw, int* hh)
+extern "C" int mvs_frame_hist_sum(mvs_ctx* ctx, int first_slot, int n_slots, float** hist_dev, int* hw, int* hh)
 {
     if (!ctx) return MVS_ERR_ARG;
-    if (n_slots <= 0 || n_slots > MVS_MAX_SLOTS || !hist_dev) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_hist_sum: bad argument");
-    for (int i = 0; i < n_slots; ++i)
-        if (!ctx->slots[i].valid || ctx->slots[i].hw != ctx->slots[0].hw || ctx->slots[i].hh != ctx->slots[0].hh)
+    if (first_slot < 0 || n_slots <= 0 || first_slot + n_slots > MVS_MAX_SLOTS || !hist_dev)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_hist_sum: bad argument");
+    const FrameSlot& f0 = ctx->slots[first_slot];
+    for (int i = first_slot; i < first_slot + n_slots; ++i)
+        if (!ctx->slots[i].valid || ctx->slots[i].hw != f0.hw || ctx->slots[i].hh != f0.hh)
             return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_hist_sum: slot %d empty or of different size", i);
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
-    int w = ctx->slots[0].hw, h = ctx->slots[0].hh;
+    int w = f0.hw, h = f0.hh;
     float* hists = (float*)arena_get(ctx, "slots.cam_hists", 0);
-    MVS_ARENA(ctx, float, sum, "slots.hist_sum", (size_t)w * h);
-    int rc = hist_sum_dev(ctx, hists, n_slots, w, h, sum);
+    char nm[48];
+    snprintf(nm, sizeof(nm), "slots.hist_sum.%d", first_slot);
+    MVS_ARENA(ctx, float, sum, nm, (size_t)w * h);
+    int rc = hist_sum_dev(ctx, hists + (size_t)first_slot * w * h, n_slots, w, h, sum);
     if (rc) return rc;
     *hist_dev = sum;
     if (hw) *hw = w;

@@ -97,6 +97,15 @@ int mvs_sgbm_compute16(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l,
 int mvs_disparity_sgbm(mvs_ctx* ctx, const mvs_sgbm_params* p, double presmooth_sigma, const uint8_t* l,
                        const uint8_t* r, int channels, int w, int h, size_t step, float* out, size_t ostep);
 
+/* -- a8: merge with the scene's reference disparity ------------------------------------------------------
+ * Replaces the loop of disp_map_update::Task::execute, pipeline/nodes/disp_map_update.cpp:98-113: in place,
+ * disp[x] = ref[x] where ref[x] is finite, labels[x] >= 0 and (the super-pixel is not flagged still_cuttoff, or
+ * disp[x] is not finite, or disp[x] <= 0).  disp, ref: CV_32FC1 w x h; labels: int32 w x h (the SLIC lookup);
+ * still_cutoff: one byte per super-pixel (ImageFeatures2d::slic_info[].still_cuttoff); labels >= n_labels are
+ * skipped.  The caller then rebuilds the cloud with mvs_point_cloud (disp_map_update.cpp:115-119).  Bit-exact. */
+int mvs_disp_merge_ref(mvs_ctx* ctx, float* disp, size_t dstep, const float* ref, size_t rstep, const int32_t* labels,
+                       size_t lstep, const uint8_t* still_cutoff, int n_labels, int w, int h);
+
 /* -- a6/a7: point cloud -----------------------------------------------------------------------------
  * The 24 doubles of BinocularCamera that the device needs: KRR_inv_[2] (row-major 3x3) and C_[2],
  * geometry/projective/binocular-camera.hpp (members filled by binocular-camera.cpp:682-785). */

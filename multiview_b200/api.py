@@ -219,6 +219,22 @@ def presmooth(image, sigma=2.15, ctx: Context | None = None):
     return out
 
 
+def disp_map_update(disparity, ref_disparity, slic_lookup, still_cuttoff, ctx: Context | None = None):
+    """The merge of disp_map_update::Task::execute (pipeline/nodes/disp_map_update.cpp:98-113): returns the
+    disparity with holes / non-still super-pixels filled from the scene's reference disparity."""
+    ctx = ctx or default_context()
+    d = np.array(disparity, np.float32, order="C")
+    r = np.ascontiguousarray(ref_disparity, np.float32)
+    lab = np.ascontiguousarray(slic_lookup, np.int32)
+    cut = np.ascontiguousarray(still_cuttoff, np.uint8)
+    if d.shape != r.shape or d.shape != lab.shape or d.ndim != 2:
+        raise MvsError("disp_map_update: disparity, reference disparity and SLIC lookup must have the same size")
+    h, w = d.shape
+    ctx.check(ctx.lib.mvs_disp_merge_ref(ctx.h, _vp(d), w * 4, _vp(r), w * 4, _vp(lab), w * 4, _vp(cut) if cut.size else None,
+                                         int(cut.size), w, h), "mvs_disp_merge_ref")
+    return d
+
+
 # ---------------------------------------------------------------------------------------------- a6-a7
 class BinocularCamera:
     """The part of BinocularCamera the path needs: init() -> KRR_inv_[2], C_[2] (host side, numpy),

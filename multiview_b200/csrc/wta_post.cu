@@ -282,3 +282,53 @@ int disp_to_float_dev(mvs_ctx* ctx, const int16_t* d16, int w, int h, float* out
     MVS_LAUNCH_CHECK(ctx, "disp_to_float_kernel");
     return MVS_OK;
 }
+
+// ---- a8: disp_map_update merge with the scene's reference disparity (pipeline/nodes/disp_map_update.cpp:98-113) ------
+// dst[x] = ref[x] where ref is finite, the pixel has a super-pixel label, and (the super-pixel is not flagged
+// still_cuttoff, or dst is not finite, or dst <= 0).  Labels beyond the table are skipped (the reference would
+// index past its vector there).
+__global__ void disp_merge_ref_kernel(float* __restrict__ dst, const float* __restrict__ ref, const int32_t* __restrict__ labels,
+                                      const uint8_t* __restrict__ still_cutoff, int n_labels, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float s = ref[i];
+    const int label = labels[i];
+    if (!isfinite(s) || label < 0 || label >= n_labels) return;
+    const float d = dst[i];
+    if (!still_cutoff[label] || !isfinite(d) || d <= 0.0f) dst[i] = s;
+}
+
+int disp_merge_ref_dev(mvs_ctx* ctx, float* disp, const float* ref, const int32_t* labels, const uint8_t* still_cutoff,
+                       int n_labels, int w, int h)
+{
+    size_t n = (size_t)w * h;
+    disp_merge_ref_kernel<<<cdiv(n, 256), 256, 0, ctx->stream>>>(disp, ref, labels, still_cutoff, n_labels, n);
+    MVS_LAUNCH_CHECK(ctx, "disp_merge_ref_kernel");
+    return MVS_OK;
+}
+
+extern "C" int mvs_disp_merge_ref(mvs_ctx* ctx, float* disp, size_t dstep, const float* ref, size_t rstep, const int32_t* labels,
+                                  size_t lstep, const uint8_t* still_cutoff, int n_labels, int w, int h)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!disp || !ref || !labels || (n_labels > 0 && !still_cutoff) || n_labels < 0 || w <= 0 || h <= 0 || dstep < (size_t)w * 4 ||
+        rstep < (size_t)w * 4 || lstep < (size_t)w * 4)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_disp_merge_ref: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    size_t n = (size_t)w * h;
+    MVS_ARENA(ctx, float, dd, "merge.api.disp", n);
+    MVS_ARENA(ctx, float, dr, "merge.api.ref", n);
+    MVS_ARENA(ctx, int32_t, dl, "merge.api.labels", n);
+    MVS_ARENA(ctx, uint8_t, dc, "merge.api.cutoff", (size_t)n_labels + 1);
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(dd, (size_t)w * 4, disp, dstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(dr, (size_t)w * 4, ref, rstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(dl, (size_t)w * 4, labels, lstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+    if (n_labels > 0) MVS_CUDA(ctx, cudaMemcpyAsync(dc, still_cutoff, (size_t)n_labels, cudaMemcpyHostToDevice, s));
+    int rc = disp_merge_ref_dev(ctx, dd, dr, dl, dc, n_labels, w, h);
+    if (rc) return rc;
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(disp, dstep, dd, (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyDeviceToHost, s));
+    MVS_CUDA(ctx, cudaStreamSynchronize(s));
+    return MVS_OK;
+}

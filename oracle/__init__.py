@@ -222,3 +222,13 @@ def hist_sum(cam_hists):
     out = np.empty((hh, hw), np.float32)
     lib().orc_hist_sum(_p(ch), n, hw, hh, _p(out))
     return out
+
+
+def disp_merge_ref(disp, ref, labels, still_cutoff):
+    d = np.array(disp, np.float32, order="C")
+    r = np.ascontiguousarray(ref, np.float32)
+    lab = np.ascontiguousarray(labels, np.int32)
+    cut = np.ascontiguousarray(still_cutoff, np.uint8)
+    h, w = d.shape
+    lib().orc_disp_merge_ref(_p(d), _p(r), _p(lab), _p(cut) if cut.size else None, int(cut.size), w, h)
+    return d

@@ -223,3 +223,15 @@ void orc_hist_sum(const float* cam_hists, int n_cams, int hw, int hh, float* his
     for (int c = 0; c < n_cams; ++c)
         for (size_t i = 0; i < (size_t)hw * hh; ++i) hist[i] += cam_hists[(size_t)c * hw * hh + i];
 }
+
+/* pipeline/nodes/disp_map_update.cpp:98-113: fill from the reference disparity, in place. */
+void orc_disp_merge_ref(float* disp, const float* ref, const int32_t* labels, const uint8_t* still_cutoff, int n_labels, int w,
+                        int h)
+{
+    for (size_t i = 0; i < (size_t)w * h; ++i) {
+        int label = labels[i];
+        if (!isfinite(ref[i])) continue;
+        if (label < 0 || label >= n_labels) continue; /* >= n_labels: the reference would read past its vector */
+        if (!still_cutoff[label] || !isfinite(disp[i]) || disp[i] <= 0.0f) disp[i] = ref[i];
+    }
+}

@@ -224,3 +224,21 @@ def test_frame_batch_equals_single_frames(ctx):
     rect = [oracle.remap_cubic_bgr8(cams[0]["sensor"][i], cams[0]["mapx"][i], cams[0]["mapy"][i]) for i in range(2)]
     want = oracle.disp_to_float(oracle.sgbm_compute(_op(sp), oracle.presmooth(rect[0]), oracle.presmooth(rect[1])))
     assert np.array_equal(single[0]["disp"], want)
+
+
+def test_disp_map_update_merge(ctx):
+    """a8: the reference-disparity merge of disp_map_update (holes and non-still super-pixels are filled)."""
+    rng = np.random.default_rng(12)
+    h, w = 90, 140
+    disp = rng.uniform(-2, 60, (h, w)).astype(np.float32)
+    disp[rng.random((h, w)) < 0.2] = 0.0
+    disp[rng.random((h, w)) < 0.05] = np.nan
+    ref = rng.uniform(1, 60, (h, w)).astype(np.float32)
+    ref[rng.random((h, w)) < 0.1] = np.nan
+    ref[rng.random((h, w)) < 0.02] = np.inf
+    labels = rng.integers(-1, 40, (h, w)).astype(np.int32)  # some labels are beyond the 32-entry table
+    cut = (rng.random(32) < 0.5).astype(np.uint8)
+    got = api.disp_map_update(disp, ref, labels, cut, ctx=ctx)
+    want = oracle.disp_merge_ref(disp, ref, labels, cut)
+    assert np.array_equal(got, want, equal_nan=True)
+    assert (got != disp).sum() > 1000 and np.array_equal(got[labels < 0], disp[labels < 0], equal_nan=True)

@@ -33,8 +33,17 @@
 #ifndef WAVE_PUBLISH
 #define WAVE_PUBLISH 8       // inter-band progress is published every this many pixels
 #endif
+#ifndef WAVE_D12
+#define WAVE_D12 6           // ring depth for L1 / L2 (lock-step needs 4 / 3)
+#endif
+#ifndef WAVE_D3
+#define WAVE_D3 4            // ring depth for L3 (lock-step needs 2)
+#endif
 #define WAVE_SPIN_LIMIT (1 << 20)
 #define WAVE_CTL_PAD 16
+// a producer at pixel x may overwrite its slots once the consumer has finished pixel x - WAVE_WAR - 1:
+// L1 slot x % D12 held pixel x - D12 (read at x - D12 + 1), L3 slot x % D3 held pixel x - D3 (read at x - D3 - 1)
+#define WAVE_WAR ((WAVE_D12 - 2) < WAVE_D3 ? (WAVE_D12 - 2) : WAVE_D3)
 
 struct WaveFrame {
     const uint32_t* C;
@@ -137,7 +146,7 @@ struct Ring {
     static constexpr int SLOT = WPP + 8;       // header(4) + data + tail(4)
     static constexpr int BSLOT = WPP + 4;      // boundary-buffer slot in global memory: header + data
     // rows written by compute warps: lock-step needs 4 / 3 / 2 slots for L1 / L2 / L3; two more give two pixels of slack
-    static constexpr int D12 = 6, D3 = 4;
+    static constexpr int D12 = WAVE_D12, D3 = WAVE_D3;
     static constexpr int ROW_SLOTS = 2 * D12 + D3;
     static constexpr int HD = 8;               // row above the band (helper): 8 slots per direction
     static constexpr int HELP_SLOTS = 3 * HD;
@@ -217,17 +226,15 @@ wave_kernel(WaveParams p)
 
         // bounded wait on a shared-memory counter: every lane polls the same word (a broadcast read)
         // `seen` caches the last value read, so a warp that runs with slack does not touch the counter at all
-        auto wait_smem = [&](uint32_t saddr, int need, int& seen) {
-            if (seen >= need || failed) return;
+        // Returns true when it had to read the counter: the caller then issues ONE acquire fence for all its waits.
+        auto wait_smem = [&](uint32_t saddr, int need, int& seen) -> bool {
+            if (seen >= need || failed) return false;
             int spins = 0;
             while ((seen = lds_relaxed(saddr)) < need) {
                 if (++spins > WAVE_SPIN_LIMIT) { atomicExch(p.error, 1); failed = true; break; }
                 if ((spins & 4095) == 0 && *(volatile int*)p.error) { failed = true; break; }
-#ifdef WAVE_SPIN_SLEEP
-                __nanosleep(WAVE_SPIN_SLEEP);  // leave the issue slots to the warps that have work
-#endif
             }
-            fence_cta();  // acquire: the ring accesses below stay behind the counter read
+            return true;
         };
 
         // zero slots prepared before anybody runs: the row above the image, and "x = -1" of the row each warp reads
@@ -254,7 +261,7 @@ wave_kernel(WaveParams p)
                     for (int xp = 0; xp <= W1 + 2; ++xp) {
                         if (xp <= W1) {
                             // slot xp % 8 last held pixel xp - 8, read by warp 0 (direction 1) at its pixel xp - 7
-                            if (xp >= 7) wait_smem(cons_s, xp - 6, seen_cons);
+                            if (xp >= 7 && wait_smem(cons_s, xp - 6, seen_cons)) fence_cta();  // acquire before overwriting the slot
                             if (xp < W1) {
                                 const int need = xp + 1;
                                 if (seen < need && !failed) {
@@ -324,8 +331,9 @@ wave_kernel(WaveParams p)
             for (int x = 0; x < W1; ++x) {
                 stream_issue(x + RG::STAGE - 1);
                 if (VERT) {
-                    wait_smem(my_done_s, min(x + 2, W1 + 1), seen_done);          // the row above is written through pixel x + 1
-                    if (to_ring && x >= 4) wait_smem(nx_cons_s, x - 4, seen_cons);  // the slots about to be overwritten were read
+                    bool polled = wait_smem(my_done_s, min(x + 2, W1 + 1), seen_done);      // the row above is written through pixel x + 1
+                    if (to_ring && x >= WAVE_WAR) polled |= wait_smem(nx_cons_s, x - WAVE_WAR, seen_cons);  // the slots about to be overwritten were read
+                    if (polled) fence_cta();  // acquire: the ring accesses below stay behind the counter reads
                 }
                 cp_async_wait<RG::STAGE - 1>();  // this lane's words of pixel x have landed (own copies only)
                 uint32_t Cw[NW], Sw[NW];
@@ -428,13 +436,13 @@ wave_kernel(WaveParams p)
                 i2 = i2 + 1 == rd12 ? 0 : i2 + 1;
                 i3 = i3 + 1 == rd3 ? 0 : i3 + 1;
                 j12 = j12 + 1 == RG::D12 ? 0 : j12 + 1;
-                j3 = (j3 + 1) & (RG::D3 - 1);
+                j3 = j3 + 1 == RG::D3 ? 0 : j3 + 1;
             }
             if (to_ring && VERT) {
                 // zero slot "x = W1" for direction 3 of the row below (its predecessor is outside the image);
                 // "W1 + 1 pixels written" is what the row below waits for at its last pixel
                 if (DIRMASK & 8) {
-                    if (W1 >= 4) wait_smem(nx_cons_s, W1 - 4, seen_cons);
+                    if (W1 >= RG::D3 && wait_smem(nx_cons_s, W1 - RG::D3, seen_cons)) fence_cta();  // that L3 slot held pixel W1 - D3
                     uint32_t* d = ring + wb3 + j3 * RG::SLOT;
                     for (int k = lane; k < RG::WPP; k += 32) d[k - lw + 4] = 0;
                     if (lane == 0) d[-4] = 0;

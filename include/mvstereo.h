@@ -170,6 +170,15 @@ int mvs_floor_hist_camera(mvs_ctx* ctx, const mvs_hist_params* p, const double e
  * cam_hists: n_cams consecutive hw x hh float images, summed in camera order. */
 int mvs_hist_sum(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int hh, float* hist);
 
+/* Replaces the tail of FloorHistogram::calculate, cost-functions/floor-histogram.cpp:411-434: in place,
+ * cv::GaussianBlur(CV_32F, ksize = ceil(sigma)*4 | 1, sigma, BORDER_DEFAULT) when gaussian_sigma is finite and > 0,
+ * then clip (values < min_hist_count -> 0, values > max_hist_count -> max_hist_count).  Applied to the summed
+ * histogram (after the cross-GPU sum).  Float arithmetic: within 1e-6 relative of OpenCV (whose own result varies by
+ * an ulp with its SIMD dispatch).  mvs_hist_post takes a host image, mvs_hist_post_dev a device image (asynchronous). */
+int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float gaussian_sigma, float min_hist_count, float max_hist_count);
+int mvs_hist_post_dev(mvs_ctx* ctx, float* hist_dev, int hw, int hh, float gaussian_sigma, float min_hist_count,
+                      float max_hist_count);
+
 /* -- device-resident frame path ----------------------------------------------------------------------
  * One camera-frame through a1 -> a10 without leaving the GPU: what calc_rectified[2c],[2c+1] ->
  * disp_init[c] -> disp_map_update[c] (pass-through, disp_map_update.cpp:89-93) -> floor_hist compute

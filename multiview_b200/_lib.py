@@ -67,6 +67,8 @@ SIGNATURES = {
     "mvs_floor_hist_camera": (c_int, [c_void_p, C.POINTER(HistParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                       C.c_int32, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int]),
     "mvs_hist_sum": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "mvs_hist_post": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_float]),
+    "mvs_hist_post_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_float]),
     "mvs_frame_run": (c_int, [c_void_p, c_int, C.POINTER(FrameDesc), C.POINTER(FrameResult)]),
     "mvs_frame_run_batch": (c_int, [c_void_p, c_int, C.POINTER(FrameDesc), c_int, C.POINTER(FrameResult)]),
     "mvs_frame_fetch": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, C.POINTER(C.c_int32),

@@ -343,9 +343,8 @@ def hist_dims(aabb, hist_sz):
 
 
 class FloorHistogram:
-    """FloorHistogram::calculate lines 105-300 (per-camera histograms and their sum).  The Gaussian blur and
-    clip that follow (:411-434) are small host-side post-processing of the caller and are not part of the
-    accelerated path (SURVEY.md 8a, a10 'negligible')."""
+    """FloorHistogram::calculate (cost-functions/floor-histogram.cpp:105-300, 411-434): per-camera histograms, their
+    sum in camera order, Gaussian smoothing and clipping.  `hist_raw` keeps the sum before smoothing."""
 
     Params = FloorHistogramParams
 
@@ -353,6 +352,7 @@ class FloorHistogram:
         self.bounds = None
         self.hist_sz = 0.05
         self.hist = None
+        self.hist_raw = None
         self.camera_hists = []
 
     @staticmethod
@@ -387,6 +387,9 @@ class FloorHistogram:
         ctx.check(ctx.lib.mvs_hist_sum(ctx.h, _vp(hists), n_cams, hw, hh, _vp(total)), "mvs_hist_sum")
         floor_hist.bounds = tuple(aabb)
         floor_hist.hist_sz = float(np.float32(p.hist_sz))
+        floor_hist.hist_raw = total.copy()
+        ctx.check(ctx.lib.mvs_hist_post(ctx.h, _vp(total), hw, hh, float(p.gaussian_sigma), float(p.min_hist_count),
+                                        float(p.max_hist_count)), "mvs_hist_post")
         floor_hist.hist = total
         floor_hist.camera_hists = [hists[i] for i in range(n_cams)]
         return True

@@ -184,3 +184,98 @@ extern "C" int mvs_hist_sum(mvs_ctx* ctx, const float* cam_hists, int n_cams, in
     MVS_CUDA(ctx, cudaStreamSynchronize(s));
     return MVS_OK;
 }
+
+// ---- a10 tail: Gaussian smoothing and clipping of the summed histogram (cost-functions/floor-histogram.cpp:411-434) ----
+// cv::GaussianBlur(CV_32F, ksize = ceil(sigma)*4 | 1, sigma, BORDER_DEFAULT): separable, symmetric taps
+// s = c*k0 + sum_i (src[-i] + src[+i]) * k_i, evaluated in float without FMA (this file is built --fmad=false).
+// OpenCV's own float path differs from this by 1-2 ulp depending on its SIMD dispatch, so parity is <= 1e-6 relative.
+struct HistBlurTaps { float k[17]; int r; };
+
+__device__ __forceinline__ int hreflect101(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) {
+        if (i < 0) i = -i;
+        if (i >= n) i = 2 * (n - 1) - i;
+    }
+    return i;
+}
+__global__ void hist_blur_h_kernel(const float* __restrict__ src, int w, int h, HistBlurTaps t, float* __restrict__ dst)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= w) return;
+    const float* row = src + (size_t)y * w;
+    float s = row[x] * t.k[0];
+    for (int i = 1; i <= t.r; ++i) s = s + (row[hreflect101(x - i, w)] + row[hreflect101(x + i, w)]) * t.k[i];
+    dst[(size_t)y * w + x] = s;
+}
+__global__ void hist_blur_v_clip_kernel(const float* __restrict__ src, int w, int h, HistBlurTaps t, int do_blur, float minc,
+                                        float maxc, float* __restrict__ dst)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= w) return;
+    float s = src[(size_t)y * w + x];
+    if (do_blur) {
+        s = s * t.k[0];
+        for (int i = 1; i <= t.r; ++i)
+            s = s + (src[(size_t)hreflect101(y - i, h) * w + x] + src[(size_t)hreflect101(y + i, h) * w + x]) * t.k[i];
+    }
+    if (s < minc) s = 0.0f;   // floor-histogram.cpp:429-430
+    if (s > maxc) s = maxc;
+    dst[(size_t)y * w + x] = s;
+}
+
+int hist_post_dev(mvs_ctx* ctx, float* hist, int hw, int hh, float sigma, float minc, float maxc)
+{
+    HistBlurTaps t;
+    memset(&t, 0, sizeof(t));
+    const bool blur = isfinite(sigma) && sigma > 0.0f;
+    if (blur) {
+        int n = (int)(ceilf(sigma) * 4.0f);
+        if (n % 2 == 0) n += 1;
+        if (n > 33) return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "hist_post: gaussian_sigma %g needs a %d-tap kernel (max 33)", sigma, n);
+        t.r = n / 2;
+        // cv::getGaussianKernel(n, sigma, CV_32F): double weights, normalised, stored as float
+        double kd[33], sum = 0, s2 = -0.5 / ((double)sigma * sigma);
+        for (int i = 0; i < n; ++i) { double x = i - (n - 1) * 0.5; kd[i] = exp(s2 * x * x); sum += kd[i]; }
+        for (int i = 0; i <= t.r; ++i) t.k[i] = (float)(kd[t.r + i] / sum);
+    }
+    MVS_ARENA(ctx, float, tmp, "hist.post.tmp", (size_t)hw * hh);
+    dim3 grid(cdiv(hw, 128), hh);
+    const float* src = hist;
+    if (blur) {
+        hist_blur_h_kernel<<<grid, 128, 0, ctx->stream>>>(hist, hw, hh, t, tmp);
+        src = tmp;
+    } else {
+        MVS_CUDA(ctx, cudaMemcpyAsync(tmp, hist, sizeof(float) * (size_t)hw * hh, cudaMemcpyDeviceToDevice, ctx->stream));
+        src = tmp;
+    }
+    hist_blur_v_clip_kernel<<<grid, 128, 0, ctx->stream>>>(src, hw, hh, t, blur ? 1 : 0, minc, maxc, hist);
+    MVS_LAUNCH_CHECK_N(ctx, "hist post kernels", blur ? 2 : 1);
+    return MVS_OK;
+}
+
+extern "C" int mvs_hist_post_dev(mvs_ctx* ctx, float* hist_dev, int hw, int hh, float gaussian_sigma, float min_hist_count,
+                                 float max_hist_count)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!hist_dev || hw <= 0 || hh <= 0) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_hist_post_dev: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return hist_post_dev(ctx, hist_dev, hw, hh, gaussian_sigma, min_hist_count, max_hist_count);
+}
+
+extern "C" int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float gaussian_sigma, float min_hist_count,
+                             float max_hist_count)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!hist || hw <= 0 || hh <= 0) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_hist_post: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    size_t n = (size_t)hw * hh;
+    MVS_ARENA(ctx, float, d, "hist.post.api", n);
+    MVS_CUDA(ctx, cudaMemcpyAsync(d, hist, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = hist_post_dev(ctx, d, hw, hh, gaussian_sigma, min_hist_count, max_hist_count);
+    if (rc) return rc;
+    MVS_CUDA(ctx, cudaMemcpyAsync(hist, d, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MVS_OK;
+}

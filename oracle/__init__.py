@@ -232,3 +232,13 @@ def disp_merge_ref(disp, ref, labels, still_cutoff):
     h, w = d.shape
     lib().orc_disp_merge_ref(_p(d), _p(r), _p(lab), _p(cut) if cut.size else None, int(cut.size), w, h)
     return d
+
+
+def hist_post(hist, sigma=0.5, min_count=0.0, max_count=1000.0):
+    """Tail of FloorHistogram::calculate (floor-histogram.cpp:411-434): blur + clip."""
+    a = np.array(hist, np.float32, order="C")
+    hh, hw = a.shape
+    rc = lib().orc_hist_post(_p(a), hw, hh, ctypes.c_float(sigma), ctypes.c_float(min_count), ctypes.c_float(max_count))
+    if rc:
+        raise RuntimeError(f"orc_hist_post rc={rc}")
+    return a

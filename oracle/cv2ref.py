@@ -56,3 +56,18 @@ def disparity_calculate(p, bgr0, bgr1, sigma=2.15):
 
 def set_threads(n: int):
     _cv2().setNumThreads(int(n))
+
+
+def hist_post(hist, sigma=0.5, min_count=0.0, max_count=1000.0):
+    """floor-histogram.cpp:411-434 with the real cv::GaussianBlur."""
+    cv2 = _cv2()
+    import math
+
+    a = np.array(hist, np.float32)
+    if math.isfinite(sigma) and sigma > 0:
+        n = int(math.ceil(sigma) * 4.0)
+        n += 1 if n % 2 == 0 else 0
+        a = cv2.GaussianBlur(a, (n, n), sigma, sigmaY=sigma, borderType=cv2.BORDER_DEFAULT)
+    a[a < min_count] = 0.0
+    a[a > max_count] = max_count
+    return a

@@ -235,3 +235,53 @@ void orc_disp_merge_ref(float* disp, const float* ref, const int32_t* labels, co
         if (!still_cutoff[label] || !isfinite(disp[i]) || disp[i] <= 0.0f) disp[i] = ref[i];
     }
 }
+
+static int orc_reflect101(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) {
+        if (i < 0) i = -i;
+        if (i >= n) i = 2 * (n - 1) - i;
+    }
+    return i;
+}
+/* floor-histogram.cpp:411-434: GaussianBlur (CV_32F, ksize ceil(sigma)*4|1, BORDER_DEFAULT) + clip, in place.
+ * Separable symmetric form in float without FMA; OpenCV's float path agrees to 1-2 ulp (SIMD-dispatch dependent). */
+int orc_hist_post(float* hist, int w, int h, float sigma, float minc, float maxc)
+{
+    size_t n = (size_t)w * h;
+    float* tmp = (float*)malloc(sizeof(float) * n);
+    if (!tmp) return -2;
+    if (isfinite(sigma) && sigma > 0.0f) {
+        int ks = (int)(ceilf(sigma) * 4.0f);
+        if (ks % 2 == 0) ks += 1;
+        int r = ks / 2;
+        double kd[65], sum = 0, s2 = -0.5 / ((double)sigma * sigma);
+        float k[33];
+        if (ks > 33) { free(tmp); return -1; }
+        for (int i = 0; i < ks; ++i) { double x = i - (ks - 1) * 0.5; kd[i] = exp(s2 * x * x); sum += kd[i]; }
+        for (int i = 0; i <= r; ++i) k[i] = (float)(kd[r + i] / sum);
+        for (int y = 0; y < h; ++y)
+            for (int x = 0; x < w; ++x) {
+                float s = hist[(size_t)y * w + x] * k[0];
+                for (int i = 1; i <= r; ++i)
+                    s = s + (hist[(size_t)y * w + orc_reflect101(x - i, w)] + hist[(size_t)y * w + orc_reflect101(x + i, w)]) * k[i];
+                tmp[(size_t)y * w + x] = s;
+            }
+        for (int y = 0; y < h; ++y)
+            for (int x = 0; x < w; ++x) {
+                float s = tmp[(size_t)y * w + x] * k[0];
+                for (int i = 1; i <= r; ++i)
+                    s = s + (tmp[(size_t)orc_reflect101(y - i, h) * w + x] + tmp[(size_t)orc_reflect101(y + i, h) * w + x]) * k[i];
+                hist[(size_t)y * w + x] = s;
+            }
+    }
+    for (size_t i = 0; i < n; ++i) {
+        float v = hist[i];
+        if (v < minc) v = 0.0f;
+        if (v > maxc) v = maxc;
+        hist[i] = v;
+    }
+    free(tmp);
+    return 0;
+}

@@ -169,9 +169,12 @@ def test_floor_histogram_parity(ctx):
                 assert np.allclose(fh.camera_hists[c], want[c], rtol=1e-5, atol=1e-3)
         wsum = oracle.hist_sum(np.stack(want))
         if weighting == api.WGT_NONE and not use_still:
-            assert np.array_equal(fh.hist, wsum)
+            assert np.array_equal(fh.hist_raw, wsum)
+            # smoothing + clip (floor-histogram.cpp:411-434): same float operations in the same order -> identical
+            assert np.array_equal(fh.hist, oracle.hist_post(wsum, p.gaussian_sigma, p.min_hist_count, p.max_hist_count))
         else:
-            assert np.allclose(fh.hist, wsum, rtol=1e-5, atol=1e-3)
+            assert np.allclose(fh.hist_raw, wsum, rtol=1e-5, atol=1e-3)
+            assert np.allclose(fh.hist, oracle.hist_post(wsum, p.gaussian_sigma, p.min_hist_count, p.max_hist_count), rtol=1e-5, atol=1e-2)
 
 
 def test_frame_path_matches_stagewise_oracle(ctx):

@@ -46,3 +46,13 @@ def test_remap_and_presmooth():
 def test_float_conversion():
     d = np.array([[-16, 0, 15, 2400, 2401, 32767, -32768]], np.int16)
     assert np.array_equal(oracle.disp_to_float(d), cv2ref.disp_to_float(d))
+
+
+def test_hist_post_close_to_cv2():
+    """Float blur: the restatement is within an ulp or two of cv2 (not bit-exact: OpenCV's float path depends on SIMD dispatch)."""
+    rng = np.random.default_rng(3)
+    h = ((rng.random((100, 120)) < 0.2) * rng.integers(1, 1500, (100, 120))).astype(np.float32)
+    for sigma, mn, mx in [(0.5, 0.0, 1000.0), (1.3, 2.0, 500.0), (3.0, 0.0, 1e9)]:
+        a, b = oracle.hist_post(h, sigma, mn, mx), cv2ref.hist_post(h, sigma, mn, mx)
+        assert np.allclose(a, b, rtol=1e-6, atol=1e-4), np.abs(a - b).max()
+    assert np.array_equal(oracle.hist_post(h, 0.0, 5.0, 700.0), cv2ref.hist_post(h, 0.0, 5.0, 700.0))

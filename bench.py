@@ -218,6 +218,9 @@ def run_ours(args, rank, world, local_rank):
         if world > 1:
             with torch.cuda.stream(stream):
                 dist.all_reduce(t)  # counts: exact in fp32 in any order
+        # floor-histogram.cpp:411-434 on the summed histogram: smoothing + clip, on the same stream
+        ctx.check(ctx.lib.mvs_hist_post_dev(ctx.h, ptr, hw, hh, C.c_float(hp.gaussian_sigma), C.c_float(hp.min_hist_count),
+                                            C.c_float(hp.max_hist_count)), "mvs_hist_post_dev")
         return t
 
     batch_dev = (api.FrameDesc * B)(*[descs_dev[b % len(descs_dev)] for b in range(B)])
@@ -364,7 +367,7 @@ def run_ours(args, rank, world, local_rank):
             "e2e": {"value": e2e_val, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "note": "sensor images H2D from pinned memory + float disparity, floor histogram, N, centroid D2H every frame; "
                             "the point cloud stays on the device (its consumer floor_hist runs there)"},
-            "clocks": clk.summary(), "hist_hits": hist_total}
+            "clocks": clk.summary(), "hist_mass_after_smoothing": hist_total}
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import cv2ref

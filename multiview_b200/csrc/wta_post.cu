@@ -7,62 +7,85 @@
 // disp2 (the right-view disparity) is a per-row argmin with "first writer in descending x wins ties":
 // realised as atomicMin on key = minS << 16 | (0xFFFF - x), from which the winning d follows as
 // x + minX1 - x2 - minD... (x2 = x + minX1 - d - minD), so no second array is needed.
+#define WTA_PPW 4  // pixels per warp: their loads are issued together (memory-level parallelism), then processed in turn
+// ur_magic = ceil(2^32 / (100 - ur)) (0 when the divisor is 1): n / (100 - ur) == umulhi(n, ur_magic) for n < 2^25
 template <int NW>
 __global__ void __launch_bounds__(256)
-wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key)
+wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key)
 {
     __shared__ __align__(16) uint32_t sh[8][NW * 32];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    long long pix = (long long)blockIdx.x * 8 + wib;
-    if (pix >= (long long)g.W1 * g.H) return;
-    int y = (int)(pix / g.W1), x = (int)(pix - (long long)y * g.W1);
-    const uint32_t* Sp = S + (size_t)pix * (NW * 32) + lane * NW;
-    uint32_t w[NW];
-    if (NW == 4) { uint4 v = __ldg((const uint4*)Sp); w[0] = v.x; w[1 % NW] = v.y; w[2 % NW] = v.z; w[3 % NW] = v.w; }
-    else if (NW == 2) { uint2 v = __ldg((const uint2*)Sp); w[0] = v.x; w[1 % NW] = v.y; }
-    else {
+    const long long npix = (long long)g.W1 * g.H;
+    const long long pix0 = ((long long)blockIdx.x * 8 + wib) * WTA_PPW;
+    if (pix0 >= npix) return;
+    uint32_t wall[WTA_PPW][NW];
 #pragma unroll
-        for (int j = 0; j < NW; ++j) w[j] = __ldg(Sp + j);
+    for (int q = 0; q < WTA_PPW; ++q) {
+        const long long pix = min(pix0 + q, npix - 1);
+        const uint32_t* Sp = S + (size_t)pix * (NW * 32) + lane * NW;
+        if (NW == 4) { uint4 v = __ldcs((const uint4*)Sp); wall[q][0] = v.x; wall[q][1 % NW] = v.y; wall[q][2 % NW] = v.z; wall[q][3 % NW] = v.w; }
+        else if (NW == 2) { uint2 v = __ldcs((const uint2*)Sp); wall[q][0] = v.x; wall[q][1 % NW] = v.y; }
+        else {
+#pragma unroll
+            for (int j = 0; j < NW; ++j) wall[q][j] = __ldcs(Sp + j);
+        }
     }
-    // first argmin: min over (S << 16 | d); padding (d >= D) holds 32767 and never beats a real minimum below it
-    uint32_t key = 0xffffffffu;
-    uint32_t* mysh = sh[wib];
+    uint32_t padbits[NW];
 #pragma unroll
     for (int j = 0; j < NW; ++j) {
         const uint32_t d0 = (uint32_t)(lane * NW + j) * 2;
-        key = min(key, min(w[j] * 65536u + d0, (w[j] & 0xffff0000u) | (d0 + 1)));
-        // staged copy for the uniqueness test: padding is taken out of it (0xFFFF never counts)
-        mysh[lane * NW + j] = w[j] | (d0 >= (uint32_t)g.D ? 0xffffu : 0u) | (d0 + 1 >= (uint32_t)g.D ? 0xffff0000u : 0u);
+        padbits[j] = (d0 >= (uint32_t)g.D ? 0xffffu : 0u) | (d0 + 1 >= (uint32_t)g.D ? 0xffff0000u : 0u);
     }
-    key = __reduce_min_sync(0xffffffffu, key);
-    const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
-    if (minS >= 32767) return;  // every cost saturated: the reference leaves / writes INV here
-    __syncwarp();
-    // uniqueness: reject if some d outside best-1..best+1 has S*(100-ur) < minS*100, i.e. S <= thr.
-    // Lane 0 reads the two neighbours it needs for the sub-pixel fit, blanks best-1..best+1 in the staged copy,
-    // and the warp takes one packed minimum over what is left.
-    const uint16_t* h16 = (const uint16_t*)mysh;
-    int sm = 0, sp = 0;
-    if (lane == 0) {
-        uint16_t* hw = (uint16_t*)mysh;
-        if (best > 0) { sm = h16[best - 1]; hw[best - 1] = 0xffffu; }
-        if (best < g.D - 1) { sp = h16[best + 1]; hw[best + 1] = 0xffffu; }
-        hw[best] = 0xffffu;
-    }
-    __syncwarp();
-    uint32_t m = 0xffffffffu;
+    uint32_t* mysh = sh[wib];
+    uint16_t* hw = (uint16_t*)mysh;
+    // lane q keeps the outcome of pixel q; the divisions, the atomic and the store happen once per warp at the end
+    int my_best = -1, my_minS = 0, my_sm = 0, my_sp = 0;
 #pragma unroll
-    for (int j = 0; j < NW; ++j) m = __vminu2(m, mysh[lane * NW + j]);
-    const uint32_t mn = __reduce_min_sync(0xffffffffu, min(m & 0xffffu, m >> 16));
-    const uint32_t thr = minS > 0 ? (uint32_t)(minS * 100 - 1) / (uint32_t)(100 - g.ur) : 0xffffffffu;  // ur <= 99 (mvs_sgbm_check)
-    if (minS > 0 && mn != 0xffffu && mn <= thr) return;
-    if (lane == 0) {
-        int x2 = x + g.minX1 - best - g.minD;
-        atomicMin(disp2key + (size_t)y * g.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
-        int d = best;
+    for (int q = 0; q < WTA_PPW; ++q) {
+        if (pix0 + q >= npix) break;
+        const uint32_t (&w)[NW] = wall[q];
+        // first argmin: min over (S << 16 | d); padding (d >= D) holds 32767 and never beats a real minimum below it
+        uint32_t key = 0xffffffffu;
+        __syncwarp();  // the previous pixel's staged copy has been read by every lane
+#pragma unroll
+        for (int j = 0; j < NW; ++j) {
+            const uint32_t d0 = (uint32_t)(lane * NW + j) * 2;
+            key = min(key, min(w[j] * 65536u + d0, (w[j] & 0xffff0000u) | (d0 + 1)));
+            // staged copy for the uniqueness test: padding is taken out of it (0xFFFF never counts)
+            mysh[lane * NW + j] = w[j] | padbits[j];
+        }
+        key = __reduce_min_sync(0xffffffffu, key);
+        const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
+        if (minS >= 32767) continue;  // every cost saturated: the reference leaves / writes INV here
+        __syncwarp();
+        // uniqueness: reject if some d outside best-1..best+1 has S*(100-ur) < minS*100, i.e. S <= thr.
+        // Lane q reads the two neighbours it needs for the sub-pixel fit, blanks best-1..best+1 in the staged copy,
+        // and the warp takes one packed minimum over what is left.
+        int sm = 0, sp = 0;
+        if (lane == q) {
+            if (best > 0) { sm = hw[best - 1]; hw[best - 1] = 0xffffu; }
+            if (best < g.D - 1) { sp = hw[best + 1]; hw[best + 1] = 0xffffu; }
+            hw[best] = 0xffffu;
+        }
+        __syncwarp();
+        uint32_t m = 0xffffffffu;
+#pragma unroll
+        for (int j = 0; j < NW; ++j) m = __vminu2(m, mysh[lane * NW + j]);
+        const uint32_t mn = __reduce_min_sync(0xffffffffu, min(m & 0xffffu, m >> 16));
+        const uint32_t num = (uint32_t)(minS * 100 - 1);
+        const uint32_t thr = minS > 0 ? (ur_magic ? __umulhi(num, ur_magic) : num) : 0xffffffffu;  // ur <= 99 (mvs_sgbm_check)
+        if (minS > 0 && mn != 0xffffu && mn <= thr) continue;
+        if (lane == q) { my_best = best; my_minS = minS; my_sm = sm; my_sp = sp; }
+    }
+    if (lane < WTA_PPW && my_best >= 0) {
+        int y = (int)(pix0 / g.W1), x = (int)(pix0 - (long long)y * g.W1) + lane;
+        while (x >= g.W1) { x -= g.W1; ++y; }
+        const int x2 = x + g.minX1 - my_best - g.minD;
+        atomicMin(disp2key + (size_t)y * g.W + x2, ((uint32_t)my_minS << 16) | (uint32_t)(0xffff - x));
+        int d = my_best;
         if (0 < d && d < g.D - 1) {
-            int den = max(sm + sp - 2 * minS, 1);
-            d = d * 16 + ((sm - sp) * 16 + den) / (den * 2);
+            int den = max(my_sm + my_sp - 2 * my_minS, 1);
+            d = d * 16 + ((my_sm - my_sp) * 16 + den) / (den * 2);
         } else
             d *= 16;
         raw[(size_t)y * g.W + x + g.minX1] = (int16_t)(d + g.minD * 16);
@@ -241,12 +264,14 @@ int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw
     size_t n = (size_t)g.W * g.H;
     MVS_ARENA(ctx, uint32_t, d2, "sgbm.disp2key", n);
     wta_init_kernel<<<cdiv(n, 256), 256, 0, s>>>(raw16, d2, n, g.INV);
-    int blocks = cdiv((long long)g.W1 * g.H, 8);
+    int blocks = cdiv((long long)g.W1 * g.H, 8 * WTA_PPW);
+    const uint32_t udiv = (uint32_t)(100 - g.ur);
+    const uint32_t ur_magic = udiv <= 1 ? 0u : (uint32_t)(((1ull << 32) + udiv - 1) / udiv);
     switch (g.Dp / 64) {
-    case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
-    case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
-    case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
-    case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, raw16, d2); break;
+    case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2); break;
+    case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2); break;
+    case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2); break;
+    case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2); break;
     default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
     }
     MVS_LAUNCH_CHECK_N(ctx, "wta_kernel", 2);

@@ -83,91 +83,118 @@ __global__ void prefilter_kernel(const uint8_t* __restrict__ img, int W, int H, 
 }
 
 // ---- per-pixel BT cost + horizontal box sum ------------------------------------------------------------------
-// One block: NY rows x one tile of TX output columns (W1 coordinates) x all disparities.  A thread owns a pair of
+// One block: a few rows x one tile of output columns (W1 coordinates) x all disparities.  A thread owns a pair of
 // disparities (u16x2) and walks along x keeping the last WIN pixel costs in a register ring, so the row box sum is
-// a sliding window (one add, one subtract per step).  The right image's six prefilter planes are staged reversed
-// in shared memory so that consecutive disparities are consecutive halfwords; a second copy shifted by one
-// halfword keeps the packed loads aligned for odd offsets.  All arithmetic is packed 16-bit with a +1024 bias so
-// that the Birchfield-Tomasi differences never go negative (plain 32-bit adds/subs then act per halfword).
+// a sliding window (one add, one subtract per step).  Step k of a tile is the virtual column xs + k; columns left
+// of the image are folded into the ring's initial state, columns right of it repeat the last pixel cost
+// (replicate clamping).  The right image's prefilter planes are staged reversed in shared memory, three planes of a
+// channel per 16-byte element, so that the element of disparity pair t at step k sits at (NS/2 + t - ceil(k/2)) of
+// the copy of k's parity (the odd copy is shifted by one halfword): every address of the unrolled loop is a
+// running pointer plus an immediate.  All arithmetic is packed 16-bit with a +1024 bias so that the
+// Birchfield-Tomasi differences never go negative (plain 32-bit adds/subs then act per halfword).
 #define COST_K2 0x04000400u
-template <int WIN>
-__global__ void __launch_bounds__(128)
+template <int WIN, int NW>
+struct CostTile {
+    static constexpr int HALF = 32 * NW;                       // disparity pairs = threads per row
+    static constexpr int ROWS = NW == 3 ? 1 : 128 / HALF;      // rows per block
+    static constexpr int THREADS = ROWS * HALF;
+    static constexpr int BODY = 2 * WIN;                       // steps per unrolled body (even, a multiple of the ring length)
+    static constexpr int NS = BODY * ((128 + BODY - 1) / BODY);  // steps per tile
+    static constexpr int SW = WIN / 2;
+    static constexpr int TX = NS - (WIN - 1);                  // output columns of an inner tile
+    static constexpr int TX0 = NS - SW;                        // output columns of the first tile (its left window half is folded)
+    static constexpr int KW = (NS + 2 * HALF + 2) / 2;         // staged right-image elements per copy
+    static constexpr int R4 = 4 * KW;                          // uint4 per row: [channel][copy E/O][KW]
+    static constexpr int L4 = 2 * NS;                          // uint4 per row: [step][channel]
+    static constexpr size_t SMEM = (size_t)ROWS * (R4 + L4) * 16;
+};
+
+__device__ __forceinline__ uint32_t bt_pair_cost(const uint4& r0, const uint4& r1, const uint4& l0, const uint4& l1)
+{
+    // element r = {v, lo(v), hi(v), -} of the right image, l = {u + K, K - u, K - hi(u), lo(u) + K} of the left image
+    // c0 + K = max(K, u - hi(v) + K, lo(v) - u + K); c1 + K = max(K, v - hi(u) + K, lo(u) - v + K)
+    uint32_t a0 = __vimax3_u16x2(l0.x - r0.z, r0.y + l0.y, COST_K2);
+    uint32_t a1 = __vimax3_u16x2(r0.x + l0.z, l0.w - r0.x, COST_K2);
+    uint32_t ca = __vminu2(a0, a1) - COST_K2;
+    uint32_t b0 = __vimax3_u16x2(l1.x - r1.z, r1.y + l1.y, COST_K2);
+    uint32_t b1 = __vimax3_u16x2(r1.x + l1.z, l1.w - r1.x, COST_K2);
+    uint32_t cb = __vminu2(b0, b1) - COST_K2;
+    return ca + ((cb >> 2) & 0x3fff3fffu);
+}
+
+template <int WIN, int NW>
+__global__ void __launch_bounds__(CostTile<WIN, NW>::THREADS)
 pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, SgbmGeom g, uint32_t* __restrict__ hsum)
 {
-    constexpr int NS = 10 * WIN;            // steps per tile (a multiple of the ring length)
-    constexpr int TX = NS - (WIN - 1);      // output columns per tile
-    constexpr int SW = WIN / 2;
-    extern __shared__ __align__(16) uint16_t sm[];
-    const int half = g.Dp >> 1;             // disparity pairs = threads per row
-    const int t = threadIdx.x % half, ry = threadIdx.x / half;
-    const int y = blockIdx.y * (blockDim.x / half) + ry;
-    const int x0 = blockIdx.x * TX;
+    using T = CostTile<WIN, NW>;
+    constexpr int NS = T::NS, SW = T::SW, HALF = T::HALF, KW = T::KW;
+    extern __shared__ __align__(16) uint4 sm4[];
+    const int t = threadIdx.x % HALF, ry = threadIdx.x / HALF;
+    const int y = blockIdx.y * T::ROWS + ry;
+    const bool first = blockIdx.x == 0;
+    const int xs = first ? 0 : T::TX0 + (blockIdx.x - 1) * T::TX - SW;   // virtual column of step 0
     const size_t plane = (size_t)g.W * g.H;
-    // right-image planes, reversed: Rr[k] = R[xmax - k], xmax = largest image x2 any cell of the tile touches
-    const int xmax = min(x0 + TX - 1 + SW, g.W1 - 1) + g.minX1 - g.minD;
-    const int span = NS + g.Dp + 2;
-    const int rows = blockDim.x / half;
-    uint16_t* myR = sm + (size_t)ry * (12 * span);          // [plane 0..5][copy E/O][span]
-    uint32_t* myL = (uint32_t*)(sm + (((size_t)rows * 12 * span + 7) & ~(size_t)7)) + (size_t)ry * (8 * NS);  // [step][8] pre-biased left values, 16-byte aligned
+    uint4* myR = sm4 + (size_t)ry * (T::R4 + T::L4);
+    uint4* myL = myR + T::R4;
+    // reversed right row: E[k] = R[xmax - k]; pair t at step k needs halfwords E[k0], E[k0 + 1], k0 = NS + 2t - k
+    const int xmax = xs + NS + g.minX1 - g.minD;
     if (y < g.H) {
         const uint8_t* R = PR + (size_t)y * g.W;
-        for (int idx = t; idx < 6 * span; idx += half) {
-            int pl = idx / span, k = idx - pl * span;
-            int xr = min(max(xmax - k, 0), g.W - 1);
-            uint16_t v = R[pl * plane + xr];
-            myR[(pl * 2) * span + k] = v;                    // copy E
-            if (k > 0) myR[(pl * 2 + 1) * span + k - 1] = v;  // copy O: O[k] = E[k + 1]
+        for (int idx = t; idx < T::R4; idx += HALF) {
+            const int ch = idx / (2 * KW), rem = idx - ch * (2 * KW), copy = rem / KW, kw = rem - copy * KW;
+            const int k = 2 * kw + copy;
+            const int xa = min(max(xmax - k, 0), g.W - 1), xb = min(max(xmax - k - 1, 0), g.W - 1);
+            const uint8_t* q = R + (size_t)(3 * ch) * plane;
+            uint4 e;
+            e.x = (uint32_t)q[xa] | ((uint32_t)q[xb] << 16);
+            e.y = (uint32_t)q[plane + xa] | ((uint32_t)q[plane + xb] << 16);
+            e.z = (uint32_t)q[2 * plane + xa] | ((uint32_t)q[2 * plane + xb] << 16);
+            e.w = 0;
+            myR[idx] = e;
         }
         const uint8_t* L = PL + (size_t)y * g.W;
-        for (int k = t; k < NS; k += half) {
-            int x = min(max(x0 - SW + k, 0), g.W1 - 1) + g.minX1;
-            for (int ch = 0; ch < 2; ++ch) {
-                uint32_t u = L[(3 * ch) * plane + x], u0 = L[(3 * ch + 1) * plane + x], u1 = L[(3 * ch + 2) * plane + x];
-                myL[k * 8 + ch * 4 + 0] = u * 0x10001u + COST_K2;   // u + K
-                myL[k * 8 + ch * 4 + 1] = COST_K2 - u * 0x10001u;   // K - u
-                myL[k * 8 + ch * 4 + 2] = COST_K2 - u1 * 0x10001u;  // K - hi(u)
-                myL[k * 8 + ch * 4 + 3] = u0 * 0x10001u + COST_K2;  // lo(u) + K
-            }
+        for (int idx = t; idx < T::L4; idx += HALF) {
+            const int k = idx >> 1, ch = idx & 1;
+            const int x = min(max(xs + k, 0), g.W1 - 1) + g.minX1;
+            const uint32_t u = L[(3 * ch) * plane + x], u0 = L[(3 * ch + 1) * plane + x], u1 = L[(3 * ch + 2) * plane + x];
+            myL[idx] = make_uint4(u * 0x10001u + COST_K2, COST_K2 - u * 0x10001u, COST_K2 - u1 * 0x10001u, u0 * 0x10001u + COST_K2);
         }
     }
     __syncthreads();
     if (y >= g.H) return;
+    const uint32_t padmask = (2 * t >= g.D ? 0u : 0xffffu) | (2 * t + 1 >= g.D ? 0u : 0xffff0000u);
+    const uint4* pR = myR + NS / 2 + t;   // element of step 0 (even copy, channel 0)
+    const uint4* pL = myL;
+    const int nvalid = min(NS, g.W1 - xs);            // steps whose column lies inside the image
+    const int nout = min(NS, g.W1 - xs + SW);         // steps that still produce an output column
+    const int kmin = first ? SW : WIN - 1;            // first step with a complete window
     uint32_t ring[WIN];
+    uint32_t hs = 0, pix = 0;
 #pragma unroll
     for (int i = 0; i < WIN; ++i) ring[i] = 0;
-    uint32_t hs = 0;
-    const bool padlo = 2 * t >= g.D, padhi = 2 * t + 1 >= g.D;
-    uint32_t* out = hsum + ((size_t)y * g.W1) * half + t;
+    if (first) {
+        // columns -SW..-1 repeat column 0: they sit in the ring slots that leave the window at steps SW+1..WIN-1
+        const uint32_t pb = bt_pair_cost(pR[0], pR[2 * KW], pL[0], pL[1]) & padmask;
+#pragma unroll
+        for (int i = SW + 1; i < WIN; ++i) ring[i] = pb;
+        hs = SW * pb;
+    }
+    uint32_t* out = hsum + ((ptrdiff_t)y * g.W1 + (xs - SW)) * HALF + t;   // output column of step 0 (never stored when negative)
 #pragma unroll 1
-    for (int kb = 0; kb < NS; kb += WIN) {
+    for (int kb = 0; kb < NS; kb += T::BODY) {
 #pragma unroll
-        for (int i = 0; i < WIN; ++i) {
+        for (int i = 0; i < T::BODY; ++i) {
             const int k = kb + i;
-            const int x = min(max(x0 - SW + k, 0), g.W1 - 1) + g.minX1;
-            // halfword index of the pair (d = 2t -> x2, d = 2t+1 -> x2 - 1) in the reversed row
-            const int k0 = xmax - (x - g.minD) + 2 * t;
-            const uint16_t* base = myR + ((k0 & 1) ? span : 0);
-            const uint32_t* pr = (const uint32_t*)(base) + (k0 >> 1);
-            const uint4 lva = *(const uint4*)(myL + k * 8), lvb = *(const uint4*)(myL + k * 8 + 4);  // two broadcast 16-byte reads
-            const uint32_t lv[8] = {lva.x, lva.y, lva.z, lva.w, lvb.x, lvb.y, lvb.z, lvb.w};
-            uint32_t pix = 0;
-#pragma unroll
-            for (int ch = 0; ch < 2; ++ch) {
-                const uint32_t v = pr[(ch * 3 + 0) * span], v0 = pr[(ch * 3 + 1) * span], v1 = pr[(ch * 3 + 2) * span];
-                const uint32_t uK = lv[ch * 4 + 0], Ku = lv[ch * 4 + 1], Ku1 = lv[ch * 4 + 2], u0K = lv[ch * 4 + 3];
-                // c0 + K = max(K, u - hi(v) + K, lo(v) - u + K); c1 + K = max(K, v - hi(u) + K, lo(u) - v + K)
-                uint32_t c0 = __vimax3_u16x2(uK - v1, v0 + Ku, COST_K2);
-                uint32_t c1 = __vimax3_u16x2(v + Ku1, u0K - v, COST_K2);
-                uint32_t c = __vminu2(c0, c1) - COST_K2;
-                pix += ch ? ((c >> 2) & 0x3fff3fffu) : c;
-            }
-            if (padlo) pix &= 0xffff0000u;
-            if (padhi) pix &= 0x0000ffffu;
-            hs = hs + pix - ring[i];
-            ring[i] = pix;
-            const int xo = x0 + k - (WIN - 1);
-            if (k >= WIN - 1 && xo < g.W1) out[(size_t)xo * half] = hs;
+            const uint4* r = pR + (i & 1) * KW - ((i + 1) >> 1);
+            const uint32_t c = bt_pair_cost(r[0], r[2 * KW], pL[2 * i], pL[2 * i + 1]) & padmask;
+            pix = k < nvalid ? c : pix;
+            hs = hs + pix - ring[i % WIN];
+            ring[i % WIN] = pix;
+            if (k >= kmin && k < nout) out[(size_t)i * HALF] = hs;
         }
+        pR -= T::BODY / 2;
+        pL += 2 * T::BODY;
+        out += (size_t)T::BODY * HALF;
     }
 }
 
@@ -218,22 +245,36 @@ int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, cons
     prefilter_kernel<<<pg, 128, 0, s>>>(r, g.W, g.H, g.ftzero, planes + 6 * plane);
     MVS_LAUNCH_CHECK_N(ctx, "prefilter_kernel", 2);
     {
-        const int half = g.Dp >> 1, rows = 128 / half > 0 ? 128 / half : 1, win = 2 * g.SW2 + 1;
-        const int ns = 10 * win, tx = ns - (win - 1), span = ns + g.Dp + 2;
-        dim3 cg(cdiv(g.W1, tx), cdiv(g.H, rows));
-        size_t smem = (size_t)rows * (12 * span * sizeof(uint16_t) + 8 * ns * sizeof(uint32_t)) + 16;
         uint32_t* hs32 = (uint32_t*)hsum;
         const uint8_t* PR = planes + 6 * plane;
+        const int win = 2 * g.SW2 + 1, nw = g.Dp / 64;
+        int rc = MVS_OK;
+#define COST_LAUNCH(WIN_, NW_)                                                                                              \
+    do {                                                                                                                    \
+        using T = CostTile<WIN_, NW_>;                                                                                      \
+        dim3 cg(1 + (g.W1 > T::TX0 ? cdiv(g.W1 - T::TX0, T::TX) : 0), cdiv(g.H, T::ROWS));                                   \
+        static_assert(T::SMEM <= 48 * 1024, "cost tile exceeds the default shared-memory window");                          \
+        pixcost_hsum_kernel<WIN_, NW_><<<cg, T::THREADS, T::SMEM, s>>>(planes, PR, g, hs32);                                 \
+    } while (0)
+#define COST_LAUNCH_NW(WIN_)                                                                                                \
+    switch (nw) {                                                                                                           \
+    case 1: COST_LAUNCH(WIN_, 1); break;                                                                                    \
+    case 2: COST_LAUNCH(WIN_, 2); break;                                                                                    \
+    case 3: COST_LAUNCH(WIN_, 3); break;                                                                                    \
+    case 4: COST_LAUNCH(WIN_, 4); break;                                                                                    \
+    default: rc = MVS_ERR_UNSUPPORTED;                                                                                      \
+    }
         switch (win) {
-        case 1: pixcost_hsum_kernel<1><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
-        case 3: pixcost_hsum_kernel<3><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
-        case 5: pixcost_hsum_kernel<5><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
-        case 7: pixcost_hsum_kernel<7><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
-        case 9: pixcost_hsum_kernel<9><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
-        case 11: pixcost_hsum_kernel<11><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
-        case 13: pixcost_hsum_kernel<13><<<cg, rows * half, smem, s>>>(planes, PR, g, hs32); break;
-        default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "cost: block size %d", win);
+        case 1: COST_LAUNCH_NW(1); break;
+        case 3: COST_LAUNCH_NW(3); break;
+        case 5: COST_LAUNCH_NW(5); break;
+        case 7: COST_LAUNCH_NW(7); break;
+        case 9: COST_LAUNCH_NW(9); break;
+        case 11: COST_LAUNCH_NW(11); break;
+        case 13: COST_LAUNCH_NW(13); break;
+        default: rc = MVS_ERR_UNSUPPORTED;
         }
+        if (rc) return mvs_fail(ctx, rc, "cost: block size %d / Dp %d", win, g.Dp);
         MVS_LAUNCH_CHECK(ctx, "pixcost_hsum_kernel");
     }
     size_t rowwords = (size_t)g.W1 * (g.Dp >> 1);

@@ -87,10 +87,11 @@ __global__ void prefilter_kernel(const uint8_t* __restrict__ img, int W, int H, 
 // disparities (u16x2) and walks along x keeping the last WIN pixel costs in a register ring, so the row box sum is
 // a sliding window (one add, one subtract per step).  Step k of a tile is the virtual column xs + k; columns left
 // of the image are folded into the ring's initial state, columns right of it repeat the last pixel cost
-// (replicate clamping).  The right image's prefilter planes are staged reversed in shared memory, three planes of a
-// channel per 16-byte element, so that the element of disparity pair t at step k sits at (NS/2 + t - ceil(k/2)) of
-// the copy of k's parity (the odd copy is shifted by one halfword): every address of the unrolled loop is a
-// running pointer plus an immediate.  All arithmetic is packed 16-bit with a +1024 bias so that the
+// (replicate clamping).  The right image's prefilter planes are staged reversed in shared memory, one 16-byte
+// element {2 pixels x 3 planes x 2 channels, as bytes} per position, so that the element of disparity pair t at step
+// k sits at (NS/2 + t - ceil(k/2)) of the copy of k's parity (the odd copy is shifted by one pixel): every address of
+// the unrolled loop is a running pointer plus an immediate, and a step costs one 16-byte load per thread (the
+// kernel is bound by shared-memory wavefronts, so the bytes are widened to u16x2 with PRMT in registers).  All arithmetic is packed 16-bit with a +1024 bias so that the
 // Birchfield-Tomasi differences never go negative (plain 32-bit adds/subs then act per halfword).
 #define COST_K2 0x04000400u
 template <int WIN, int NW>
@@ -104,22 +105,24 @@ struct CostTile {
     static constexpr int TX = NS - (WIN - 1);                  // output columns of an inner tile
     static constexpr int TX0 = NS - SW;                        // output columns of the first tile (its left window half is folded)
     static constexpr int KW = (NS + 2 * HALF + 2) / 2;         // staged right-image elements per copy
-    static constexpr int R4 = 4 * KW;                          // uint4 per row: [channel][copy E/O][KW]
+    static constexpr int R4 = 2 * KW;                          // uint4 per row: [copy E/O][KW]
     static constexpr int L4 = 2 * NS;                          // uint4 per row: [step][channel]
     static constexpr size_t SMEM = (size_t)ROWS * (R4 + L4) * 16;
 };
 
-__device__ __forceinline__ uint32_t bt_pair_cost(const uint4& r0, const uint4& r1, const uint4& l0, const uint4& l1)
+__device__ __forceinline__ uint32_t bt_channel_cost(uint32_t w0, uint32_t w1, const uint4& l)
 {
-    // element r = {v, lo(v), hi(v), -} of the right image, l = {u + K, K - u, K - hi(u), lo(u) + K} of the left image
+    // right image: w0 = bytes {v, v', lo(v), lo(v')}, w1 = bytes {hi(v), hi(v'), -, -} (v' = the pair's second disparity);
+    // left image: l = {u + K, K - u, K - hi(u), lo(u) + K}
     // c0 + K = max(K, u - hi(v) + K, lo(v) - u + K); c1 + K = max(K, v - hi(u) + K, lo(u) - v + K)
-    uint32_t a0 = __vimax3_u16x2(l0.x - r0.z, r0.y + l0.y, COST_K2);
-    uint32_t a1 = __vimax3_u16x2(r0.x + l0.z, l0.w - r0.x, COST_K2);
-    uint32_t ca = __vminu2(a0, a1) - COST_K2;
-    uint32_t b0 = __vimax3_u16x2(l1.x - r1.z, r1.y + l1.y, COST_K2);
-    uint32_t b1 = __vimax3_u16x2(r1.x + l1.z, l1.w - r1.x, COST_K2);
-    uint32_t cb = __vminu2(b0, b1) - COST_K2;
-    return ca + ((cb >> 2) & 0x3fff3fffu);
+    const uint32_t v = __byte_perm(w0, 0u, 0x4140), vlo = __byte_perm(w0, 0u, 0x4342), vhi = __byte_perm(w1, 0u, 0x4140);
+    uint32_t c0 = __vimax3_u16x2(l.x - vhi, vlo + l.y, COST_K2);
+    uint32_t c1 = __vimax3_u16x2(v + l.z, l.w - v, COST_K2);
+    return __vminu2(c0, c1) - COST_K2;
+}
+__device__ __forceinline__ uint32_t bt_pair_cost(const uint4& r, const uint4& l0, const uint4& l1)
+{
+    return bt_channel_cost(r.x, r.y, l0) + ((bt_channel_cost(r.z, r.w, l1) >> 2) & 0x3fff3fffu);
 }
 
 template <int WIN, int NW>
@@ -141,16 +144,17 @@ pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ 
     if (y < g.H) {
         const uint8_t* R = PR + (size_t)y * g.W;
         for (int idx = t; idx < T::R4; idx += HALF) {
-            const int ch = idx / (2 * KW), rem = idx - ch * (2 * KW), copy = rem / KW, kw = rem - copy * KW;
+            const int copy = idx / KW, kw = idx - copy * KW;
             const int k = 2 * kw + copy;
             const int xa = min(max(xmax - k, 0), g.W - 1), xb = min(max(xmax - k - 1, 0), g.W - 1);
-            const uint8_t* q = R + (size_t)(3 * ch) * plane;
-            uint4 e;
-            e.x = (uint32_t)q[xa] | ((uint32_t)q[xb] << 16);
-            e.y = (uint32_t)q[plane + xa] | ((uint32_t)q[plane + xb] << 16);
-            e.z = (uint32_t)q[2 * plane + xa] | ((uint32_t)q[2 * plane + xb] << 16);
-            e.w = 0;
-            myR[idx] = e;
+            uint32_t w[4];
+#pragma unroll
+            for (int ch = 0; ch < 2; ++ch) {
+                const uint8_t* q = R + (size_t)(3 * ch) * plane;
+                w[2 * ch] = (uint32_t)q[xa] | ((uint32_t)q[xb] << 8) | ((uint32_t)q[plane + xa] << 16) | ((uint32_t)q[plane + xb] << 24);
+                w[2 * ch + 1] = (uint32_t)q[2 * plane + xa] | ((uint32_t)q[2 * plane + xb] << 8);
+            }
+            myR[idx] = make_uint4(w[0], w[1], w[2], w[3]);
         }
         const uint8_t* L = PL + (size_t)y * g.W;
         for (int idx = t; idx < T::L4; idx += HALF) {
@@ -163,7 +167,7 @@ pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ 
     __syncthreads();
     if (y >= g.H) return;
     const uint32_t padmask = (2 * t >= g.D ? 0u : 0xffffu) | (2 * t + 1 >= g.D ? 0u : 0xffff0000u);
-    const uint4* pR = myR + NS / 2 + t;   // element of step 0 (even copy, channel 0)
+    const uint4* pR = myR + NS / 2 + t;   // element of step 0 (even copy)
     const uint4* pL = myL;
     const int nvalid = min(NS, g.W1 - xs);            // steps whose column lies inside the image
     const int nout = min(NS, g.W1 - xs + SW);         // steps that still produce an output column
@@ -174,7 +178,7 @@ pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ 
     for (int i = 0; i < WIN; ++i) ring[i] = 0;
     if (first) {
         // columns -SW..-1 repeat column 0: they sit in the ring slots that leave the window at steps SW+1..WIN-1
-        const uint32_t pb = bt_pair_cost(pR[0], pR[2 * KW], pL[0], pL[1]) & padmask;
+        const uint32_t pb = bt_pair_cost(pR[0], pL[0], pL[1]) & padmask;
 #pragma unroll
         for (int i = SW + 1; i < WIN; ++i) ring[i] = pb;
         hs = SW * pb;
@@ -186,7 +190,7 @@ pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ 
         for (int i = 0; i < T::BODY; ++i) {
             const int k = kb + i;
             const uint4* r = pR + (i & 1) * KW - ((i + 1) >> 1);
-            const uint32_t c = bt_pair_cost(r[0], r[2 * KW], pL[2 * i], pL[2 * i + 1]) & padmask;
+            const uint32_t c = bt_pair_cost(r[0], pL[2 * i], pL[2 * i + 1]) & padmask;
             pix = k < nvalid ? c : pix;
             hs = hs + pix - ring[i % WIN];
             ring[i % WIN] = pix;

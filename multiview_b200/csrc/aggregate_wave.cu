@@ -11,9 +11,12 @@
 //   * L0 stays in registers; L1/L2/L3 of the row above come from a shared-memory ring written by warp r-1.
 //     A ring slot is {min(L) x2, -, -, SENT | L[0..D) | SENT, -, -, -}: the sentinel words give the d-1 / d+1
 //     neighbours of lanes 0 and 31 without branches and the minimum travels with the data;
-//   * neighbouring warps are coupled only by two shared-memory counters per ring row ("pixels written",
-//     "pixels consumed", release/acquire at CTA scope): there is no CTA-wide barrier inside a band, and the rings
-//     are two slots deeper than lock-step needs, so a warp that stalls does not stall the other fifteen;
+//   * neighbouring warps are coupled only by mbarriers: per ring row eight "pixel p written" and eight "pixel p
+//     consumed" barriers (index p mod 8, phase parity (p / 8) & 1; the ring depths keep producer and consumer less
+//     than eight pixels apart, so a parity is never ambiguous).  arrive has release and try_wait acquire semantics
+//     at CTA scope, so no memory fence is issued and a waiting warp is suspended instead of burning issue slots.
+//     There is no CTA-wide barrier inside a band, and the rings are two slots deeper than lock-step needs, so a
+//     warp that stalls does not stall the other fifteen;
 //   * image borders need no branches: the slots "x = -1" and "x = W1" are filled with zeros (Lr = 0, minLr = 0
 //     outside the image, as the reference initialises its Lr buffers);
 //   * C (and S in the backward sweep) stream through a per-warp cp.async pipeline three pixels ahead;
@@ -40,6 +43,7 @@
 #define WAVE_D3 4            // ring depth for L3 (lock-step needs 2)
 #endif
 #define WAVE_SPIN_LIMIT (1 << 20)
+#define WAVE_NB 8            // mbarriers per ring row and kind (pixel index mod WAVE_NB)
 #define WAVE_CTL_PAD 16
 // a producer at pixel x may overwrite its slots once the consumer has finished pixel x - WAVE_WAR - 1:
 // L1 slot x % D12 held pixel x - D12 (read at x - D12 + 1), L3 slot x % D3 held pixel x - D3 (read at x - D3 - 1)
@@ -70,20 +74,21 @@ __device__ __forceinline__ void st_release(int* p, int v)
 {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-__device__ __forceinline__ int lds_relaxed(uint32_t saddr)
+__device__ __forceinline__ void mbar_init(uint32_t saddr, int count)
 {
-    int v;
-    asm volatile("ld.relaxed.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"(saddr) : "memory");
-    return v;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(saddr), "r"(count) : "memory");
 }
-__device__ __forceinline__ void fence_cta() { asm volatile("fence.acq_rel.cta;" ::: "memory"); }
-__device__ __forceinline__ void sts_release(uint32_t saddr, int v)
+__device__ __forceinline__ void mbar_inval(uint32_t saddr) { asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(saddr) : "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint32_t saddr)  // release at CTA scope
 {
-    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(saddr) : "memory");
 }
-__device__ __forceinline__ void sts_relaxed(uint32_t saddr, int v)
+__device__ __forceinline__ bool mbar_try_wait(uint32_t saddr, uint32_t parity)  // acquire at CTA scope; may suspend the warp
 {
-    asm volatile("st.relaxed.cta.shared.s32 [%0], %1;" ::"r"(saddr), "r"(v) : "memory");
+    uint32_t ok;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(saddr), "r"(parity) : "memory");
+    return ok != 0;
 }
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gmem)
 {
@@ -178,15 +183,20 @@ wave_kernel(WaveParams p)
     uint32_t* cstream = ring + RG::WORDS;                  // [warp][stage][WPP] cost stream
     uint32_t* sstream = cstream + RG::STREAM_WORDS;        // [warp][stage][WPP] S-in stream (backward sweep only)
     __shared__ int s_item;
-    __shared__ int s_done[WAVE_R + 1];   // [ring row k] pixels of ring row k written (k = 0: by the helper, else by warp k-1)
-    __shared__ int s_cons[WAVE_R + 1];   // [ring row k] pixels of ring row k consumed by warp k
+    // [ring row k][p mod NB]: "pixel p of ring row k written" (k = 0: by the helper, else by warp k-1) and
+    // "pixel p of ring row k consumed" (by warp k); the pseudo-pixel W1 is the zero slot behind the row
+    __shared__ __align__(8) uint64_t s_full[WAVE_R + 1][WAVE_NB];
+    __shared__ __align__(8) uint64_t s_cons[WAVE_R + 1][WAVE_NB];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const bool helper = wid == WAVE_R;
     const int r = wid;
     const int W1 = p.W1;
     const uint32_t P1x2 = wdup16((uint32_t)p.P1), P2x2 = wdup16((uint32_t)p.P2);
     const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
-    const uint32_t done_s = (uint32_t)__cvta_generic_to_shared(s_done), cons_s = (uint32_t)__cvta_generic_to_shared(s_cons);
+    const uint32_t full_s = (uint32_t)__cvta_generic_to_shared(s_full), cons_s = (uint32_t)__cvta_generic_to_shared(s_cons);
+    auto bar_of = [](uint32_t base, int row, int pixel) -> uint32_t { return base + (uint32_t)(row * WAVE_NB + (pixel & (WAVE_NB - 1))) * 8u; };
+    auto par_of = [](int pixel) -> uint32_t { return (uint32_t)(pixel / WAVE_NB) & 1u; };
+    bool bars_valid = false;
 
     for (int s = threadIdx.x; s < RG::NSLOTS; s += blockDim.x) {  // sentinels: written once, never overwritten
         ring[s * RG::SLOT + 3] = SENT2;
@@ -210,7 +220,20 @@ wave_kernel(WaveParams p)
     for (;;) {
         __syncthreads();  // every warp has left the previous band
         if (threadIdx.x == 0) s_item = atomicAdd(p.ticket, 1);
-        if (threadIdx.x <= WAVE_R) { s_done[threadIdx.x] = 0; s_cons[threadIdx.x] = 0; }
+        // re-arm the mbarriers: invalidate all of them, then (after a CTA barrier: an invalidation may drop barrier state
+        // another thread has just initialised) initialise them for one arrival per phase
+        if (bars_valid) {
+            for (int i = threadIdx.x; i < (WAVE_R + 1) * WAVE_NB; i += blockDim.x) {
+                mbar_inval(full_s + (uint32_t)i * 8u);
+                mbar_inval(cons_s + (uint32_t)i * 8u);
+            }
+            __syncthreads();
+        }
+        for (int i = threadIdx.x; i < (WAVE_R + 1) * WAVE_NB; i += blockDim.x) {
+            mbar_init(full_s + (uint32_t)i * 8u, 1);
+            mbar_init(cons_s + (uint32_t)i * 8u, 1);
+        }
+        bars_valid = true;
         __syncthreads();
         if (s_item >= p.nbands * p.F) break;
         const int band = s_item / p.F, fi = s_item - band * p.F;
@@ -224,17 +247,20 @@ wave_kernel(WaveParams p)
         const int* prev_progress = my_progress - (first_band ? 0 : 1);
         bool failed = false;
 
-        // bounded wait on a shared-memory counter: every lane polls the same word (a broadcast read)
-        // `seen` caches the last value read, so a warp that runs with slack does not touch the counter at all
-        // Returns true when it had to read the counter: the caller then issues ONE acquire fence for all its waits.
-        auto wait_smem = [&](uint32_t saddr, int need, int& seen) -> bool {
-            if (seen >= need || failed) return false;
+        // bounded wait for "pixel `pixel` of ring row `row` written / consumed"
+        auto wait_bar = [&](uint32_t base, int row, int pixel) {
+            if (failed) return;
+            const uint32_t b = bar_of(base, row, pixel), par = par_of(pixel);
             int spins = 0;
-            while ((seen = lds_relaxed(saddr)) < need) {
-                if (++spins > WAVE_SPIN_LIMIT) { atomicExch(p.error, 1); failed = true; break; }
-                if ((spins & 4095) == 0 && *(volatile int*)p.error) { failed = true; break; }
+            while (!mbar_try_wait(b, par)) {
+                if (++spins > WAVE_SPIN_LIMIT) {
+                    // where it happened: kind (1 written / 2 consumed), ring row, band, pixel
+                    atomicCAS(p.error, 0, ((base == full_s ? 1 : 2) << 28) | (row << 23) | ((band & 127) << 16) | (pixel & 0xffff));
+                    failed = true;
+                    break;
+                }
+                if ((spins & 63) == 0 && *(volatile int*)p.error) { failed = true; break; }
             }
-            return true;
         };
 
         // zero slots prepared before anybody runs: the row above the image, and "x = -1" of the row each warp reads
@@ -253,15 +279,13 @@ wave_kernel(WaveParams p)
 
         if (helper) {
             if (VERT) {
-                if (first_band) {
-                    if (lane == 0) sts_release(done_s, W1 + 1);  // everything above the image is zero, for good
-                } else {
+                if (!first_band) {  // (first band: everything above the image is zero, warp 0 does not wait)
                     // boundary row of the previous band -> ring row 0, four pixels ahead of publication
-                    int seen = 0, seen_cons = 0;
+                    int seen = 0;
                     for (int xp = 0; xp <= W1 + 2; ++xp) {
                         if (xp <= W1) {
                             // slot xp % 8 last held pixel xp - 8, read by warp 0 (direction 1) at its pixel xp - 7
-                            if (xp >= 7 && wait_smem(cons_s, xp - 6, seen_cons)) fence_cta();  // acquire before overwriting the slot
+                            if (xp >= 7) wait_bar(cons_s, 0, xp - 7);  // acquire before overwriting the slot
                             if (xp < W1) {
                                 const int need = xp + 1;
                                 if (seen < need && !failed) {
@@ -269,7 +293,7 @@ wave_kernel(WaveParams p)
                                     while ((seen = ld_acquire(prev_progress)) < need) {
                                         // bounded: a timeout here or anywhere else in the grid ends all waiting (results are
                                         // then invalid and the host reports an error): a logic fault cannot hang the GPU
-                                        if (++spins > WAVE_SPIN_LIMIT) { atomicExch(p.error, 1); failed = true; break; }
+                                        if (++spins > WAVE_SPIN_LIMIT) { atomicCAS(p.error, 0, (3 << 28) | ((band & 127) << 16) | (xp & 0xffff)); failed = true; break; }
                                         if ((spins & 1023) == 0 && *(volatile int*)p.error) { failed = true; break; }
                                         __nanosleep(32);
                                     }
@@ -295,16 +319,15 @@ wave_kernel(WaveParams p)
                         cp_async_commit();
                         cp_async_wait<2>();  // the group of pixel xp - 2 has landed
                         if (xp >= 2) {
-                            __syncwarp();  // all lanes' copies are in; lane 0 publishes them
-                            if (lane == 0) sts_release(done_s, xp - 1);
+                            __syncwarp();  // all lanes' copies are in; lane 0 publishes pixel xp - 2
+                            if (lane == 0) mbar_arrive(bar_of(full_s, 0, xp - 2));
                         }
                     }
                 }
             }
         } else if (r < rows) {
             const bool to_ring = r + 1 < rows, to_global = VERT && r + 1 == rows && !last_band;
-            const uint32_t my_done_s = done_s + 4 * r, my_cons_s = cons_s + 4 * r;          // ring row r (read)
-            const uint32_t nx_done_s = done_s + 4 * (r + 1), nx_cons_s = cons_s + 4 * (r + 1);  // ring row r+1 (written)
+            const bool wait_above = VERT && !(first_band && r == 0);
             uint32_t L0[NW];
 #pragma unroll
             for (int j = 0; j < NW; ++j) L0[j] = 0;
@@ -326,15 +349,11 @@ wave_kernel(WaveParams p)
             uint32_t* gout = bout + lw;  // this lane's data words of boundary pixel 0, direction 1
             // running slot indices: reads (x-1) % rd12, x % rd12, (x+1) % rd3; writes x % D12, x % D3
             int i1 = rd12 - 1, i2 = 0, i3 = 1 % rd3, j12 = 0, j3 = 0;
-            int seen_done = 0, seen_cons = 0;
 
             for (int x = 0; x < W1; ++x) {
                 stream_issue(x + RG::STAGE - 1);
-                if (VERT) {
-                    bool polled = wait_smem(my_done_s, min(x + 2, W1 + 1), seen_done);      // the row above is written through pixel x + 1
-                    if (to_ring && x >= WAVE_WAR) polled |= wait_smem(nx_cons_s, x - WAVE_WAR, seen_cons);  // the slots about to be overwritten were read
-                    if (polled) fence_cta();  // acquire: the ring accesses below stay behind the counter reads
-                }
+                if (wait_above) wait_bar(full_s, r, x + 1);                                       // the row above is written through pixel x + 1
+                if (VERT && to_ring && x > WAVE_WAR) wait_bar(cons_s, r + 1, x - WAVE_WAR - 1);  // the slots about to be overwritten were read
                 cp_async_wait<RG::STAGE - 1>();  // this lane's words of pixel x have landed (own copies only)
                 uint32_t Cw[NW], Sw[NW];
                 ldw<NW>(cstream + my_stream + (x & (RG::STAGE - 1)) * RG::WPP, Cw);
@@ -424,12 +443,11 @@ wave_kernel(WaveParams p)
                 }
                 if (VERT) {
                     // publish: ring row r+1 holds pixel x; ring row r has been read for pixel x.  The warp barrier
-                    // puts every lane's ring reads and writes before lane 0's release store.
+                    // puts every lane's ring reads and writes before lane 0's arrivals (release).
                     __syncwarp();
                     if (lane == 0) {
-                        fence_cta();
-                        sts_relaxed(nx_done_s, x + 1);
-                        sts_relaxed(my_cons_s, x + 1);
+                        if (to_ring) mbar_arrive(bar_of(full_s, r + 1, x));
+                        mbar_arrive(bar_of(cons_s, r, x));
                     }
                 }
                 i1 = i1 + 1 == rd12 ? 0 : i1 + 1;
@@ -440,15 +458,15 @@ wave_kernel(WaveParams p)
             }
             if (to_ring && VERT) {
                 // zero slot "x = W1" for direction 3 of the row below (its predecessor is outside the image);
-                // "W1 + 1 pixels written" is what the row below waits for at its last pixel
+                // the pseudo-pixel W1 is what the row below waits for at its last pixel
                 if (DIRMASK & 8) {
-                    if (W1 >= RG::D3 && wait_smem(nx_cons_s, W1 - RG::D3, seen_cons)) fence_cta();  // that L3 slot held pixel W1 - D3
+                    if (W1 > RG::D3) wait_bar(cons_s, r + 1, W1 - RG::D3 - 1);  // that L3 slot held pixel W1 - D3
                     uint32_t* d = ring + wb3 + j3 * RG::SLOT;
                     for (int k = lane; k < RG::WPP; k += 32) d[k - lw + 4] = 0;
                     if (lane == 0) d[-4] = 0;
                 }
                 __syncwarp();
-                if (lane == 0) sts_release(nx_done_s, W1 + 1);
+                if (lane == 0) mbar_arrive(bar_of(full_s, r + 1, W1));
             }
         }
         cp_async_wait<0>();
@@ -538,7 +556,8 @@ int sgbm_aggregate_wave_status(mvs_ctx* ctx, cudaStream_t stream)
     MVS_CUDA(ctx, cudaStreamSynchronize(stream));
     if (h) {
         cudaMemsetAsync(it->second.p, 0, sizeof(int), stream);
-        return mvs_fail(ctx, MVS_ERR_CUDA, "aggregation: a bounded inter-band wait expired (results invalid)");
+        return mvs_fail(ctx, MVS_ERR_CUDA, "aggregation: a bounded wait expired (results invalid; kind %d, ring row %d, band %d, pixel %d)",
+                        (h >> 28) & 3, (h >> 23) & 31, (h >> 16) & 127, h & 0xffff);
     }
     return MVS_OK;
 }

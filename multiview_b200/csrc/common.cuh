@@ -115,6 +115,8 @@ int hist_sum_dev(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int h
 
 // stage kernels of the SGBM chain (cost.cu, aggregate.cu, wta_post.cu)
 int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, const uint8_t* r, int16_t* C);
+int sgbm_cost_volume_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const uint8_t* const* l, const uint8_t* const* r,
+                               int16_t* const* C);
 int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);       // fused wavefront sweeps
 int sgbm_aggregate_paths_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S); // one kernel per direction (debug/A-B)
 int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);

@@ -126,16 +126,16 @@ __device__ __forceinline__ uint32_t bt_pair_cost(const uint4& r, const uint4& l0
 }
 
 template <int WIN, int NW>
-__global__ void __launch_bounds__(CostTile<WIN, NW>::THREADS)
-pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, SgbmGeom g, uint32_t* __restrict__ hsum)
+__device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ PR, const SgbmGeom& g,
+                                                   uint32_t* __restrict__ hsum, int tile, int yblock)
 {
     using T = CostTile<WIN, NW>;
     constexpr int NS = T::NS, SW = T::SW, HALF = T::HALF, KW = T::KW;
     extern __shared__ __align__(16) uint4 sm4[];
     const int t = threadIdx.x % HALF, ry = threadIdx.x / HALF;
-    const int y = blockIdx.y * T::ROWS + ry;
-    const bool first = blockIdx.x == 0;
-    const int xs = first ? 0 : T::TX0 + (blockIdx.x - 1) * T::TX - SW;   // virtual column of step 0
+    const int y = yblock * T::ROWS + ry;
+    const bool first = tile == 0;
+    const int xs = first ? 0 : T::TX0 + (tile - 1) * T::TX - SW;   // virtual column of step 0
     const size_t plane = (size_t)g.W * g.H;
     uint4* myR = sm4 + (size_t)ry * (T::R4 + T::L4);
     uint4* myL = myR + T::R4;
@@ -203,95 +203,128 @@ pixcost_hsum_kernel(const uint8_t* __restrict__ PL, const uint8_t* __restrict__ 
 }
 
 // ---- vertical box sum: C[y] = sum_{dy} hsum[clamp(y+dy)] ; packed u16x2, sliding along y ------------------------
-// A thread owns one packed word (x, disparity pair) of a strip of rows and keeps the WIN row sums of its window
-// in a register ring, so every row sum is read once per strip (+ WIN-1 at the strip start).
+// A thread owns four packed words (16 bytes) of a strip of rows: C(y+1) = C(y) + hsum(y+SH+1) - hsum(y-SH).  The row
+// leaving the window was read WIN rows earlier by the same thread and is still in L2, so HBM sees every row sum once
+// per strip (+ WIN-1 at the strip start) while the instruction count stays at ~4 per word and row.
 #define VSUM_ROWS 96
-template <int WIN>
-__global__ void __launch_bounds__(256)
-vsum_kernel(const uint32_t* __restrict__ hsum, SgbmGeom g, uint32_t* __restrict__ C)
+__device__ __forceinline__ uint4 add4(uint4 a, uint4 b) { return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ uint4 sub4(uint4 a, uint4 b) { return make_uint4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
+template <int WIN, int THREADS>
+__device__ __forceinline__ void vsum_block(const uint32_t* __restrict__ hsum, const SgbmGeom& g, uint32_t* __restrict__ C, int chunk, int strip)
 {
     constexpr int SH = WIN / 2;
-    const size_t rowwords = (size_t)g.W1 * (g.Dp >> 1);
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= rowwords) return;
-    const int y0 = blockIdx.y * VSUM_ROWS, y1 = min(y0 + VSUM_ROWS, g.H);
+    const size_t row4 = (size_t)g.W1 * (g.Dp >> 3);   // 16-byte elements per row (Dp/2 words per pixel, a multiple of 4)
+    const size_t i = (size_t)chunk * THREADS + threadIdx.x;
+    if (i >= row4) return;
+    const uint4* __restrict__ h4 = (const uint4*)hsum + i;
+    uint4* __restrict__ c4 = (uint4*)C + i;
+    const int y0 = strip * VSUM_ROWS, y1 = min(y0 + VSUM_ROWS, g.H);
     const int zero_from = (g.mode == MVS_MODE_HH4) ? g.H - g.SH2 : g.H;  // OpenCV 4.13 leaves these C rows zero in HH4
-    uint32_t ring[WIN];
-    uint32_t acc = 0;
+    uint4 acc = make_uint4(0, 0, 0, 0);
 #pragma unroll
-    for (int k = 0; k < WIN; ++k) {  // ring[k] holds row clamp(y0 - SH + k)
-        ring[k] = __ldg(hsum + (size_t)min(max(y0 - SH + k, 0), g.H - 1) * rowwords + i);
-        acc += ring[k];
+    for (int k = 0; k < WIN; ++k) acc = add4(acc, __ldg(h4 + (size_t)min(max(y0 - SH + k, 0), g.H - 1) * row4));
+#pragma unroll 4
+    for (int y = y0; y < y1; ++y) {
+        const uint4 in = __ldg(h4 + (size_t)min(y + SH + 1, g.H - 1) * row4);    // first touch: stays in L2 for the second
+        const uint4 out = __ldcs(h4 + (size_t)max(y - SH, 0) * row4);            // read WIN rows ago (an L2 hit), last use
+        __stcs(c4 + (size_t)y * row4, y >= zero_from ? make_uint4(0, 0, 0, 0) : acc);
+        acc = sub4(add4(acc, in), out);  // per half: no borrow (acc >= out) and no carry (sums <= 29237)
     }
-    for (int yb = y0; yb < y1; yb += WIN) {
-        uint32_t add[WIN];
-#pragma unroll
-        for (int k = 0; k < WIN; ++k)  // the WIN rows entering the window during this block of steps: all loads in flight at once
-            add[k] = __ldg(hsum + (size_t)min(yb + k + 1 + SH, g.H - 1) * rowwords + i);
-#pragma unroll
-        for (int k = 0; k < WIN; ++k) {
-            const int y = yb + k;
-            if (y < y1) C[(size_t)y * rowwords + i] = (y >= zero_from) ? 0u : acc;
-            acc = acc - ring[k] + add[k];  // per half: no borrow (acc >= ring[k]) and no carry (sums <= 29237)
-            ring[k] = add[k];              // slot k held row clamp(y - SH), the one leaving the window
+}
+
+// One launch = the pixel-cost + row-sum blocks of one frame ("pix") interleaved with the column-sum blocks of the
+// previous frame of the batch ("vsum").  The first kind is bound by shared-memory wavefronts and issue slots, the
+// second by HBM: co-resident on the same SMs they overlap almost completely.  Either kind may be absent (n = 0).
+struct CostJob {
+    const uint8_t *PL, *PR;   // pix: prefilter planes of the left / right image
+    uint32_t* hsum_out;       // pix: row sums written
+    const uint32_t* hsum_in;  // vsum: row sums read (the other half of the double buffer)
+    uint32_t* C;              // vsum: cost volume written
+    int n_pix, n_vsum;        // blocks of each kind
+    int ntiles, nchunks;      // pix block = (tile, row block), vsum block = (column chunk, row strip)
+};
+template <int WIN, int NW>
+__global__ void __launch_bounds__(CostTile<WIN, NW>::THREADS)
+cost_kernel(CostJob j, SgbmGeom g)
+{
+    using T = CostTile<WIN, NW>;
+    // proportional interleave: block i is the v-th vsum block iff v = floor(i * n_vsum / n) steps up at i + 1
+    const unsigned long long n = (unsigned long long)j.n_pix + j.n_vsum;
+    const int v0 = (int)((unsigned long long)blockIdx.x * j.n_vsum / n), v1 = (int)(((unsigned long long)blockIdx.x + 1) * j.n_vsum / n);
+    const bool pix = v1 == v0;
+    const int idx = pix ? (int)blockIdx.x - v0 : v0;
+    if (pix) pixcost_hsum_block<WIN, NW>(j.PL, j.PR, g, j.hsum_out, idx % j.ntiles, idx / j.ntiles);
+    else vsum_block<WIN, T::THREADS>(j.hsum_in, g, j.C, idx % j.nchunks, idx / j.nchunks);
+}
+
+template <int WIN, int NW>
+static int launch_cost(mvs_ctx* ctx, const SgbmGeom& g, CostJob j, bool pix, bool vsum)
+{
+    using T = CostTile<WIN, NW>;
+    static_assert(T::SMEM <= 48 * 1024, "cost tile exceeds the default shared-memory window");
+    j.ntiles = 1 + (g.W1 > T::TX0 ? cdiv(g.W1 - T::TX0, T::TX) : 0);
+    j.nchunks = cdiv((long long)g.W1 * (g.Dp >> 3), T::THREADS);
+    j.n_pix = pix ? j.ntiles * cdiv(g.H, T::ROWS) : 0;
+    j.n_vsum = vsum ? j.nchunks * cdiv(g.H, VSUM_ROWS) : 0;
+    cost_kernel<WIN, NW><<<j.n_pix + j.n_vsum, T::THREADS, T::SMEM, ctx->stream>>>(j, g);
+    MVS_LAUNCH_CHECK(ctx, "cost_kernel");
+    return MVS_OK;
+}
+template <int WIN>
+static int launch_cost_nw(mvs_ctx* ctx, const SgbmGeom& g, const CostJob& j, bool pix, bool vsum)
+{
+    switch (g.Dp / 64) {
+    case 1: return launch_cost<WIN, 1>(ctx, g, j, pix, vsum);
+    case 2: return launch_cost<WIN, 2>(ctx, g, j, pix, vsum);
+    case 3: return launch_cost<WIN, 3>(ctx, g, j, pix, vsum);
+    case 4: return launch_cost<WIN, 4>(ctx, g, j, pix, vsum);
+    }
+    return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "cost: Dp %d", g.Dp);
+}
+static int launch_cost_win(mvs_ctx* ctx, const SgbmGeom& g, const CostJob& j, bool pix, bool vsum)
+{
+    switch (2 * g.SW2 + 1) {
+    case 1: return launch_cost_nw<1>(ctx, g, j, pix, vsum);
+    case 3: return launch_cost_nw<3>(ctx, g, j, pix, vsum);
+    case 5: return launch_cost_nw<5>(ctx, g, j, pix, vsum);
+    case 7: return launch_cost_nw<7>(ctx, g, j, pix, vsum);
+    case 9: return launch_cost_nw<9>(ctx, g, j, pix, vsum);
+    case 11: return launch_cost_nw<11>(ctx, g, j, pix, vsum);
+    case 13: return launch_cost_nw<13>(ctx, g, j, pix, vsum);
+    }
+    return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "cost: block size %d", 2 * g.SW2 + 1);
+}
+
+// Cost volumes of a batch of F pairs: launch k builds the row sums of frame k and, from the other half of a
+// double buffer, the column sums (= the cost volume) of frame k - 1.
+int sgbm_cost_volume_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const uint8_t* const* l, const uint8_t* const* r,
+                               int16_t* const* C)
+{
+    cudaStream_t s = ctx->stream;
+    const size_t plane = (size_t)g.W * g.H;
+    MVS_ARENA(ctx, uint8_t, planes, "sgbm.planes", plane * 12);
+    uint16_t* hsum[2];
+    hsum[0] = (uint16_t*)arena_get(ctx, "sgbm.hsum", g.cells() * 2);
+    hsum[1] = F > 1 ? (uint16_t*)arena_get(ctx, "sgbm.hsum.1", g.cells() * 2) : hsum[0];
+    if (!hsum[0] || !hsum[1]) return MVS_ERR_NOMEM;
+    dim3 pg(cdiv(g.W, 128), g.H);
+    for (int k = 0; k <= F; ++k) {
+        CostJob j;
+        memset(&j, 0, sizeof(j));
+        if (k < F) {
+            prefilter_kernel<<<pg, 128, 0, s>>>(l[k], g.W, g.H, g.ftzero, planes);
+            prefilter_kernel<<<pg, 128, 0, s>>>(r[k], g.W, g.H, g.ftzero, planes + 6 * plane);
+            MVS_LAUNCH_CHECK_N(ctx, "prefilter_kernel", 2);
+            j.PL = planes; j.PR = planes + 6 * plane; j.hsum_out = (uint32_t*)hsum[k & 1];
         }
+        if (k > 0) { j.hsum_in = (const uint32_t*)hsum[(k - 1) & 1]; j.C = (uint32_t*)C[k - 1]; }
+        int rc = launch_cost_win(ctx, g, j, k < F, k > 0);
+        if (rc) return rc;
     }
+    return MVS_OK;
 }
 
 int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, const uint8_t* r, int16_t* C)
 {
-    cudaStream_t s = ctx->stream;
-    size_t plane = (size_t)g.W * g.H;
-    MVS_ARENA(ctx, uint8_t, planes, "sgbm.planes", plane * 12);
-    MVS_ARENA(ctx, uint16_t, hsum, "sgbm.hsum", g.cells());
-    dim3 pg(cdiv(g.W, 128), g.H);
-    prefilter_kernel<<<pg, 128, 0, s>>>(l, g.W, g.H, g.ftzero, planes);
-    prefilter_kernel<<<pg, 128, 0, s>>>(r, g.W, g.H, g.ftzero, planes + 6 * plane);
-    MVS_LAUNCH_CHECK_N(ctx, "prefilter_kernel", 2);
-    {
-        uint32_t* hs32 = (uint32_t*)hsum;
-        const uint8_t* PR = planes + 6 * plane;
-        const int win = 2 * g.SW2 + 1, nw = g.Dp / 64;
-        int rc = MVS_OK;
-#define COST_LAUNCH(WIN_, NW_)                                                                                              \
-    do {                                                                                                                    \
-        using T = CostTile<WIN_, NW_>;                                                                                      \
-        dim3 cg(1 + (g.W1 > T::TX0 ? cdiv(g.W1 - T::TX0, T::TX) : 0), cdiv(g.H, T::ROWS));                                   \
-        static_assert(T::SMEM <= 48 * 1024, "cost tile exceeds the default shared-memory window");                          \
-        pixcost_hsum_kernel<WIN_, NW_><<<cg, T::THREADS, T::SMEM, s>>>(planes, PR, g, hs32);                                 \
-    } while (0)
-#define COST_LAUNCH_NW(WIN_)                                                                                                \
-    switch (nw) {                                                                                                           \
-    case 1: COST_LAUNCH(WIN_, 1); break;                                                                                    \
-    case 2: COST_LAUNCH(WIN_, 2); break;                                                                                    \
-    case 3: COST_LAUNCH(WIN_, 3); break;                                                                                    \
-    case 4: COST_LAUNCH(WIN_, 4); break;                                                                                    \
-    default: rc = MVS_ERR_UNSUPPORTED;                                                                                      \
-    }
-        switch (win) {
-        case 1: COST_LAUNCH_NW(1); break;
-        case 3: COST_LAUNCH_NW(3); break;
-        case 5: COST_LAUNCH_NW(5); break;
-        case 7: COST_LAUNCH_NW(7); break;
-        case 9: COST_LAUNCH_NW(9); break;
-        case 11: COST_LAUNCH_NW(11); break;
-        case 13: COST_LAUNCH_NW(13); break;
-        default: rc = MVS_ERR_UNSUPPORTED;
-        }
-        if (rc) return mvs_fail(ctx, rc, "cost: block size %d / Dp %d", win, g.Dp);
-        MVS_LAUNCH_CHECK(ctx, "pixcost_hsum_kernel");
-    }
-    size_t rowwords = (size_t)g.W1 * (g.Dp >> 1);
-    dim3 vg(cdiv(rowwords, 256), cdiv(g.H, VSUM_ROWS));
-    switch (2 * g.SH2 + 1) {
-    case 1: vsum_kernel<1><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
-    case 3: vsum_kernel<3><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
-    case 5: vsum_kernel<5><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
-    case 7: vsum_kernel<7><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
-    case 9: vsum_kernel<9><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
-    case 11: vsum_kernel<11><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
-    default: vsum_kernel<13><<<vg, 256, 0, s>>>((const uint32_t*)hsum, g, (uint32_t*)C); break;
-    }
-    MVS_LAUNCH_CHECK(ctx, "vsum_kernel");
-    return MVS_OK;
+    return sgbm_cost_volume_batch_dev(ctx, g, 1, &l, &r, &C);
 }

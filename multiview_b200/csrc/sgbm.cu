@@ -39,7 +39,7 @@ int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, cons
     int16_t* raw = (F == 1 && raw16_tap) ? raw16_tap : (int16_t*)arena_get(ctx, "sgbm.raw", sizeof(int16_t) * (size_t)w * h);
     if (!raw) return MVS_ERR_NOMEM;
     stage_begin(ctx, "cost");
-    for (int f = 0; f < F && !rc; ++f) rc = sgbm_cost_volume_dev(ctx, g, l[f], r[f], C[f]);
+    rc = sgbm_cost_volume_batch_dev(ctx, g, F, l, r, C);
     stage_end(ctx, "cost");
     if (rc) return rc;
     stage_begin(ctx, "aggregate");

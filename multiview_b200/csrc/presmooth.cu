@@ -100,6 +100,108 @@ __global__ void blur_v_kernel(const uint16_t* __restrict__ src, int w, int h, Bl
     dst[(size_t)y * dstep + x] = (uint8_t)((s + (1u << 15)) >> 16);
 }
 
+// ---- packed fast paths: four pixels per thread, byte / halfword dot products (IDP.4A / IDP.2A) ----------------------
+// R = tap radius rounded up to 4k+3 (window 2R+2 taps, the last one zero).  Same integer sums as the scalar kernels.
+struct BlurPacked {
+    uint32_t t4[8];    // horizontal: taps lo'..lo'+2R+1 as bytes, four per word (lo' = 15 - R)
+    uint32_t t2[16];   // vertical: the same taps, two per word (low two bytes)
+};
+template <int R>
+__global__ void __launch_bounds__(128)
+blur_h4_kernel(const uint8_t* __restrict__ src, size_t sstep, int w, int h, BlurTaps t, BlurPacked pk, uint16_t* __restrict__ dst)
+{
+    constexpr int NT = (2 * R + 2) / 4;   // dot products per output
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y;
+    if (x0 >= w) return;
+    const uint8_t* row = src + (size_t)y * sstep;
+    uint16_t* out = dst + (size_t)y * w + x0;
+    if (x0 - R - 1 >= 0 && x0 + R + 5 <= w) {
+        // words from the aligned byte x0 - R - 1; the window of output q starts q + 1 bytes into them
+        const uint32_t* wp = (const uint32_t*)(row + x0 - R - 1);
+        uint32_t W[NT + 1];   // bytes x0 - R - 1 .. x0 + R + 4
+#pragma unroll
+        for (int n = 0; n <= NT; ++n) W[n] = __ldg(wp + n);
+        uint32_t s[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int n = 0; n < NT; ++n) {
+                const uint32_t v = q == 3 ? W[n + 1] : __funnelshift_r(W[n], W[n + 1], 8 * (q + 1));
+                s[q] = __dp4a(v, pk.t4[n], s[q]);
+            }
+        *(uint2*)out = make_uint2(s[0] | (s[1] << 16), s[2] | (s[3] << 16));
+    } else {
+        for (int q = 0; q < 4 && x0 + q < w; ++q) {
+            unsigned a = 0;
+            for (int j = t.lo; j <= t.hi; ++j) a += (unsigned)t.k[j] * row[reflect101(x0 + q + j - 15, w)];
+            out[q] = (uint16_t)a;
+        }
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(128)
+blur_v4_kernel(const uint16_t* __restrict__ src, int w, int h, BlurTaps t, BlurPacked pk, uint8_t* __restrict__ dst, size_t dstep)
+{
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y;
+    if (x0 >= w) return;
+    if (y - R >= 0 && y + R + 1 < h) {
+        const uint16_t* col = src + (size_t)(y - R) * w + x0;
+        uint32_t s[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int n = 0; n <= R; ++n) {  // rows y - R + 2n and y - R + 2n + 1 (the last one has a zero tap)
+            const uint2 a = __ldg((const uint2*)(col + (size_t)(2 * n) * w)), b = __ldg((const uint2*)(col + (size_t)(2 * n + 1) * w));
+            s[0] = __dp2a_lo(__byte_perm(a.x, b.x, 0x5410), pk.t2[n], s[0]);
+            s[1] = __dp2a_lo(__byte_perm(a.x, b.x, 0x7632), pk.t2[n], s[1]);
+            s[2] = __dp2a_lo(__byte_perm(a.y, b.y, 0x5410), pk.t2[n], s[2]);
+            s[3] = __dp2a_lo(__byte_perm(a.y, b.y, 0x7632), pk.t2[n], s[3]);
+        }
+        uint32_t o = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) o |= ((s[q] + (1u << 15)) >> 16) << (8 * q);
+        *(uint32_t*)(dst + (size_t)y * dstep + x0) = o;
+    } else {
+        for (int q = 0; q < 4; ++q) {
+            unsigned a = 0;
+            for (int i = t.lo; i <= t.hi; ++i) a += (unsigned)t.k[i] * src[(size_t)reflect101(y + i - 15, h) * w + x0 + q];
+            dst[(size_t)y * dstep + x0 + q] = (uint8_t)((a + (1u << 15)) >> 16);
+        }
+    }
+}
+
+template <int R>
+static void blur_packed_launch(cudaStream_t s, const uint8_t* src, int w, int h, const BlurTaps& t, uint16_t* tmp, uint8_t* dst,
+                               size_t dstep)
+{
+    BlurPacked pk;
+    memset(&pk, 0, sizeof(pk));
+    for (int i = 0; i < 2 * R + 1; ++i) {
+        const uint32_t k = (uint32_t)t.k[15 - R + i];
+        pk.t4[i / 4] |= k << (8 * (i % 4));
+        pk.t2[i / 2] |= k << (8 * (i % 2));
+    }
+    dim3 grid(cdiv(w, 512), h);
+    blur_h4_kernel<R><<<grid, 128, 0, s>>>(src, (size_t)w, w, h, t, pk, tmp);
+    blur_v4_kernel<R><<<grid, 128, 0, s>>>(tmp, w, h, t, pk, dst, dstep);
+}
+
+// one blur pass (horizontal then vertical): packed kernels when the rows are 4-byte aligned and every tap fits a byte
+static void blur_pass(cudaStream_t s, const uint8_t* src, int w, int h, const BlurTaps& t, uint16_t* tmp, uint8_t* dst, size_t dstep)
+{
+    bool packed = (w % 4) == 0 && (dstep % 4) == 0 && ((uintptr_t)src % 4) == 0 && ((uintptr_t)dst % 4) == 0 && ((uintptr_t)tmp % 8) == 0;
+    for (int i = t.lo; i <= t.hi; ++i) packed = packed && t.k[i] >= 0 && t.k[i] <= 255;
+    const int radius = 15 - t.lo;
+    if (packed && radius <= 3) blur_packed_launch<3>(s, src, w, h, t, tmp, dst, dstep);
+    else if (packed && radius <= 7) blur_packed_launch<7>(s, src, w, h, t, tmp, dst, dstep);
+    else if (packed && radius <= 11) blur_packed_launch<11>(s, src, w, h, t, tmp, dst, dstep);
+    else if (packed) blur_packed_launch<15>(s, src, w, h, t, tmp, dst, dstep);
+    else {
+        dim3 grid(cdiv(w, 128), h);
+        blur_h_kernel<<<grid, 128, 0, s>>>(src, (size_t)w, w, h, t, tmp);
+        blur_v_kernel<<<grid, 128, 0, s>>>(tmp, w, h, t, dst, dstep);
+    }
+}
+
 int presmooth_dev(mvs_ctx* ctx, const char* tag, const uint8_t* src, int channels, int w, int h, size_t step,
                   double sigma, uint8_t* dst, size_t dstep)
 {
@@ -121,10 +223,8 @@ int presmooth_dev(mvs_ctx* ctx, const char* tag, const uint8_t* src, int channel
     BlurTaps t;
     if (gauss_taps_q8(sigma, &t)) return mvs_fail(ctx, MVS_ERR_ARG, "presmooth: bad sigma");
     // pass 1: grey -> grey (through tmp); pass 2: grey -> dst
-    blur_h_kernel<<<grid, 128, 0, s>>>(grey, (size_t)w, w, h, t, tmp);
-    blur_v_kernel<<<grid, 128, 0, s>>>(tmp, w, h, t, grey, (size_t)w);
-    blur_h_kernel<<<grid, 128, 0, s>>>(grey, (size_t)w, w, h, t, tmp);
-    blur_v_kernel<<<grid, 128, 0, s>>>(tmp, w, h, t, dst, dstep);
+    blur_pass(s, grey, w, h, t, tmp, grey, (size_t)w);
+    blur_pass(s, grey, w, h, t, tmp, dst, dstep);
     MVS_LAUNCH_CHECK_N(ctx, "blur kernels", 4);
     return MVS_OK;
 }

@@ -70,10 +70,24 @@ __device__ __forceinline__ int cv_round_f(float v)
 }
 __device__ __forceinline__ int sat16_i(int v) { return max(-32768, min(32767, v)); }
 
+// d + a.lo16 * b.byte0 + a.hi16 * b.byte1 (signed weights, unsigned pixels) and the same with bytes 2, 3
+__device__ __forceinline__ int dp2a_lo_su(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 __global__ void __launch_bounds__(256)
 remap_cubic_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t sstep, const float* __restrict__ mapx,
                         const float* __restrict__ mapy, size_t mstep, int w, int h, const int16_t* __restrict__ tab,
-                        int b0, int b1, int b2, uint8_t* __restrict__ dst, size_t dstep)
+                        int b0, int b1, int b2, uint8_t* __restrict__ dst, size_t dstep, bool aligned4)
 {
     int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= w || y >= h) return;
@@ -91,6 +105,31 @@ remap_cubic_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t 
         return;
     }
     bool inside = X >= 0 && X + 3 < sw && Y >= 0 && Y + 3 < sh;
+    // fast path: the 12 bytes of a tap row come from four aligned words (the kernel is bound by L1 requests, not by
+    // arithmetic), the weighted sums are 16-bit x 8-bit dot products.  Not taken where the last word could reach
+    // past the end of the image buffer.
+    if (inside && aligned4 && (Y + 3 < sh - 1 || X + 4 < sw)) {
+        const uint8_t* p0 = src + (size_t)Y * sstep + (size_t)X * 3;
+        const int sh8 = ((int)(uintptr_t)p0 & 3) * 8;
+#pragma unroll
+        for (int k1 = 0; k1 < 4; ++k1) {
+            const uint32_t* a = (const uint32_t*)((uintptr_t)(p0 + (size_t)k1 * sstep) & ~(uintptr_t)3);
+            const uint32_t A0 = __ldg(a), A1 = __ldg(a + 1), A2 = __ldg(a + 2), A3 = __ldg(a + 3);
+            // w0 = B0 G0 R0 B1, w1 = G1 R1 B2 G2, w2 = R2 B3 G3 R3
+            const uint32_t w0 = __funnelshift_r(A0, A1, sh8), w1 = __funnelshift_r(A1, A2, sh8), w2 = __funnelshift_r(A2, A3, sh8);
+            const uint32_t wl = (uint32_t)wraw[k1 * 2], wh = (uint32_t)wraw[k1 * 2 + 1];  // taps (0,1) and (2,3) as s16 pairs
+            const uint32_t cb = __byte_perm(__byte_perm(w0, w1, 0x0630), w2, 0x5210);   // B0 B1 B2 B3
+            const uint32_t cg = __byte_perm(__byte_perm(w0, w1, 0x0741), w2, 0x6210);   // G0 G1 G2 G3
+            const uint32_t cr = __byte_perm(__byte_perm(w0, w1, 0x0052), w2, 0x7410);   // R0 R1 R2 R3
+            s0 = dp2a_hi_su(wh, cb, dp2a_lo_su(wl, cb, s0));
+            s1 = dp2a_hi_su(wh, cg, dp2a_lo_su(wl, cg, s1));
+            s2 = dp2a_hi_su(wh, cr, dp2a_lo_su(wl, cr, s2));
+        }
+        d[0] = (uint8_t)max(0, min(255, (s0 + (1 << 14)) >> 15));
+        d[1] = (uint8_t)max(0, min(255, (s1 + (1 << 14)) >> 15));
+        d[2] = (uint8_t)max(0, min(255, (s2 + (1 << 14)) >> 15));
+        return;
+    }
 #pragma unroll
     for (int k1 = 0; k1 < 4; ++k1) {
         int yy = Y + k1;
@@ -123,7 +162,8 @@ int remap_bgr8_dev(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sste
     if (rc) return rc;
     dim3 grid(cdiv(w, 32), cdiv(h, 8));
     remap_cubic_bgr8_kernel<<<grid, 256, 0, ctx->stream>>>(src, sw, sh, sstep, mapx, mapy, mstep, w, h,
-                                                           ctx->cubic_tab_dev, border[0], border[1], border[2], dst, dstep);
+                                                           ctx->cubic_tab_dev, border[0], border[1], border[2], dst, dstep,
+                                                           ((uintptr_t)src & 3) == 0);
     MVS_LAUNCH_CHECK(ctx, "remap_cubic_bgr8_kernel");
     return MVS_OK;
 }

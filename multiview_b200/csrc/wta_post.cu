@@ -7,7 +7,7 @@
 // disp2 (the right-view disparity) is a per-row argmin with "first writer in descending x wins ties":
 // realised as atomicMin on key = minS << 16 | (0xFFFF - x), from which the winning d follows as
 // x + minX1 - x2 - minD... (x2 = x + minX1 - d - minD), so no second array is needed.
-#define WTA_PPW 4  // pixels per warp: their loads are issued together (memory-level parallelism), then processed in turn
+#define WTA_PPW 8  // pixels per warp: their loads are issued together (memory-level parallelism), then processed in turn
 // ur_magic = ceil(2^32 / (100 - ur)) (0 when the divisor is 1): n / (100 - ur) == umulhi(n, ur_magic) for n < 2^25
 template <int NW>
 __global__ void __launch_bounds__(256)

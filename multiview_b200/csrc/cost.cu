@@ -118,11 +118,13 @@ __device__ __forceinline__ uint32_t bt_channel_cost(uint32_t w0, uint32_t w1, co
     const uint32_t v = __byte_perm(w0, 0u, 0x4140), vlo = __byte_perm(w0, 0u, 0x4342), vhi = __byte_perm(w1, 0u, 0x4140);
     uint32_t c0 = __vimax3_u16x2(l.x - vhi, vlo + l.y, COST_K2);
     uint32_t c1 = __vimax3_u16x2(v + l.z, l.w - v, COST_K2);
-    return __vminu2(c0, c1) - COST_K2;
+    return __vminu2(c0, c1);   // cost + K per half
 }
 __device__ __forceinline__ uint32_t bt_pair_cost(const uint4& r, const uint4& l0, const uint4& l1)
 {
-    return bt_channel_cost(r.x, r.y, l0) + ((bt_channel_cost(r.z, r.w, l1) >> 2) & 0x3fff3fffu);
+    // cost(channel 0) + cost(channel 1) / 4 per half; K is a multiple of 4, so ((c + K) >> 2) = (c >> 2) + K / 4 and
+    // both biases come off in one subtraction
+    return bt_channel_cost(r.x, r.y, l0) + ((bt_channel_cost(r.z, r.w, l1) >> 2) & 0x3fff3fffu) - (COST_K2 + (COST_K2 >> 2));
 }
 
 template <int WIN, int NW>
@@ -186,6 +188,21 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
     uint32_t* out = hsum + ((ptrdiff_t)y * g.W1 + (xs - SW)) * HALF + t;   // output column of step 0 (never stored when negative)
 #pragma unroll 1
     for (int kb = 0; kb < NS; kb += T::BODY) {
+        if (kb >= T::BODY && kb + T::BODY <= nvalid) {
+            // interior body: every step is inside the image and produces an output (nvalid <= nout)
+#pragma unroll
+            for (int i = 0; i < T::BODY; ++i) {
+                const uint4* r = pR + (i & 1) * KW - ((i + 1) >> 1);
+                pix = bt_pair_cost(r[0], pL[2 * i], pL[2 * i + 1]) & padmask;
+                hs = hs + pix - ring[i % WIN];
+                ring[i % WIN] = pix;
+                out[(size_t)i * HALF] = hs;
+            }
+            pR -= T::BODY / 2;
+            pL += 2 * T::BODY;
+            out += (size_t)T::BODY * HALF;
+            continue;
+        }
 #pragma unroll
         for (int i = 0; i < T::BODY; ++i) {
             const int k = kb + i;

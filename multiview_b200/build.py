@@ -24,7 +24,8 @@ UNITS = {
     "presmooth.cu": [],
     "cost.cu": [],
     "aggregate.cu": [],
-    "aggregate_wave.cu": ([f"-DWAVE_R={os.environ['MVS_WAVE_R']}"] if os.environ.get("MVS_WAVE_R") else []),
+    # tuning experiments: MVS_WAVE_FLAGS="-DWAVE_R=15 -DWAVE_D12=7" python -m multiview_b200.build --force
+    "aggregate_wave.cu": os.environ.get("MVS_WAVE_FLAGS", "").split(),
     "wta_post.cu": [],
     "sgbm.cu": [],
     "frame.cu": [],

@@ -16,7 +16,7 @@
 //     than eight pixels apart, so a parity is never ambiguous).  arrive has release and try_wait acquire semantics
 //     at CTA scope, so no memory fence is issued and a waiting warp is suspended instead of burning issue slots.
 //     There is no CTA-wide barrier inside a band, and the rings are two slots deeper than lock-step needs, so a
-//     warp that stalls does not stall the other fifteen;
+//     warp that stalls does not stall the others at once;
 //   * image borders need no branches: the slots "x = -1" and "x = W1" are filled with zeros (Lr = 0, minLr = 0
 //     outside the image, as the reference initialises its Lr buffers);
 //   * C (and S in the backward sweep) stream through a per-warp cp.async pipeline three pixels ahead;
@@ -30,14 +30,14 @@
 
 #define SENT2 0x7FFF7FFFu
 #ifndef WAVE_R
-#define WAVE_R 16            // rows (compute warps) per band
+#define WAVE_R 15            // rows (compute warps) per band: with the helper 16 warps, four per scheduler
 #endif
 #define WAVE_THREADS ((WAVE_R + 1) * 32)
 #ifndef WAVE_PUBLISH
 #define WAVE_PUBLISH 8       // inter-band progress is published every this many pixels
 #endif
 #ifndef WAVE_D12
-#define WAVE_D12 6           // ring depth for L1 / L2 (lock-step needs 4 / 3)
+#define WAVE_D12 7           // ring depth for L1 / L2 (lock-step needs 4 / 3); measured: 15 rows x 7/7/4 beats 16 x 6/6/4
 #endif
 #ifndef WAVE_D3
 #define WAVE_D3 4            // ring depth for L3 (lock-step needs 2)

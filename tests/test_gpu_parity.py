@@ -45,9 +45,10 @@ def test_remap_cubic_bit_exact(ctx):
 
 def test_presmooth_bit_exact(ctx):
     rng = np.random.default_rng(8)
-    for (w, h) in [(131, 97), (20, 12), (640, 48)]:
+    # widths that are / are not multiples of 4 (packed and scalar kernels), every tap-radius class of the packed kernels
+    for (w, h) in [(131, 97), (20, 12), (640, 48), (64, 40), (36, 36)]:
         img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
-        for sigma in (2.15, 1.0, 5.0):
+        for sigma in (2.15, 1.0, 5.0, 3.2, 0.4, 0.8):
             assert np.array_equal(api.presmooth(img, sigma, ctx=ctx), oracle.presmooth(img, sigma))
         assert np.array_equal(api.presmooth(img[..., 0].copy(), 2.15, ctx=ctx), oracle.presmooth(img[..., 0].copy(), 2.15))
         assert np.array_equal(api.presmooth(img, 0.0, ctx=ctx), oracle.bgr2gray(img))
@@ -69,6 +70,7 @@ def test_sgbm_volumes_and_disparity(ctx, mode, W, H, D):
 
 
 @pytest.mark.parametrize("params", [
+    dict(block=1, p1=4, p2=16, ur=0, d12=1, sw=0, sr=0),
     dict(block=3, p1=8, p2=32, ur=0, d12=1, sw=0, sr=0),
     dict(block=5, p1=8, p2=32, ur=10, d12=2, sw=0, sr=0),
     dict(block=9, p1=22, p2=1000, ur=3, d12=596, sw=0, sr=0),

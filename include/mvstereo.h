@@ -36,7 +36,7 @@ typedef enum {
 } mvs_status;
 
 /* cv::INTER_* values accepted by mvs_remap_bgr8 (calc_rectified.hpp:17-22). */
-enum { MVS_INTER_NEAREST = 0, MVS_INTER_LINEAR = 1, MVS_INTER_CUBIC = 2 };
+enum { MVS_INTER_NEAREST = 0, MVS_INTER_LINEAR = 1, MVS_INTER_CUBIC = 2, MVS_INTER_LANCZOS4 = 4 };
 
 /* cv::StereoSGBM modes (stereosgbm_disp.cpp:55-80): 0 = 5-path, 1 = 8-path full DP, 3 = 4-path HH4. */
 enum { MVS_MODE_SGBM = 0, MVS_MODE_HH = 1, MVS_MODE_HH4 = 3 };
@@ -56,8 +56,9 @@ long long mvs_launch_count(const mvs_ctx* ctx); /* kernels launched through this
 /* -- a1: rectification -----------------------------------------------------------------------------
  * Replaces cv::remap(in, rectified, mapx, mapy, interp, BORDER_CONSTANT, Scalar(255,255,255)) in
  * calc_rectified::Task::execute, pipeline/nodes/calc_rectified.cpp:109-115.
- * src: BGR 8UC3 sw x sh; mapx/mapy: CV_32FC1 w x h; dst: BGR 8UC3 w x h.  Bit-exact for INTER_CUBIC (the
- * reference default, calc_rectified.hpp:34); other interpolation modes return MVS_ERR_UNSUPPORTED. */
+ * src: BGR 8UC3 sw x sh; mapx/mapy: CV_32FC1 w x h; dst: BGR 8UC3 w x h.  Bit-exact with OpenCV's fixed-point path for
+ * the four modes the node offers (calc_rectified.hpp:17-22): INTER_NEAREST, INTER_LINEAR, INTER_CUBIC (the default,
+ * calc_rectified.hpp:34; the tuned kernel) and INTER_LANCZOS4; any other value returns MVS_ERR_UNSUPPORTED. */
 int mvs_remap_bgr8(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
                    const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border_bgr[3],
                    uint8_t* dst, size_t dstep);

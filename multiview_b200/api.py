@@ -26,7 +26,7 @@ import numpy as np
 from . import _lib
 from ._lib import Bcam, FrameDesc, FrameResult, HistParams, MvsError, SgbmParams
 
-INTER_NEAREST, INTER_LINEAR, INTER_CUBIC = 0, 1, 2
+INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4 = 0, 1, 2, 4
 MODE_SGBM, MODE_HH, MODE_SGBM_3WAY, MODE_HH4 = 0, 1, 2, 3
 WGT_NONE, WGT_NORM, WGT_QUADRANCE = 0, 1, 2
 

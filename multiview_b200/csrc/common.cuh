@@ -48,6 +48,7 @@ struct mvs_ctx {
     std::map<std::string, StageTimer> timers;
     FrameSlot slots[MVS_MAX_SLOTS];
     int16_t* cubic_tab_dev = nullptr;  // 32*32*16 Q15 bicubic weights
+    int16_t* interp_tab_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // by cv::INTER_* value: 32*32*K*K Q15 weights
     int sm_count = 148;
     bool wave_err_cleared = false;
     long long launches = 0;  // kernels launched through this context (bench.py reports it)

@@ -51,6 +51,77 @@ static void build_cubic_tab(int16_t* tab)
         }
 }
 
+// The other fixed-point modes of cv::remap: K x K taps, K = 2 (LINEAR) / 8 (LANCZOS4), same table construction
+// (initInterTab2D).  The correction window {K/2, K/2+1}^2 reaches into the next entry for K = 2, which is still zero
+// while OpenCV fills the table in order: the table is built in a zero-initialised flat array in the same order.
+static int interp_ksize(int interp) { return interp == MVS_INTER_LINEAR ? 2 : interp == MVS_INTER_CUBIC ? 4 : interp == MVS_INTER_LANCZOS4 ? 8 : 0; }
+static void interp_coeffs(int interp, float x, float* c)
+{
+    if (interp == MVS_INTER_LINEAR) { c[0] = 1.f - x; c[1] = x; return; }
+    static const double s45 = 0.70710678118654752440084436210485;
+    static const double cs[8][2] = {{1, 0}, {-s45, -s45}, {0, 1}, {s45, -s45}, {-1, 0}, {s45, s45}, {0, -1}, {-s45, s45}};
+    if (x < 1.1920928955078125e-07f) { for (int i = 0; i < 8; ++i) c[i] = 0; c[3] = 1; return; }
+    float sum = 0;
+    double y0 = -(x + 3) * 3.1415926535897932384626433832795 * 0.25, s0 = sin(y0), c0 = cos(y0);
+    for (int i = 0; i < 8; ++i) {
+        double y = -(x + 3 - i) * 3.1415926535897932384626433832795 * 0.25;
+        c[i] = (float)((cs[i][0] * s0 + cs[i][1] * c0) / (y * y));
+        sum += c[i];
+    }
+    sum = 1.f / sum;
+    for (int i = 0; i < 8; ++i) c[i] *= sum;
+}
+static void build_interp_tab(int interp, std::vector<int16_t>& flat)
+{
+    const int K = interp_ksize(interp);
+    float c[32][8];
+    for (int i = 0; i < 32; ++i) interp_coeffs(interp, (float)i * (1.0f / 32.0f), c[i]);
+    flat.assign((size_t)1024 * K * K + 4 * K * K, 0);
+    for (int fy = 0; fy < 32; ++fy)
+        for (int fx = 0; fx < 32; ++fx) {
+            int16_t* w = flat.data() + (size_t)(fy * 32 + fx) * K * K;
+            int isum = 0;
+            for (int k1 = 0; k1 < K; ++k1)
+                for (int k2 = 0; k2 < K; ++k2) {
+                    float v = c[fy][k1] * c[fx][k2];
+                    long q = lrintf(v * 32768.0f);
+                    q = q < -32768 ? -32768 : (q > 32767 ? 32767 : q);
+                    w[k1 * K + k2] = (int16_t)q;
+                    isum += (int)q;
+                }
+            if (isum != 32768) {
+                const int diff = isum - 32768, k0 = K / 2;
+                int M = k0 * K + k0, m = k0 * K + k0;
+                for (int k1 = k0; k1 < k0 + 2; ++k1)
+                    for (int k2 = k0; k2 < k0 + 2; ++k2) {
+                        int i = k1 * K + k2;
+                        if (w[i] < w[m])
+                            m = i;
+                        else if (w[i] > w[M])
+                            M = i;
+                    }
+                if (diff < 0)
+                    w[M] = (int16_t)(w[M] - diff);
+                else
+                    w[m] = (int16_t)(w[m] - diff);
+            }
+        }
+}
+static int ensure_interp_tab(mvs_ctx* ctx, int interp)
+{
+    if (ctx->interp_tab_dev[interp]) return MVS_OK;
+    const int K = interp_ksize(interp);
+    char nm[32];
+    snprintf(nm, sizeof(nm), "remap.tab.%d", interp);
+    MVS_ARENA(ctx, int16_t, tab, nm, (size_t)1024 * K * K);
+    std::vector<int16_t> host;
+    build_interp_tab(interp, host);
+    MVS_CUDA(ctx, cudaMemcpyAsync(tab, host.data(), (size_t)1024 * K * K * sizeof(int16_t), cudaMemcpyHostToDevice, ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host vector goes out of scope
+    ctx->interp_tab_dev[interp] = tab;
+    return MVS_OK;
+}
+
 static int ensure_cubic_tab(mvs_ctx* ctx)
 {
     if (ctx->cubic_tab_dev) return MVS_OK;
@@ -110,10 +181,11 @@ remap_cubic_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t 
     // past the end of the image buffer.
     if (inside && aligned4 && (Y + 3 < sh - 1 || X + 4 < sw)) {
         const uint8_t* p0 = src + (size_t)Y * sstep + (size_t)X * 3;
-        const int sh8 = ((int)(uintptr_t)p0 & 3) * 8;
 #pragma unroll
         for (int k1 = 0; k1 < 4; ++k1) {
-            const uint32_t* a = (const uint32_t*)((uintptr_t)(p0 + (size_t)k1 * sstep) & ~(uintptr_t)3);
+            const uintptr_t addr = (uintptr_t)(p0 + (size_t)k1 * sstep);
+            const int sh8 = ((int)addr & 3) * 8;   // per row: the row pitch need not be a multiple of four
+            const uint32_t* a = (const uint32_t*)(addr & ~(uintptr_t)3);
             const uint32_t A0 = __ldg(a), A1 = __ldg(a + 1), A2 = __ldg(a + 2), A3 = __ldg(a + 3);
             // w0 = B0 G0 R0 B1, w1 = G1 R1 B2 G2, w2 = R2 B3 G3 R3
             const uint32_t w0 = __funnelshift_r(A0, A1, sh8), w1 = __funnelshift_r(A1, A2, sh8), w2 = __funnelshift_r(A2, A3, sh8);
@@ -152,15 +224,94 @@ remap_cubic_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t 
     d[2] = (uint8_t)max(0, min(255, (s2 + (1 << 14)) >> 15));
 }
 
+// INTER_NEAREST: cvRound + saturate_cast<short> of the coordinates, copy or border
+__global__ void __launch_bounds__(256)
+remap_nearest_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t sstep, const float* __restrict__ mapx,
+                          const float* __restrict__ mapy, size_t mstep, int w, int h, int b0, int b1, int b2,
+                          uint8_t* __restrict__ dst, size_t dstep)
+{
+    int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= w || y >= h) return;
+    float mx = *(const float*)((const char*)mapx + (size_t)y * mstep + (size_t)x * 4);
+    float my = *(const float*)((const char*)mapy + (size_t)y * mstep + (size_t)x * 4);
+    int X = sat16_i(cv_round_f(mx)), Y = sat16_i(cv_round_f(my));
+    uint8_t* d = dst + (size_t)y * dstep + (size_t)x * 3;
+    if (X >= 0 && X < sw && Y >= 0 && Y < sh) {
+        const uint8_t* p = src + (size_t)Y * sstep + (size_t)X * 3;
+        d[0] = p[0]; d[1] = p[1]; d[2] = p[2];
+    } else {
+        d[0] = (uint8_t)b0; d[1] = (uint8_t)b1; d[2] = (uint8_t)b2;
+    }
+}
+
+// INTER_LINEAR (K = 2) and INTER_LANCZOS4 (K = 8): K x K Q15 taps, one thread per output pixel
+template <int K>
+__global__ void __launch_bounds__(256)
+remap_taps_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t sstep, const float* __restrict__ mapx,
+                       const float* __restrict__ mapy, size_t mstep, int w, int h, const int16_t* __restrict__ tab,
+                       int b0, int b1, int b2, uint8_t* __restrict__ dst, size_t dstep)
+{
+    int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= w || y >= h) return;
+    float mx = *(const float*)((const char*)mapx + (size_t)y * mstep + (size_t)x * 4);
+    float my = *(const float*)((const char*)mapy + (size_t)y * mstep + (size_t)x * 4);
+    int sx = cv_round_f(mx * 32.0f), sy = cv_round_f(my * 32.0f);
+    int X = sat16_i(sx >> 5) - (K / 2 - 1), Y = sat16_i(sy >> 5) - (K / 2 - 1);
+    const int16_t* wt = tab + (size_t)(((sy & 31) << 5) + (sx & 31)) * (K * K);
+    uint8_t* d = dst + (size_t)y * dstep + (size_t)x * 3;
+    if (X >= sw || X + K <= 0 || Y >= sh || Y + K <= 0) {
+        d[0] = (uint8_t)b0; d[1] = (uint8_t)b1; d[2] = (uint8_t)b2;
+        return;
+    }
+    const bool inside = X >= 0 && X + K - 1 < sw && Y >= 0 && Y + K - 1 < sh;
+    int s0 = 0, s1 = 0, s2 = 0;
+#pragma unroll
+    for (int k1 = 0; k1 < K; ++k1) {
+        const int yy = Y + k1;
+        const uint8_t* row = src + (size_t)yy * sstep;
+#pragma unroll
+        for (int k2 = 0; k2 < K; ++k2) {
+            const int wv = __ldg(wt + k1 * K + k2), xx = X + k2;
+            int v0 = b0, v1 = b1, v2 = b2;
+            if (inside || (yy >= 0 && yy < sh && xx >= 0 && xx < sw)) {
+                const uint8_t* p = row + (size_t)xx * 3;
+                v0 = __ldg(p); v1 = __ldg(p + 1); v2 = __ldg(p + 2);
+            }
+            s0 += wv * v0; s1 += wv * v1; s2 += wv * v2;
+        }
+    }
+    d[0] = (uint8_t)max(0, min(255, (s0 + (1 << 14)) >> 15));
+    d[1] = (uint8_t)max(0, min(255, (s1 + (1 << 14)) >> 15));
+    d[2] = (uint8_t)max(0, min(255, (s2 + (1 << 14)) >> 15));
+}
+
 int remap_bgr8_dev(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
                    const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border[3], uint8_t* dst,
                    size_t dstep)
 {
+    dim3 grid(cdiv(w, 32), cdiv(h, 8));
+    if (interp == MVS_INTER_NEAREST) {
+        remap_nearest_bgr8_kernel<<<grid, 256, 0, ctx->stream>>>(src, sw, sh, sstep, mapx, mapy, mstep, w, h, border[0], border[1],
+                                                                 border[2], dst, dstep);
+        MVS_LAUNCH_CHECK(ctx, "remap_nearest_bgr8_kernel");
+        return MVS_OK;
+    }
+    if (interp == MVS_INTER_LINEAR || interp == MVS_INTER_LANCZOS4) {
+        int rc = ensure_interp_tab(ctx, interp);
+        if (rc) return rc;
+        if (interp == MVS_INTER_LINEAR)
+            remap_taps_bgr8_kernel<2><<<grid, 256, 0, ctx->stream>>>(src, sw, sh, sstep, mapx, mapy, mstep, w, h, ctx->interp_tab_dev[interp],
+                                                                     border[0], border[1], border[2], dst, dstep);
+        else
+            remap_taps_bgr8_kernel<8><<<grid, 256, 0, ctx->stream>>>(src, sw, sh, sstep, mapx, mapy, mstep, w, h, ctx->interp_tab_dev[interp],
+                                                                     border[0], border[1], border[2], dst, dstep);
+        MVS_LAUNCH_CHECK(ctx, "remap_taps_bgr8_kernel");
+        return MVS_OK;
+    }
     if (interp != MVS_INTER_CUBIC)
-        return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "remap: only INTER_CUBIC (the reference default) is implemented");
+        return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "remap: interpolation %d (cv::INTER_NEAREST, LINEAR, CUBIC and LANCZOS4 are implemented)", interp);
     int rc = ensure_cubic_tab(ctx);
     if (rc) return rc;
-    dim3 grid(cdiv(w, 32), cdiv(h, 8));
     remap_cubic_bgr8_kernel<<<grid, 256, 0, ctx->stream>>>(src, sw, sh, sstep, mapx, mapy, mstep, w, h,
                                                            ctx->cubic_tab_dev, border[0], border[1], border[2], dst, dstep,
                                                            ((uintptr_t)src & 3) == 0);

@@ -136,6 +136,21 @@ def remap_cubic_bgr8(src, mapx, mapy, border=(255, 255, 255)):
     return dst
 
 
+def remap_bgr8(src, mapx, mapy, interp=2, border=(255, 255, 255)):
+    """cv::remap with interp = cv::INTER_NEAREST 0 | LINEAR 1 | CUBIC 2 | LANCZOS4 4 (calc_rectified.hpp:17-22)."""
+    src = np.ascontiguousarray(src, np.uint8)
+    mapx = np.ascontiguousarray(mapx, np.float32)
+    mapy = np.ascontiguousarray(mapy, np.float32)
+    sh, sw, _ = src.shape
+    h, w = mapx.shape
+    dst = np.empty((h, w, 3), np.uint8)
+    b = (ctypes.c_uint8 * 3)(*border)
+    rc = lib().orc_remap_bgr8(int(interp), _p(src), sw, sh, _sz(sw * 3), _p(mapx), _p(mapy), _sz(w * 4), w, h, b, _p(dst), _sz(w * 3))
+    if rc:
+        raise ValueError(f"orc_remap_bgr8: unsupported interpolation {interp}")
+    return dst
+
+
 def bgr2gray(src):
     src = np.ascontiguousarray(src, np.uint8)
     h, w, _ = src.shape

@@ -24,6 +24,11 @@ def remap_cubic_bgr8(src, mapx, mapy, border=(255, 255, 255)):
     return cv2.remap(src, mapx, mapy, cv2.INTER_CUBIC, borderMode=cv2.BORDER_CONSTANT, borderValue=tuple(border))
 
 
+def remap_bgr8(src, mapx, mapy, interp, border=(255, 255, 255)):
+    cv2 = _cv2()
+    return cv2.remap(src, mapx, mapy, int(interp), borderMode=cv2.BORDER_CONSTANT, borderValue=tuple(border))
+
+
 def presmooth(img, sigma=2.15):
     cv2 = _cv2()
     g = cv2.cvtColor(img, cv2.COLOR_BGR2GRAY) if img.ndim == 3 else img

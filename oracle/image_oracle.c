@@ -89,6 +89,132 @@ void orc_remap_cubic_bgr8(const uint8_t* src, int sw, int sh, size_t sstep, cons
     free(tab);
 }
 
+/* ---- the other interpolation modes of cv::remap (calc_rectified.hpp:17-22: NEAREST, LINEAR, CUBIC, LANCZOS4) ----------
+ * OpenCV builds one table of K x K Q15 weights per (fy, fx) in 1/32 pixel steps (initInterTab2D): K = 2 / 4 / 8 for
+ * LINEAR / CUBIC / LANCZOS4.  Entries that do not sum to 32768 are corrected on one of the four taps k1, k2 in
+ * {K/2, K/2 + 1}; for K = 2 that window reaches into the next table entry, which is still zero when OpenCV fills the
+ * table in order -- reproduced here by filling a zero-initialised flat array in the same order. */
+static void orc_interp_coeffs(int interp, float x, float* c)
+{
+    if (interp == 1) { c[0] = 1.f - x; c[1] = x; return; }
+    if (interp == 2) {
+        const float A = -0.75f;
+        c[0] = ((A * (x + 1) - 5 * A) * (x + 1) + 8 * A) * (x + 1) - 4 * A;
+        c[1] = ((A + 2) * x - (A + 3)) * x * x + 1;
+        c[2] = ((A + 2) * (1 - x) - (A + 3)) * (1 - x) * (1 - x) + 1;
+        c[3] = 1.f - c[0] - c[1] - c[2];
+        return;
+    }
+    /* interpolateLanczos4 */
+    static const double s45 = 0.70710678118654752440084436210485;
+    static const double cs[8][2] = {{1, 0}, {-s45, -s45}, {0, 1}, {s45, -s45}, {-1, 0}, {s45, s45}, {0, -1}, {-s45, s45}};
+    if (x < 1.1920928955078125e-07f) { for (int i = 0; i < 8; ++i) c[i] = 0; c[3] = 1; return; }
+    float sum = 0;
+    double y0 = -(x + 3) * 3.1415926535897932384626433832795 * 0.25, s0 = sin(y0), c0 = cos(y0);
+    for (int i = 0; i < 8; ++i) {
+        double y = -(x + 3 - i) * 3.1415926535897932384626433832795 * 0.25;
+        c[i] = (float)((cs[i][0] * s0 + cs[i][1] * c0) / (y * y));
+        sum += c[i];
+    }
+    sum = 1.f / sum;
+    for (int i = 0; i < 8; ++i) c[i] *= sum;
+}
+
+int orc_interp_ksize(int interp) { return interp == 1 ? 2 : interp == 2 ? 4 : interp == 4 ? 8 : 0; }
+
+/* tab[(fy*32+fx)*K*K + k1*K + k2]; tab must hold 1024*K*K entries */
+int orc_interp_tab(int interp, int16_t* tab)
+{
+    const int K = orc_interp_ksize(interp);
+    if (!K) return -1;
+    float c[32][8];
+    for (int i = 0; i < 32; ++i) orc_interp_coeffs(interp, (float)i * (1.0f / 32.0f), c[i]);
+    const size_t n = (size_t)1024 * K * K;
+    int16_t* flat = (int16_t*)calloc(n + 4 * K * K, sizeof(int16_t));
+    if (!flat) return -2;
+    for (int fy = 0; fy < 32; ++fy)
+        for (int fx = 0; fx < 32; ++fx) {
+            int16_t* w = flat + (size_t)(fy * 32 + fx) * K * K;
+            int isum = 0;
+            for (int k1 = 0; k1 < K; ++k1)
+                for (int k2 = 0; k2 < K; ++k2) {
+                    float v = c[fy][k1] * c[fx][k2];
+                    int q = sat16i((int)lrintf(v * 32768.0f));
+                    w[k1 * K + k2] = (int16_t)q;
+                    isum += q;
+                }
+            if (isum != 32768) {
+                const int diff = isum - 32768, k0 = K / 2;
+                int M = k0 * K + k0, m = k0 * K + k0;
+                for (int k1 = k0; k1 < k0 + 2; ++k1)
+                    for (int k2 = k0; k2 < k0 + 2; ++k2) {
+                        int i = k1 * K + k2;
+                        if (w[i] < w[m])
+                            m = i;
+                        else if (w[i] > w[M])
+                            M = i;
+                    }
+                if (diff < 0)
+                    w[M] = (int16_t)(w[M] - diff);
+                else
+                    w[m] = (int16_t)(w[m] - diff);
+            }
+        }
+    memcpy(tab, flat, n * sizeof(int16_t));
+    free(flat);
+    return 0;
+}
+
+/* cv::remap, CV_32FC1 maps, 8UC3, BORDER_CONSTANT(border); interp = cv::INTER_NEAREST 0 | LINEAR 1 | CUBIC 2 | LANCZOS4 4 */
+int orc_remap_bgr8(int interp, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx, const float* mapy,
+                   size_t mstep, int w, int h, const uint8_t border[3], uint8_t* dst, size_t dstep)
+{
+    if (interp == 0) {
+        for (int y = 0; y < h; ++y) {
+            const float* mx = (const float*)((const char*)mapx + (size_t)y * mstep);
+            const float* my = (const float*)((const char*)mapy + (size_t)y * mstep);
+            uint8_t* d = dst + (size_t)y * dstep;
+            for (int x = 0; x < w; ++x) {
+                /* cvRound + saturate_cast<short>; NaN / out of range give INT_MIN -> -32768 */
+                int X = sat16i((fabsf(mx[x]) < 2147483648.0f) ? (int)lrintf(mx[x]) : (int)0x80000000);
+                int Y = sat16i((fabsf(my[x]) < 2147483648.0f) ? (int)lrintf(my[x]) : (int)0x80000000);
+                const int in = X >= 0 && X < sw && Y >= 0 && Y < sh;
+                for (int c = 0; c < 3; ++c) d[x * 3 + c] = in ? src[(size_t)Y * sstep + (size_t)X * 3 + c] : border[c];
+            }
+        }
+        return 0;
+    }
+    const int K = orc_interp_ksize(interp);
+    if (!K) return -1;
+    int16_t* tab = (int16_t*)malloc(sizeof(int16_t) * 1024 * K * K);
+    if (!tab || orc_interp_tab(interp, tab)) { free(tab); return -2; }
+    for (int y = 0; y < h; ++y) {
+        const float* mx = (const float*)((const char*)mapx + (size_t)y * mstep);
+        const float* my = (const float*)((const char*)mapy + (size_t)y * mstep);
+        uint8_t* d = dst + (size_t)y * dstep;
+        for (int x = 0; x < w; ++x) {
+            float fx = mx[x] * 32.0f, fy = my[x] * 32.0f;
+            int sx = (fabsf(fx) < 2147483648.0f) ? (int)lrintf(fx) : (int)0x80000000;
+            int sy = (fabsf(fy) < 2147483648.0f) ? (int)lrintf(fy) : (int)0x80000000;
+            int X = sat16i(sx >> 5) - (K / 2 - 1), Y = sat16i(sy >> 5) - (K / 2 - 1);
+            const int16_t* wt = tab + (size_t)((sy & 31) * 32 + (sx & 31)) * K * K;
+            for (int c = 0; c < 3; ++c) {
+                int sum = 0;
+                for (int k1 = 0; k1 < K; ++k1)
+                    for (int k2 = 0; k2 < K; ++k2) {
+                        int yy = Y + k1, xx = X + k2;
+                        int v = (yy >= 0 && yy < sh && xx >= 0 && xx < sw) ? src[(size_t)yy * sstep + (size_t)xx * 3 + c]
+                                                                          : border[c];
+                        sum += wt[k1 * K + k2] * v;
+                    }
+                d[x * 3 + c] = (uint8_t)iclamp((sum + (1 << 14)) >> 15, 0, 255);
+            }
+        }
+    }
+    free(tab);
+    return 0;
+}
+
 /* A.6: cvtColor BGR2GRAY 8U */
 void orc_bgr2gray(const uint8_t* src, size_t sstep, int w, int h, uint8_t* dst, size_t dstep)
 {

@@ -43,6 +43,23 @@ def test_remap_cubic_bit_exact(ctx):
         assert np.array_equal(got, want), f"remap mismatch {(got != want).sum()} px"
 
 
+@pytest.mark.parametrize("interp", [api.INTER_NEAREST, api.INTER_LINEAR, api.INTER_CUBIC, api.INTER_LANCZOS4])
+def test_remap_interpolation_modes_bit_exact(ctx, interp):
+    """calc_rectified.hpp:17-22: every interpolation mode of the node, against the cv2-pinned oracle."""
+    rng = np.random.default_rng(70 + interp)
+    for (sw, sh, w, h) in [(80, 60, 70, 50), (33, 21, 64, 40), (200, 150, 160, 120)]:
+        src = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+        mx = (rng.random((h, w)) * (sw + 12) - 6).astype(np.float32)
+        my = (rng.random((h, w)) * (sh + 12) - 6).astype(np.float32)
+        mx[0, 0], my[0, 1], mx[1, 1], my[2, 2] = 1e9, -1e9, np.nan, 3e4
+        mx[3, :8] = np.arange(8, dtype=np.float32) * 0.5
+        got = api.calc_rectified(src, mx, my, interp, ctx=ctx)
+        want = oracle.remap_bgr8(src, mx, my, interp)
+        assert np.array_equal(got, want), f"interp {interp}: {(got != want).any(axis=2).sum()} px differ"
+    with pytest.raises(api.MvsError):
+        api.calc_rectified(src, mx, my, 3, ctx=ctx)  # INTER_AREA is not a remap mode
+
+
 def test_presmooth_bit_exact(ctx):
     rng = np.random.default_rng(8)
     # widths that are / are not multiples of 4 (packed and scalar kernels), every tap-radius class of the packed kernels

@@ -56,3 +56,17 @@ def test_hist_post_close_to_cv2():
         a, b = oracle.hist_post(h, sigma, mn, mx), cv2ref.hist_post(h, sigma, mn, mx)
         assert np.allclose(a, b, rtol=1e-6, atol=1e-4), np.abs(a - b).max()
     assert np.array_equal(oracle.hist_post(h, 0.0, 5.0, 700.0), cv2ref.hist_post(h, 0.0, 5.0, 700.0))
+
+
+@pytest.mark.parametrize("interp", [0, 1, 2, 4])
+def test_remap_all_interpolation_modes_match_cv2(interp):
+    """calc_rectified.hpp:17-22: NEAREST / LINEAR / CUBIC / LANCZOS4, incl. border crossings and NaN / huge coordinates."""
+    rng = np.random.default_rng(40 + interp)
+    for (sw, sh, w, h) in [(80, 60, 70, 50), (33, 21, 64, 40)]:
+        src = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+        mx = (rng.random((h, w)) * (sw + 12) - 6).astype(np.float32)
+        my = (rng.random((h, w)) * (sh + 12) - 6).astype(np.float32)
+        mx[0, 0], my[0, 1], mx[1, 1], my[2, 2] = 1e9, -1e9, np.nan, 3e4
+        mx[3, :8] = np.arange(8, dtype=np.float32) * 0.5  # exact halves: round-half-even
+        a, b = oracle.remap_bgr8(src, mx, my, interp), cv2ref.remap_bgr8(src, mx, my, interp)
+        assert np.array_equal(a, b), f"interp {interp}: {(a != b).any(axis=2).sum()} px differ"

@@ -1,6 +1,8 @@
 """GPU parity tests: every stage of the CUDA path, called through the C ABI, against the CPU oracle.
 
 Bit-exact for integer/byte/index results; point coordinates within 1e-4 relative (north_star)."""
+import ctypes
+
 import numpy as np
 import pytest
 
@@ -264,3 +266,30 @@ def test_disp_map_update_merge(ctx):
     want = oracle.disp_merge_ref(disp, ref, labels, cut)
     assert np.array_equal(got, want, equal_nan=True)
     assert (got != disp).sum() > 1000 and np.array_equal(got[labels < 0], disp[labels < 0], equal_nan=True)
+
+
+def test_sgbm_seeded_random_configurations(ctx):
+    """Seeded sweep over sizes, disparity ranges, block sizes, penalties and modes inside the supported domain
+    (mvs_sgbm_check): the whole SGBM chain against the cv2-pinned oracle, bit for bit."""
+    rng = np.random.default_rng(2026)
+    done = 0
+    for _ in range(60):
+        D = int(rng.choice([16, 32, 48, 64, 80, 96, 128, 160, 208, 256]))
+        minD = int(rng.integers(0, 5))
+        W = D + minD + int(rng.integers(8, 260))
+        H = int(rng.integers(1, 72))
+        block = int(rng.choice([1, 3, 5, 7, 9, 11, 13]))
+        cap = int(rng.choice([15, 31, 54, 63]))
+        p1 = int(rng.integers(0, 60))
+        p2 = p1 + 1 + int(rng.integers(0, 3000))
+        mode = int(rng.choice([0, 1, 3]))
+        sp = _sp(D, mode, block=block, p1=p1, p2=p2, ur=int(rng.integers(0, 40)), d12=int(rng.choice([-1, 0, 1, 2, 596])),
+                 sw=int(rng.choice([0, 30, 600])), sr=int(rng.choice([1, 2, 250])), cap=cap, minD=minD)
+        if ctx.lib.mvs_sgbm_check(ctypes.byref(sp.to_c()), W, H) != 0:
+            continue
+        L, R = _pair(W, H, D, 9000 + done, noise=bool(rng.integers(0, 2)) or H < 16 or W < D + 48)
+        want = oracle.sgbm_compute(_op(sp), L, R)
+        got = api.StereoSGBMDisparity.compute16(sp, L, R, ctx=ctx)
+        assert np.array_equal(got, want), f"W{W} H{H} D{D} minD{minD} block{block} mode{mode} p1 {p1} p2 {p2}: {(got != want).sum()} px differ"
+        done += 1
+    assert done >= 25

@@ -180,6 +180,24 @@ int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float gaussian_sigm
 int mvs_hist_post_dev(mvs_ctx* ctx, float* hist_dev, int hw, int hh, float gaussian_sigma, float min_hist_count,
                       float max_hist_count);
 
+/* -- next step downstream: the front half of LocalizationData::calculate,
+ * cost-functions/localization/localization-data.cpp:845-850 with the pose-less branch :855-858: from the floor histogram
+ *   motion = hist > n_deviations ? hist : 0                                   (make_motion_histogram :201-233)
+ *   rhist  = disc-weighted average of motion, radius person_diameter / 2      (make_radius_filtered_hist :147-187)
+ *   bg     = min(prob_bg_max, phi(-(rhist - background_median) / background_stddev))   (:237-253)
+ *   fg0    = phi((rhist - track_median) / track_stddev)                        (:264-285)
+ *   fg     = max(fg0, 0.1)^2                                                   (:298-315 with fg1 = fg0)
+ * Field names and defaults as LocalizationData::Params (localization-data.hpp:27-39); use_median is ignored as in the
+ * reference (:213-219).  Results within 1e-6 relative of the reference arithmetic (fp64 erfc differs by <= 1 ulp).
+ * Output pointers of mvs_localization_hists may be NULL; the _dev variant takes device images and is asynchronous. */
+typedef struct {
+    double n_deviations, person_diameter, background_median, background_stddev, track_median, track_stddev, prob_bg_max;
+} mvs_loc_params;
+int mvs_localization_hists(mvs_ctx* ctx, const mvs_loc_params* p, const float* hist, int hw, int hh, double hist_sz,
+                           float* motion, float* rhist, float* bg, float* fg0, float* fg);
+int mvs_localization_hists_dev(mvs_ctx* ctx, const mvs_loc_params* p, const float* hist_dev, int hw, int hh, double hist_sz,
+                               float* motion_dev, float* rhist_dev, float* bg_dev, float* fg0_dev, float* fg_dev);
+
 /* -- device-resident frame path ----------------------------------------------------------------------
  * One camera-frame through a1 -> a10 without leaving the GPU: what calc_rectified[2c],[2c+1] ->
  * disp_init[c] -> disp_map_update[c] (pass-through, disp_map_update.cpp:89-93) -> floor_hist compute

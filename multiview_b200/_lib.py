@@ -27,6 +27,11 @@ class HistParams(C.Structure):
     _fields_ = [("hist_sz", c_float), ("min_z", c_float), ("max_z", c_float), ("weighting", c_int), ("use_still", c_int)]
 
 
+class LocParams(C.Structure):
+    _fields_ = [(n, c_double) for n in ("n_deviations", "person_diameter", "background_median", "background_stddev",
+                                        "track_median", "track_stddev", "prob_bg_max")]
+
+
 class FrameDesc(C.Structure):
     _fields_ = [("sensor", c_void_p * 2), ("mapx", c_void_p * 2), ("mapy", c_void_p * 2),
                 ("sw", c_int), ("sh", c_int), ("w", c_int), ("h", c_int),
@@ -69,6 +74,8 @@ SIGNATURES = {
     "mvs_hist_sum": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "mvs_hist_post": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_float]),
     "mvs_hist_post_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_float]),
+    "mvs_localization_hists": (c_int, [c_void_p, C.POINTER(LocParams), c_void_p, c_int, c_int, c_double] + [c_void_p] * 5),
+    "mvs_localization_hists_dev": (c_int, [c_void_p, C.POINTER(LocParams), c_void_p, c_int, c_int, c_double] + [c_void_p] * 5),
     "mvs_frame_run": (c_int, [c_void_p, c_int, C.POINTER(FrameDesc), C.POINTER(FrameResult)]),
     "mvs_frame_run_batch": (c_int, [c_void_p, c_int, C.POINTER(FrameDesc), c_int, C.POINTER(FrameResult)]),
     "mvs_frame_fetch": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, C.POINTER(C.c_int32),

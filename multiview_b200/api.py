@@ -24,7 +24,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import _lib
-from ._lib import Bcam, FrameDesc, FrameResult, HistParams, MvsError, SgbmParams
+from ._lib import Bcam, FrameDesc, FrameResult, HistParams, LocParams, MvsError, SgbmParams
 
 INTER_NEAREST, INTER_LINEAR, INTER_CUBIC, INTER_LANCZOS4 = 0, 1, 2, 4
 MODE_SGBM, MODE_HH, MODE_SGBM_3WAY, MODE_HH4 = 0, 1, 2, 3
@@ -455,3 +455,37 @@ def frame_fetch(ctx: Context, slot: int, w: int, h: int, hw: int, hh: int, want_
     if want_cloud:
         out["Xs"], out["xy"] = Xs[:n.value], xy[:n.value]
     return out
+
+
+# ---------------------------------------------------------------------------------------- localization (front half)
+@dataclass
+class LocalizationParams:
+    """LocalizationData::Params, the fields its front half reads (localization-data.hpp:27-39, same names and defaults)."""
+    use_median: bool = False      # ignored by the reference too (localization-data.cpp:213-219)
+    n_deviations: float = 3.0
+    person_diameter: float = 0.400
+    background_median: float = 0.0
+    background_stddev: float = 20.0
+    track_median: float = 200.0
+    track_stddev: float = 50.0
+    prob_bg_max: float = 0.050
+
+    def to_c(self) -> LocParams:
+        return LocParams(self.n_deviations, self.person_diameter, self.background_median, self.background_stddev,
+                         self.track_median, self.track_stddev, self.prob_bg_max)
+
+
+class LocalizationHists:
+    """What LocalizationData::calculate derives from the floor histogram before anything else
+    (localization-data.cpp:845-850, pose-less branch :855-858): motion_hist, the radius-filtered histogram, bg, fg0, fg."""
+
+    @staticmethod
+    def calculate(p: LocalizationParams, hist, hist_sz: float, ctx: Context | None = None):
+        ctx = ctx or default_context()
+        a = np.ascontiguousarray(hist, np.float32)
+        hh, hw = a.shape
+        out = {k: np.empty((hh, hw), np.float32) for k in ("motion", "rhist", "bg", "fg0", "fg")}
+        pc = p.to_c()
+        ctx.check(ctx.lib.mvs_localization_hists(ctx.h, C.byref(pc), _vp(a), hw, hh, float(hist_sz), *[_vp(v) for v in out.values()]),
+                  "mvs_localization_hists")
+        return out

@@ -279,3 +279,86 @@ extern "C" int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float ga
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return MVS_OK;
 }
+
+// ---- localization front half: the four small images LocalizationData::calculate derives from the floor
+// histogram before anything else (cost-functions/localization/localization-data.cpp:845-850; make_motion_histogram
+// :201-233, make_radius_filtered_hist :147-187, make_bg_histogram_ :237-253, make_fg_3d_histogram_ :264-285) and the
+// pose-less foreground product (:298-315, :855-858).  One thread per cell; same operation order as the reference, fp64
+// without FMA; erfc is CUDA's (<= 1 ulp in double, invisible after the float cast except on rounding ties).
+__global__ void loc_motion_kernel(const float* __restrict__ hist, int n, double n_dev, float* __restrict__ motion)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) motion[i] = ((double)hist[i] > n_dev) ? hist[i] : 0.0f;
+}
+__global__ void loc_hists_kernel(const float* __restrict__ motion, int w, int h, double hist_sz, int radius, float radius_inv,
+                                 mvs_loc_params p, float* __restrict__ rhist, float* __restrict__ bg, float* __restrict__ fg0,
+                                 float* __restrict__ fg)
+{
+    const int x0 = blockIdx.x * blockDim.x + threadIdx.x, y0 = blockIdx.y;
+    if (x0 >= w) return;
+    double sum = 0.0;
+    long n = 0;
+    for (int dy = -radius; dy <= radius; ++dy)
+        for (int dx = -radius; dx <= radius; ++dx)
+            if (dx * dx + dy * dy <= radius * radius) {
+                const int x = x0 + dx, y = y0 + dy;
+                if (x < 0 || y < 0 || x >= w || y >= h) continue;
+                const double cell = (double)motion[y * w + x];
+                const double dist = sqrt((double)(dx * dx + dy * dy)) * hist_sz;
+                const double wght = 1.0 - dist * (double)radius_inv;
+                if (wght >= 0.0) { sum += (double)(float)(wght * wght * cell); ++n; }
+            }
+    const float r = (float)(n == 0 ? 0.0 : sum / (double)n);
+    const int i = y0 * w + x0;
+    rhist[i] = r;
+    const double k = -1.0 / sqrt(2.0);
+    const double zb = ((double)r - p.background_median) / p.background_stddev;
+    const double pb = 0.5 * erfc(k * (-zb));
+    bg[i] = (float)(p.prob_bg_max < pb ? p.prob_bg_max : pb);
+    const double zf = ((double)r - p.track_median) / p.track_stddev;
+    const float f0 = (float)(0.5 * erfc(k * zf));
+    fg0[i] = f0;
+    const float a = f0 > 0.10f ? f0 : 0.10f;
+    fg[i] = a * a;
+}
+
+int localization_hists_dev(mvs_ctx* ctx, const mvs_loc_params* p, const float* hist, int w, int h, double hist_sz, float* motion,
+                           float* rhist, float* bg, float* fg0, float* fg)
+{
+    const double in_radius = 0.5 * p->person_diameter;
+    const float radius_inv = 1.0f / (0.5f * (float)in_radius);
+    const int radius = (int)ceil(in_radius / hist_sz);
+    if (!(hist_sz > 0.0) || radius < 0 || radius > 64) return mvs_fail(ctx, MVS_ERR_ARG, "localization: radius of %d cells", radius);
+    loc_motion_kernel<<<cdiv(w * h, 256), 256, 0, ctx->stream>>>(hist, w * h, p->n_deviations, motion);
+    loc_hists_kernel<<<dim3(cdiv(w, 64), h), 64, 0, ctx->stream>>>(motion, w, h, hist_sz, radius, radius_inv, *p, rhist, bg, fg0, fg);
+    MVS_LAUNCH_CHECK_N(ctx, "localization kernels", 2);
+    return MVS_OK;
+}
+
+extern "C" int mvs_localization_hists_dev(mvs_ctx* ctx, const mvs_loc_params* p, const float* hist_dev, int hw, int hh, double hist_sz,
+                                          float* motion_dev, float* rhist_dev, float* bg_dev, float* fg0_dev, float* fg_dev)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!p || !hist_dev || !motion_dev || !rhist_dev || !bg_dev || !fg0_dev || !fg_dev || hw <= 0 || hh <= 0)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_localization_hists_dev: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return localization_hists_dev(ctx, p, hist_dev, hw, hh, hist_sz, motion_dev, rhist_dev, bg_dev, fg0_dev, fg_dev);
+}
+
+extern "C" int mvs_localization_hists(mvs_ctx* ctx, const mvs_loc_params* p, const float* hist, int hw, int hh, double hist_sz,
+                                      float* motion, float* rhist, float* bg, float* fg0, float* fg)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!p || !hist || hw <= 0 || hh <= 0) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_localization_hists: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)hw * hh;
+    MVS_ARENA(ctx, float, d, "loc.api", n * 6);
+    MVS_CUDA(ctx, cudaMemcpyAsync(d, hist, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = localization_hists_dev(ctx, p, d, hw, hh, hist_sz, d + n, d + 2 * n, d + 3 * n, d + 4 * n, d + 5 * n);
+    if (rc) return rc;
+    float* outs[5] = {motion, rhist, bg, fg0, fg};
+    for (int k = 0; k < 5; ++k)
+        if (outs[k]) MVS_CUDA(ctx, cudaMemcpyAsync(outs[k], d + (size_t)(k + 1) * n, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MVS_OK;
+}

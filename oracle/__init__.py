@@ -257,3 +257,23 @@ def hist_post(hist, sigma=0.5, min_count=0.0, max_count=1000.0):
     if rc:
         raise RuntimeError(f"orc_hist_post rc={rc}")
     return a
+
+
+class LocParams(ctypes.Structure):
+    """LocalizationData::Params fields used by the front half (localization-data.hpp:27-39)."""
+
+    _fields_ = [(n, ctypes.c_double) for n in ("n_deviations", "person_diameter", "background_median", "background_stddev",
+                                               "track_median", "track_stddev", "prob_bg_max")]
+
+    @classmethod
+    def reference_defaults(cls):
+        return cls(3.0, 0.400, 0.0, 20.0, 200.0, 50.0, 0.050)
+
+
+def localization_hists(p: LocParams, hist, hist_sz):
+    """motion, radius-filtered, background, 3-D foreground and combined foreground histograms (localization-data.cpp:845-858)."""
+    a = np.ascontiguousarray(hist, np.float32)
+    hh, hw = a.shape
+    out = [np.empty((hh, hw), np.float32) for _ in range(5)]
+    lib().orc_localization_hists(ctypes.byref(p), _p(a), hw, hh, ctypes.c_double(hist_sz), *[_p(o) for o in out])
+    return dict(zip(("motion", "rhist", "bg", "fg0", "fg"), out))

@@ -285,3 +285,47 @@ int orc_hist_post(float* hist, int w, int h, float sigma, float minc, float maxc
     free(tmp);
     return 0;
 }
+
+/* ---- localization front half: cost-functions/localization/localization-data.cpp ---------------------
+ * make_motion_histogram :201-233, make_radius_filtered_hist :147-187, make_bg_histogram_ :237-253,
+ * make_fg_3d_histogram_ :264-285, make_fg_histogram :298-315, as called by LocalizationData::calculate :845-850
+ * (pose-less branch :855-858: fg1 = fg0).  phi_function: utils/math.hpp:374-382 (0.5 * erfc(-z / sqrt 2), double). */
+typedef struct {
+    double n_deviations, person_diameter, background_median, background_stddev, track_median, track_stddev, prob_bg_max;
+} orc_loc_params;
+
+static double orc_phi(double z) { return 0.5 * erfc((-1.0 / sqrt(2.0)) * z); }
+
+void orc_localization_hists(const orc_loc_params* p, const float* hist, int w, int h, double hist_sz, float* motion,
+                            float* rhist, float* bg, float* fg0, float* fg)
+{
+    for (int i = 0; i < w * h; ++i) motion[i] = ((double)hist[i] > p->n_deviations) ? hist[i] : 0.0f;
+    const double in_radius = 0.5 * p->person_diameter;
+    const float radius_inv = 1.0f / (0.5f * (float)in_radius);
+    const int radius = (int)ceil(in_radius / hist_sz);
+    for (int y0 = 0; y0 < h; ++y0)
+        for (int x0 = 0; x0 < w; ++x0) {
+            double sum = 0.0;
+            long n = 0;
+            for (int dy = -radius; dy <= radius; ++dy)
+                for (int dx = -radius; dx <= radius; ++dx)
+                    if (dx * dx + dy * dy <= radius * radius) {
+                        const int x = x0 + dx, y = y0 + dy;
+                        if (x < 0 || y < 0 || x >= w || y >= h) continue;
+                        const double cell = (double)motion[y * w + x];
+                        const double dist = sqrt((double)(dx * dx + dy * dy)) * hist_sz;
+                        const double wght = 1.0 - dist * (double)radius_inv;
+                        if (wght >= 0.0) { sum += (double)(float)(wght * wght * cell); ++n; }
+                    }
+            rhist[y0 * w + x0] = (float)(n == 0 ? 0.0 : sum / (double)n);
+        }
+    for (int i = 0; i < w * h; ++i) {
+        const double zb = ((double)rhist[i] - p->background_median) / p->background_stddev;
+        const double pb = orc_phi(-zb);
+        bg[i] = (float)(p->prob_bg_max < pb ? p->prob_bg_max : pb);
+        const double zf = ((double)rhist[i] - p->track_median) / p->track_stddev;
+        fg0[i] = (float)orc_phi(zf);
+        const float a = fg0[i] > 0.10f ? fg0[i] : 0.10f;
+        fg[i] = a * a;
+    }
+}

@@ -293,3 +293,20 @@ def test_sgbm_seeded_random_configurations(ctx):
         assert np.array_equal(got, want), f"W{W} H{H} D{D} minD{minD} block{block} mode{mode} p1 {p1} p2 {p2}: {(got != want).sum()} px differ"
         done += 1
     assert done >= 25
+
+
+def test_localization_front_half(ctx):
+    """motion / radius-filtered / bg / fg histograms from the floor histogram (localization-data.cpp:845-858)."""
+    rng = np.random.default_rng(77)
+    for (hh, hw, hist_sz, diam) in [(100, 100, 0.10, 0.4), (37, 53, 0.05, 0.4), (64, 48, 0.10, 0.9), (9, 7, 0.25, 0.4)]:
+        hist = ((rng.random((hh, hw)) < 0.3) * rng.gamma(2.0, 120.0, (hh, hw))).astype(np.float32)
+        p = api.LocalizationParams(person_diameter=diam)
+        got = api.LocalizationHists.calculate(p, hist, hist_sz, ctx=ctx)
+        op = oracle.LocParams(p.n_deviations, p.person_diameter, p.background_median, p.background_stddev, p.track_median,
+                              p.track_stddev, p.prob_bg_max)
+        want = oracle.localization_hists(op, hist, hist_sz)
+        assert np.array_equal(got["motion"], want["motion"])
+        assert np.array_equal(got["rhist"], want["rhist"])          # same fp64 operations in the same order
+        for k in ("bg", "fg0", "fg"):                                  # erfc: CUDA vs libm, <= 1 ulp in double
+            assert np.allclose(got[k], want[k], rtol=1e-6, atol=1e-12), k
+            assert (got[k] != want[k]).mean() < 0.01, k

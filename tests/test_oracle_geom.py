@@ -74,3 +74,35 @@ def test_floor_hist_counts_by_hand():
     h2 = oracle.floor_hist_camera(hp2, et, aabb, (0, 0, 0), Xs[:1], xy[:1])
     assert h2[2, 2] == np.float32(1.0)
     assert np.array_equal(oracle.hist_sum(np.stack([h, h2])), h + h2)
+
+
+def test_localization_front_half_against_numpy_formulas():
+    """The C restatement of localization-data.cpp:147-315 against an independent numpy/scipy formulation."""
+    from scipy.special import erfc
+
+    rng = np.random.default_rng(5)
+    hist = ((rng.random((40, 30)) < 0.4) * rng.gamma(2.0, 100.0, (40, 30))).astype(np.float32)
+    p = oracle.LocParams.reference_defaults()
+    hist_sz = 0.1
+    out = oracle.localization_hists(p, hist, hist_sz)
+    motion = np.where(hist.astype(np.float64) > p.n_deviations, hist, 0).astype(np.float32)
+    assert np.array_equal(out["motion"], motion)
+    radius = int(np.ceil(0.5 * p.person_diameter / hist_sz))
+    rinv = float(np.float32(1.0) / (np.float32(0.5) * np.float32(0.5 * p.person_diameter)))
+    want = np.zeros_like(motion, dtype=np.float64)
+    for y0 in range(40):
+        for x0 in range(30):
+            vals = []
+            for dy in range(-radius, radius + 1):
+                for dx in range(-radius, radius + 1):
+                    if dx * dx + dy * dy <= radius * radius and 0 <= x0 + dx < 30 and 0 <= y0 + dy < 40:
+                        wg = 1.0 - np.sqrt(dx * dx + dy * dy) * hist_sz * rinv
+                        if wg >= 0:
+                            vals.append(float(np.float32(wg * wg * float(motion[y0 + dy, x0 + dx]))))
+            want[y0, x0] = sum(vals) / len(vals) if vals else 0.0
+    assert np.allclose(out["rhist"], want.astype(np.float32), rtol=1e-6)
+    phi = lambda z: 0.5 * erfc(-z / np.sqrt(2.0))
+    r = out["rhist"].astype(np.float64)
+    assert np.allclose(out["bg"], np.minimum(p.prob_bg_max, phi(-(r - p.background_median) / p.background_stddev)), rtol=1e-6)
+    assert np.allclose(out["fg0"], phi((r - p.track_median) / p.track_stddev), rtol=1e-6)
+    assert np.allclose(out["fg"], np.maximum(out["fg0"], 0.1) ** 2, rtol=1e-6)

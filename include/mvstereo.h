@@ -180,6 +180,17 @@ int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float gaussian_sigm
 int mvs_hist_post_dev(mvs_ctx* ctx, float* hist_dev, int hw, int hh, float gaussian_sigma, float min_hist_count,
                       float max_hist_count);
 
+/* -- the step upstream: input_images::Task::execute, pipeline/nodes/input_images.cpp:65-76:
+ *   equal = raw_image_equalize ? hist_equalize(raw) : raw     (graphics/hist-equalize.cpp:9-30: BGR -> YCrCb,
+ *                                                               cv::equalizeHist on Y, YCrCb -> BGR)
+ *   grey  = cvtColor(equal, BGR2GRAY)
+ * raw: BGR 8UC3 w x h.  equal (8UC3) and grey (8UC1) may each be NULL.  Bit-exact with OpenCV.  The _dev variant takes
+ * device images (so a decoded frame can go straight on to mvs_frame_run with inputs_on_device) and is asynchronous. */
+int mvs_input_images(mvs_ctx* ctx, const uint8_t* raw, int w, int h, size_t step, int raw_image_equalize, uint8_t* equal,
+                     size_t estep, uint8_t* grey, size_t gstep);
+int mvs_input_images_dev(mvs_ctx* ctx, const uint8_t* raw_dev, int w, int h, size_t step, int raw_image_equalize,
+                         uint8_t* equal_dev, size_t estep, uint8_t* grey_dev, size_t gstep);
+
 /* -- next step downstream: the front half of LocalizationData::calculate,
  * cost-functions/localization/localization-data.cpp:845-850 with the pose-less branch :855-858: from the floor histogram
  *   motion = hist > n_deviations ? hist : 0                                   (make_motion_histogram :201-233)

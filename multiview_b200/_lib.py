@@ -74,6 +74,8 @@ SIGNATURES = {
     "mvs_hist_sum": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "mvs_hist_post": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_float]),
     "mvs_hist_post_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_float]),
+    "mvs_input_images": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_int, c_void_p, c_size_t, c_void_p, c_size_t]),
+    "mvs_input_images_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_int, c_void_p, c_size_t, c_void_p, c_size_t]),
     "mvs_localization_hists": (c_int, [c_void_p, C.POINTER(LocParams), c_void_p, c_int, c_int, c_double] + [c_void_p] * 5),
     "mvs_localization_hists_dev": (c_int, [c_void_p, C.POINTER(LocParams), c_void_p, c_int, c_int, c_double] + [c_void_p] * 5),
     "mvs_frame_run": (c_int, [c_void_p, c_int, C.POINTER(FrameDesc), C.POINTER(FrameResult)]),

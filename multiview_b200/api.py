@@ -489,3 +489,18 @@ class LocalizationHists:
         ctx.check(ctx.lib.mvs_localization_hists(ctx.h, C.byref(pc), _vp(a), hw, hh, float(hist_sz), *[_vp(v) for v in out.values()]),
                   "mvs_localization_hists")
         return out
+
+
+# ------------------------------------------------------------------------------------------------- input images
+def input_images(raw, raw_image_equalize: bool = False, ctx: Context | None = None):
+    """input_images::Task::execute (pipeline/nodes/input_images.cpp:65-76): returns (equal, grey)."""
+    ctx = ctx or default_context()
+    raw = np.ascontiguousarray(raw, np.uint8)
+    if raw.ndim != 3 or raw.shape[2] != 3:
+        raise ValueError("input_images: BGR 8UC3 image expected")
+    h, w, _ = raw.shape
+    equal = np.empty((h, w, 3), np.uint8)
+    grey = np.empty((h, w), np.uint8)
+    ctx.check(ctx.lib.mvs_input_images(ctx.h, _vp(raw), w, h, w * 3, int(bool(raw_image_equalize)), _vp(equal), w * 3, _vp(grey), w),
+              "mvs_input_images")
+    return equal, grey

@@ -248,3 +248,121 @@ extern "C" int mvs_presmooth(mvs_ctx* ctx, const uint8_t* src, int channels, int
     MVS_CUDA(ctx, cudaStreamSynchronize(s));
     return MVS_OK;
 }
+
+// ---- input side: input_images::Task::execute, pipeline/nodes/input_images.cpp:65-76 ----------------------
+// equal = raw_image_equalize ? hist_equalize(raw) : raw (graphics/hist-equalize.cpp:9-30: BGR -> YCrCb, equalizeHist on Y,
+// YCrCb -> BGR), grey = cvtColor(equal, BGR2GRAY); OpenCV's 8-bit fixed-point arithmetic, bit-exact.
+__device__ __forceinline__ int sat8(int v) { return max(0, min(255, v)); }
+__device__ __forceinline__ void bgr2ycrcb(int B, int G, int Rr, int& Y, int& Cr, int& Cb)
+{
+    Y = (Rr * 4899 + G * 9617 + B * 1868 + (1 << 13)) >> 14;
+    Cr = sat8(((Rr - Y) * 11682 + 128 * (1 << 14) + (1 << 13)) >> 14);
+    Cb = sat8(((B - Y) * 9241 + 128 * (1 << 14) + (1 << 13)) >> 14);
+}
+__global__ void __launch_bounds__(256)
+luma_hist_kernel(const uint8_t* __restrict__ src, size_t sstep, int w, int h, unsigned* __restrict__ hist)
+{
+    __shared__ unsigned sh[256];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    for (int y = blockIdx.x; y < h; y += gridDim.x) {
+        const uint8_t* row = src + (size_t)y * sstep;
+        for (int x = threadIdx.x; x < w; x += 256) {
+            int Y, Cr, Cb;
+            bgr2ycrcb(row[3 * x], row[3 * x + 1], row[3 * x + 2], Y, Cr, Cb);
+            atomicAdd(&sh[Y], 1u);
+        }
+    }
+    __syncthreads();
+    if (sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], sh[threadIdx.x]);
+}
+// cv::equalizeHist look-up table; one thread (256 sequential steps on integers)
+__global__ void equalize_lut_kernel(const unsigned* __restrict__ hist, unsigned total, uint8_t* __restrict__ lut)
+{
+    if (threadIdx.x || blockIdx.x) return;
+    int i = 0;
+    while (i < 256 && !hist[i]) ++i;
+    if (i == 256 || hist[i] == total) {
+        for (int k = 0; k < 256; ++k) lut[k] = (uint8_t)(i < 256 ? i : 0);
+        return;
+    }
+    const float scale = 255.f / (float)(total - hist[i]);
+    unsigned sum = 0;
+    for (int k = 0; k <= i; ++k) lut[k] = 0;
+    for (++i; i < 256; ++i) {
+        sum += hist[i];
+        lut[i] = (uint8_t)sat8(__float2int_rn((float)sum * scale));
+    }
+}
+__global__ void __launch_bounds__(128)
+equalize_apply_kernel(const uint8_t* __restrict__ src, size_t sstep, int w, int h, const uint8_t* __restrict__ lut, int equalize,
+                      uint8_t* __restrict__ equal, size_t estep, uint8_t* __restrict__ grey, size_t gstep)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= w) return;
+    const uint8_t* p = src + (size_t)y * sstep + (size_t)x * 3;
+    int b = p[0], g = p[1], r = p[2];
+    if (equalize) {
+        int Y, Cr, Cb;
+        bgr2ycrcb(b, g, r, Y, Cr, Cb);
+        Y = lut[Y];
+        b = sat8(Y + (((Cb - 128) * 29049 + (1 << 13)) >> 14));
+        g = sat8(Y + (((Cb - 128) * -5636 + (Cr - 128) * -11698 + (1 << 13)) >> 14));
+        r = sat8(Y + (((Cr - 128) * 22987 + (1 << 13)) >> 14));
+    }
+    if (equal) {
+        uint8_t* e = equal + (size_t)y * estep + (size_t)x * 3;
+        e[0] = (uint8_t)b; e[1] = (uint8_t)g; e[2] = (uint8_t)r;
+    }
+    if (grey) grey[(size_t)y * gstep + x] = (uint8_t)((3735 * b + 19235 * g + 9798 * r + 16384) >> 15);
+}
+
+int input_images_dev(mvs_ctx* ctx, const uint8_t* raw, int w, int h, size_t sstep, int equalize, uint8_t* equal, size_t estep,
+                     uint8_t* grey, size_t gstep)
+{
+    cudaStream_t s = ctx->stream;
+    MVS_ARENA(ctx, unsigned, hist, "input.hist", 256);
+    MVS_ARENA(ctx, uint8_t, lut, "input.lut", 256);
+    if (equalize) {
+        MVS_CUDA(ctx, cudaMemsetAsync(hist, 0, 256 * sizeof(unsigned), s));
+        luma_hist_kernel<<<min(h, 592), 256, 0, s>>>(raw, sstep, w, h, hist);
+        equalize_lut_kernel<<<1, 32, 0, s>>>(hist, (unsigned)((size_t)w * h), lut);
+        MVS_LAUNCH_CHECK_N(ctx, "equalize kernels", 2);
+    }
+    equalize_apply_kernel<<<dim3(cdiv(w, 128), h), 128, 0, s>>>(raw, sstep, w, h, lut, equalize, equal, estep, grey, gstep);
+    MVS_LAUNCH_CHECK(ctx, "equalize_apply_kernel");
+    return MVS_OK;
+}
+
+extern "C" int mvs_input_images(mvs_ctx* ctx, const uint8_t* raw, int w, int h, size_t step, int raw_image_equalize,
+                                uint8_t* equal, size_t estep, uint8_t* grey, size_t gstep)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!raw || w <= 0 || h <= 0 || step < (size_t)w * 3 || (equal && estep < (size_t)w * 3) || (grey && gstep < (size_t)w) ||
+        (size_t)w * h > 0xffffffffull)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_input_images: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    MVS_ARENA(ctx, uint8_t, dsrc, "input.api.src", (size_t)h * w * 3);
+    MVS_ARENA(ctx, uint8_t, deq, "input.api.equal", (size_t)h * w * 3);
+    MVS_ARENA(ctx, uint8_t, dgr, "input.api.grey", (size_t)h * w);
+    MVS_CUDA(ctx, cudaMemcpy2DAsync(dsrc, (size_t)w * 3, raw, step, (size_t)w * 3, h, cudaMemcpyHostToDevice, s));
+    int rc = input_images_dev(ctx, dsrc, w, h, (size_t)w * 3, raw_image_equalize, equal ? deq : nullptr, (size_t)w * 3,
+                              grey ? dgr : nullptr, (size_t)w);
+    if (rc) return rc;
+    if (equal) MVS_CUDA(ctx, cudaMemcpy2DAsync(equal, estep, deq, (size_t)w * 3, (size_t)w * 3, h, cudaMemcpyDeviceToHost, s));
+    if (grey) MVS_CUDA(ctx, cudaMemcpy2DAsync(grey, gstep, dgr, (size_t)w, (size_t)w, h, cudaMemcpyDeviceToHost, s));
+    MVS_CUDA(ctx, cudaStreamSynchronize(s));
+    return MVS_OK;
+}
+
+extern "C" int mvs_input_images_dev(mvs_ctx* ctx, const uint8_t* raw_dev, int w, int h, size_t step, int raw_image_equalize,
+                                    uint8_t* equal_dev, size_t estep, uint8_t* grey_dev, size_t gstep)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!raw_dev || w <= 0 || h <= 0 || step < (size_t)w * 3 || (equal_dev && estep < (size_t)w * 3) ||
+        (grey_dev && gstep < (size_t)w) || (size_t)w * h > 0xffffffffull)
+        return mvs_fail(ctx, MVS_ERR_ARG, "mvs_input_images_dev: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    return input_images_dev(ctx, raw_dev, w, h, step, raw_image_equalize, equal_dev, estep, grey_dev, gstep);
+}

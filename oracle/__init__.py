@@ -277,3 +277,13 @@ def localization_hists(p: LocParams, hist, hist_sz):
     out = [np.empty((hh, hw), np.float32) for _ in range(5)]
     lib().orc_localization_hists(ctypes.byref(p), _p(a), hw, hh, ctypes.c_double(hist_sz), *[_p(o) for o in out])
     return dict(zip(("motion", "rhist", "bg", "fg0", "fg"), out))
+
+
+def input_images(raw, equalize=True):
+    """input_images node (pipeline/nodes/input_images.cpp:65-76): (equal, grey)."""
+    raw = np.ascontiguousarray(raw, np.uint8)
+    h, w, _ = raw.shape
+    equal = np.empty((h, w, 3), np.uint8)
+    grey = np.empty((h, w), np.uint8)
+    lib().orc_input_images(_p(raw), w, h, _sz(w * 3), int(bool(equalize)), _p(equal), _sz(w * 3), _p(grey), _sz(w))
+    return equal, grey

@@ -76,3 +76,15 @@ def hist_post(hist, sigma=0.5, min_count=0.0, max_count=1000.0):
     a[a < min_count] = 0.0
     a[a > max_count] = max_count
     return a
+
+
+def input_images(raw, equalize=True):
+    """hist_equalize (graphics/hist-equalize.cpp:9-30) + cvtColor BGR2GRAY, as input_images.cpp:65-76 calls them."""
+    cv2 = _cv2()
+    equal = raw
+    if equalize:
+        ycc = cv2.cvtColor(raw, cv2.COLOR_BGR2YCrCb)
+        ch = list(cv2.split(ycc))
+        ch[0] = cv2.equalizeHist(ch[0])
+        equal = cv2.cvtColor(cv2.merge(ch), cv2.COLOR_YCrCb2BGR)
+    return equal, cv2.cvtColor(equal, cv2.COLOR_BGR2GRAY)

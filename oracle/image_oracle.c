@@ -284,3 +284,63 @@ int orc_gauss_blur_u8(const uint8_t* src, size_t sstep, int w, int h, int n, dou
     free(tmp);
     return 0;
 }
+
+/* ---- input side: input_images::Task::execute, pipeline/nodes/input_images.cpp:65-76 ---------------------
+ * equal = raw_image_equalize ? hist_equalize(raw) : raw  (graphics/hist-equalize.cpp:9-30: BGR -> YCrCb, equalizeHist on
+ * Y, YCrCb -> BGR), grey = cvtColor(equal, BGR2GRAY).  OpenCV 8-bit fixed point (14 fractional bits), pinned against cv2. */
+static inline uint8_t sat8i(long v) { return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
+static inline void orc_bgr2ycrcb(const uint8_t* p, int* Y, int* Cr, int* Cb)
+{
+    const int B = p[0], G = p[1], Rr = p[2];
+    const int y = (Rr * 4899 + G * 9617 + B * 1868 + (1 << 13)) >> 14;
+    *Y = y;   /* <= 255 by construction */
+    *Cr = sat8i(((Rr - y) * 11682 + 128 * (1 << 14) + (1 << 13)) >> 14);
+    *Cb = sat8i(((B - y) * 9241 + 128 * (1 << 14) + (1 << 13)) >> 14);
+}
+/* cv::equalizeHist look-up table from the 256-bin histogram of `total` pixels */
+void orc_equalize_lut(const int* hist, long total, uint8_t* lut)
+{
+    int i = 0;
+    while (i < 256 && !hist[i]) ++i;
+    if (i == 256 || hist[i] == total) {   /* one grey level: the image is filled with it */
+        for (int k = 0; k < 256; ++k) lut[k] = (uint8_t)(i < 256 ? i : 0);
+        return;
+    }
+    const float scale = 255.f / (float)(total - hist[i]);
+    long sum = 0;
+    for (int k = 0; k <= i; ++k) lut[k] = 0;
+    for (++i; i < 256; ++i) {
+        sum += hist[i];
+        lut[i] = sat8i(lrintf((float)sum * scale));
+    }
+}
+void orc_input_images(const uint8_t* raw, int w, int h, size_t sstep, int equalize, uint8_t* equal, size_t estep, uint8_t* grey,
+                      size_t gstep)
+{
+    uint8_t lut[256];
+    if (equalize) {
+        int hist[256] = {0};
+        for (int y = 0; y < h; ++y)
+            for (int x = 0; x < w; ++x) {
+                int Y, Cr, Cb;
+                orc_bgr2ycrcb(raw + (size_t)y * sstep + (size_t)x * 3, &Y, &Cr, &Cb);
+                hist[Y]++;
+            }
+        orc_equalize_lut(hist, (long)w * h, lut);
+    }
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const uint8_t* p = raw + (size_t)y * sstep + (size_t)x * 3;
+            uint8_t o[3] = {p[0], p[1], p[2]};
+            if (equalize) {
+                int Y, Cr, Cb;
+                orc_bgr2ycrcb(p, &Y, &Cr, &Cb);
+                Y = lut[Y];
+                o[0] = sat8i(Y + (((Cb - 128) * 29049 + (1 << 13)) >> 14));
+                o[1] = sat8i(Y + (((Cb - 128) * -5636 + (Cr - 128) * -11698 + (1 << 13)) >> 14));
+                o[2] = sat8i(Y + (((Cr - 128) * 22987 + (1 << 13)) >> 14));
+            }
+            if (equal) { uint8_t* e = equal + (size_t)y * estep + (size_t)x * 3; e[0] = o[0]; e[1] = o[1]; e[2] = o[2]; }
+            if (grey) grey[(size_t)y * gstep + x] = (uint8_t)((3735 * o[0] + 19235 * o[1] + 9798 * o[2] + 16384) >> 15);
+        }
+}

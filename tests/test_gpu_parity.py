@@ -310,3 +310,14 @@ def test_localization_front_half(ctx):
         for k in ("bg", "fg0", "fg"):                                  # erfc: CUDA vs libm, <= 1 ulp in double
             assert np.allclose(got[k], want[k], rtol=1e-6, atol=1e-12), k
             assert (got[k] != want[k]).mean() < 0.01, k
+
+
+def test_input_images_node(ctx):
+    """hist_equalize + BGR2GRAY (input_images.cpp:65-76), bit-exact against the cv2-pinned oracle."""
+    rng = np.random.default_rng(31)
+    imgs = [rng.integers(0, 256, (97, 131, 3), dtype=np.uint8), rng.integers(90, 140, (64, 80, 3), dtype=np.uint8),
+            np.full((20, 24, 3), 77, np.uint8), synth.make_camera(640, 400, 64, config=3)["sensor"][0]]
+    for img in imgs:
+        for eq in (True, False):
+            got, want = api.input_images(img, eq, ctx=ctx), oracle.input_images(img, eq)
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])

@@ -70,3 +70,15 @@ def test_remap_all_interpolation_modes_match_cv2(interp):
         mx[3, :8] = np.arange(8, dtype=np.float32) * 0.5  # exact halves: round-half-even
         a, b = oracle.remap_bgr8(src, mx, my, interp), cv2ref.remap_bgr8(src, mx, my, interp)
         assert np.array_equal(a, b), f"interp {interp}: {(a != b).any(axis=2).sum()} px differ"
+
+
+def test_input_images_equalize_matches_cv2():
+    """hist_equalize + BGR2GRAY of the input_images node, bit-exact with cv2."""
+    rng = np.random.default_rng(31)
+    imgs = [rng.integers(0, 256, (97, 131, 3), dtype=np.uint8), rng.integers(90, 140, (64, 80, 3), dtype=np.uint8),
+            np.full((20, 24, 3), 77, np.uint8), synth.make_camera(320, 200, 64, config=3)["sensor"][0]]
+    imgs[0][:30, :40] = rng.integers(0, 30, (30, 40, 3))
+    for img in imgs:
+        for eq in (True, False):
+            a, b = oracle.input_images(img, eq), cv2ref.input_images(img, eq)
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])

@@ -71,5 +71,33 @@ def main():
     print("wrote", os.path.join(HERE, "cv2_golden.npz"), {k: v.shape for k, v in out.items() if "disp" in k or k.endswith("_out")})
 
 
+def main_widened():
+    """Second fixture file (rows added later in round 1): the other cv::remap modes, the input_images node and the
+    float histogram blur.  Own seed, so the first file never changes."""
+    cv2ref.set_threads(1)
+    rng = np.random.default_rng(20261107)
+    out = {}
+    sw, sh, w, h = 120, 90, 96, 72
+    src = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+    mx = (rng.random((h, w)) * (sw + 12) - 6).astype(np.float32)
+    my = (rng.random((h, w)) * (sh + 12) - 6).astype(np.float32)
+    mx[0, 0], my[0, 1], mx[1, 1], my[2, 2] = 1e9, -1e9, np.nan, 3e4
+    out["remap_src"], out["remap_mapx"], out["remap_mapy"] = src, mx, my
+    for interp in (0, 1, 2, 4):
+        out[f"remap_out_{interp}"] = cv2ref.remap_bgr8(src, mx, my, interp)
+    img = synth.make_camera(320, 200, 64, config=3)["sensor"][0]
+    out["input_raw"] = img
+    for eq in (0, 1):
+        e, g = cv2ref.input_images(img, bool(eq))
+        out[f"input_equal_{eq}"], out[f"input_grey_{eq}"] = e, g
+    hist = ((rng.random((100, 120)) < 0.2) * rng.integers(1, 1500, (100, 120))).astype(np.float32)
+    out["hist_in"] = hist
+    out["hist_post"] = cv2ref.hist_post(hist, 0.5, 0.0, 1000.0)
+    np.savez_compressed(os.path.join(HERE, "cv2_golden_widened.npz"), **out)
+    print("wrote", os.path.join(HERE, "cv2_golden_widened.npz"), sorted(out))
+
+
 if __name__ == "__main__":
-    main()
+    if "--widened-only" not in sys.argv:
+        main()
+    main_widened()

@@ -32,3 +32,18 @@ def test_chain_golden(ctx):
     p = api.DisparityParams(stereosgbm_params=api.StereoSGBMParams(sg_num_disparities=64, sg_mode=1))
     got = api.Disparity.calculate(p, True, rect[0], rect[1], ctx=ctx)
     assert np.array_equal(got, G["chain_disp"])
+
+
+GW = np.load(os.path.join(os.path.dirname(__file__), "golden", "cv2_golden_widened.npz"))
+
+
+@pytest.mark.parametrize("interp", [0, 1, 2, 4])
+def test_remap_modes_golden(ctx, interp):
+    got = api.calc_rectified(GW["remap_src"], GW["remap_mapx"], GW["remap_mapy"], interp, ctx=ctx)
+    assert np.array_equal(got, GW[f"remap_out_{interp}"])
+
+
+@pytest.mark.parametrize("eq", [0, 1])
+def test_input_images_golden(ctx, eq):
+    equal, grey = api.input_images(GW["input_raw"], bool(eq), ctx=ctx)
+    assert np.array_equal(equal, GW[f"input_equal_{eq}"]) and np.array_equal(grey, GW[f"input_grey_{eq}"])

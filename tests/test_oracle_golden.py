@@ -43,3 +43,23 @@ def test_taps_are_consistent():
     assert (t["S"] >= t["S1"]).all() and (t["C"] >= 0).all()
     d = oracle.filter_speckles(oracle.median3_s16(t["raw"]), (p.min_disp - 1) * 16, p.speckle_win, 16 * p.speckle_range)
     assert np.array_equal(d, t["disp"])
+
+
+GW = np.load(os.path.join(os.path.dirname(__file__), "golden", "cv2_golden_widened.npz"))
+
+
+@pytest.mark.parametrize("interp", [0, 1, 2, 4])
+def test_remap_modes_golden(interp):
+    got = oracle.remap_bgr8(GW["remap_src"], GW["remap_mapx"], GW["remap_mapy"], interp)
+    assert np.array_equal(got, GW[f"remap_out_{interp}"])
+
+
+@pytest.mark.parametrize("eq", [0, 1])
+def test_input_images_golden(eq):
+    equal, grey = oracle.input_images(GW["input_raw"], bool(eq))
+    assert np.array_equal(equal, GW[f"input_equal_{eq}"]) and np.array_equal(grey, GW[f"input_grey_{eq}"])
+
+
+def test_hist_post_golden():
+    got = oracle.hist_post(GW["hist_in"], 0.5, 0.0, 1000.0)
+    assert np.allclose(got, GW["hist_post"], rtol=1e-6, atol=1e-4)  # float blur: OpenCV's result varies by an ulp with its SIMD path

@@ -22,7 +22,7 @@ UNITS = {
     "ctx.cu": [],
     "remap.cu": [],
     "presmooth.cu": [],
-    "cost.cu": [],
+    "cost.cu": os.environ.get("MVS_COST_FLAGS", "").split(),
     "aggregate.cu": [],
     # tuning experiments: MVS_WAVE_FLAGS="-DWAVE_R=15 -DWAVE_D12=7" python -m multiview_b200.build --force
     "aggregate_wave.cu": os.environ.get("MVS_WAVE_FLAGS", "").split(),

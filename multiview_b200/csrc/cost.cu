@@ -223,7 +223,9 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
 // A thread owns four packed words (16 bytes) of a strip of rows: C(y+1) = C(y) + hsum(y+SH+1) - hsum(y-SH).  The row
 // leaving the window was read WIN rows earlier by the same thread and is still in L2, so HBM sees every row sum once
 // per strip (+ WIN-1 at the strip start) while the instruction count stays at ~4 per word and row.
+#ifndef VSUM_ROWS
 #define VSUM_ROWS 96
+#endif
 __device__ __forceinline__ uint4 add4(uint4 a, uint4 b) { return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
 __device__ __forceinline__ uint4 sub4(uint4 a, uint4 b) { return make_uint4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
 template <int WIN, int THREADS>

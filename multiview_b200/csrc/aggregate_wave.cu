@@ -479,12 +479,16 @@ template <int NW, int DIRMASK, bool PAD, bool BWD>
 static int launch_wave(mvs_ctx* ctx, const WaveParams& p)
 {
     const int smem = (Ring<NW>::WORDS + (BWD ? 2 : 1) * Ring<NW>::STREAM_WORDS) * 4;
-    static int per_sm = 0;  // per instantiation
+    // per instantiation and device (function attributes are per device; doing this twice from two threads is harmless)
+    static int per_sm_dev[MVS_MAX_DEVICES] = {};
+    const int dv = ctx->device >= 0 && ctx->device < MVS_MAX_DEVICES ? ctx->device : 0;
+    int per_sm = dv == ctx->device ? per_sm_dev[dv] : 0;
     if (!per_sm) {
         MVS_CUDA(ctx, cudaFuncSetAttribute(wave_kernel<NW, DIRMASK, PAD, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         int n = 1;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wave_kernel<NW, DIRMASK, PAD, BWD>, WAVE_THREADS, smem);
         per_sm = n < 1 ? 1 : n;
+        per_sm_dev[dv] = per_sm;
     }
     int grid = min(p.nbands * p.F, ctx->sm_count * per_sm);
     wave_kernel<NW, DIRMASK, PAD, BWD><<<grid, WAVE_THREADS, smem, ctx->stream>>>(p);

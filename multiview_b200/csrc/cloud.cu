@@ -264,7 +264,6 @@ extern "C" int mvs_point_cloud(mvs_ctx* ctx, const mvs_bcam* bcam, const float* 
 #define MVS_STATIC_CLOUD_SCRATCH_BYTES (MVS_STATIC_CLOUD_MAX_TILES * (2 * sizeof(int) + 3 * sizeof(double)))
 static __device__ __align__(256) unsigned char g_cloud_scratch[MVS_STATIC_CLOUD_SCRATCH_BYTES];
 
-#define MVS_MAX_DEVICES 64
 static unsigned char* g_cloud_scratch_addr[MVS_MAX_DEVICES];  // device address of g_cloud_scratch, per device
 
 extern "C" int mvs_point_cloud_static_dev(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp_dev, int w, int h,

@@ -11,6 +11,7 @@
 
 #include "../../include/mvstereo.h"
 
+#define MVS_MAX_DEVICES 64   // per-device one-time state (function attributes are per device)
 #define MVS_MAX_SLOTS 64
 #define MVS_MAX_BATCH 16  // camera-frames per batched launch
 

@@ -111,10 +111,11 @@ int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double e
     MVS_CUDA(ctx, cudaMemsetAsync(cam_hist, 0, sizeof(float) * (size_t)hw * hh, ctx->stream));
     const size_t smem = sizeof(float) * (size_t)hw * hh;
     if (smem <= 100 * 1024) {  // two blocks per SM keep a private histogram each
-        static bool configured = false;
-        if (!configured) {
+        static bool configured[MVS_MAX_DEVICES] = {};  // function attributes are per device; setting one twice is harmless
+        const int dv = ctx->device >= 0 && ctx->device < MVS_MAX_DEVICES ? ctx->device : 0;
+        if (!configured[dv] || dv != ctx->device) {
             MVS_CUDA(ctx, cudaFuncSetAttribute(floor_hist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-            configured = true;
+            configured[dv] = true;
         }
         floor_hist_kernel<true><<<ctx->sm_count * 2, 512, smem, ctx->stream>>>(a, Xs, xy, n_dev, n_host, labels, still, cam_hist);
     } else {

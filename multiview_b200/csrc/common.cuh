@@ -98,6 +98,8 @@ int sgbm_geom(mvs_ctx* ctx, const mvs_sgbm_params* p, int w, int h, SgbmGeom* g)
 int remap_bgr8_dev(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
                    const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border[3], uint8_t* dst,
                    size_t dstep);
+int presmooth_batch_dev(mvs_ctx* ctx, int n, const uint8_t* const* src, int channels, int w, int h, size_t step, double sigma,
+                        uint8_t* const* dst, size_t dstep);
 int presmooth_dev(mvs_ctx* ctx, const char* tag, const uint8_t* src, int channels, int w, int h, size_t step,
                   double sigma, uint8_t* dst, size_t dstep);
 // grey images (step == w) -> disparity16 (step == w*2); volumes stay in the arena ("sgbm.C", "sgbm.S")

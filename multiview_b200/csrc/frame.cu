@@ -120,9 +120,20 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     }
     stage_end(ctx, "rectify");
     stage_begin(ctx, "presmooth");
-    for (int f = 0; f < n_frames && !rc; ++f)
-        for (int i = 0; i < 2 && !rc; ++i)
-            rc = presmooth_dev(ctx, i ? "r" : "l", sb[f].rect[i], 3, w, h, (size_t)w * 3, descs[f].presmooth_sigma, sb[f].grey[i], (size_t)w);
+    {
+        // all sensors of the batch in one launch per pass when they share the blur strength
+        bool same_sigma = true;
+        for (int f = 1; f < n_frames; ++f) same_sigma = same_sigma && descs[f].presmooth_sigma == d0.presmooth_sigma;
+        const uint8_t* ps[2 * MVS_MAX_BATCH];
+        uint8_t* pd[2 * MVS_MAX_BATCH];
+        for (int f = 0; f < n_frames; ++f)
+            for (int i = 0; i < 2; ++i) { ps[2 * f + i] = sb[f].rect[i]; pd[2 * f + i] = sb[f].grey[i]; }
+        if (same_sigma && !rc)
+            rc = presmooth_batch_dev(ctx, 2 * n_frames, ps, 3, w, h, (size_t)w * 3, d0.presmooth_sigma, pd, (size_t)w);
+        else
+            for (int f = 0; f < n_frames && !rc; ++f)
+                rc = presmooth_batch_dev(ctx, 2, ps + 2 * f, 3, w, h, (size_t)w * 3, descs[f].presmooth_sigma, pd + 2 * f, (size_t)w);
+    }
     stage_end(ctx, "presmooth");
     if (!rc) {
         const uint8_t *l[MVS_MAX_BATCH], *r[MVS_MAX_BATCH];

@@ -107,8 +107,8 @@ struct BlurPacked {
     uint32_t t2[16];   // vertical: the same taps, two per word (low two bytes)
 };
 template <int R>
-__global__ void __launch_bounds__(128)
-blur_h4_kernel(const uint8_t* __restrict__ src, size_t sstep, int w, int h, BlurTaps t, BlurPacked pk, uint16_t* __restrict__ dst)
+__device__ __forceinline__ void
+blur_h4_body(const uint8_t* __restrict__ src, size_t sstep, int w, int h, BlurTaps t, BlurPacked pk, uint16_t* __restrict__ dst)
 {
     constexpr int NT = (2 * R + 2) / 4;   // dot products per output
     const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y;
@@ -140,8 +140,8 @@ blur_h4_kernel(const uint8_t* __restrict__ src, size_t sstep, int w, int h, Blur
 }
 
 template <int R>
-__global__ void __launch_bounds__(128)
-blur_v4_kernel(const uint16_t* __restrict__ src, int w, int h, BlurTaps t, BlurPacked pk, uint8_t* __restrict__ dst, size_t dstep)
+__device__ __forceinline__ void
+blur_v4_body(const uint16_t* __restrict__ src, int w, int h, BlurTaps t, BlurPacked pk, uint8_t* __restrict__ dst, size_t dstep)
 {
     const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y;
     if (x0 >= w) return;
@@ -167,6 +167,36 @@ blur_v4_kernel(const uint16_t* __restrict__ src, int w, int h, BlurTaps t, BlurP
             dst[(size_t)y * dstep + x0 + q] = (uint8_t)((a + (1u << 15)) >> 16);
         }
     }
+}
+
+template <int R>
+__global__ void __launch_bounds__(128)
+blur_h4_kernel(const uint8_t* __restrict__ src, size_t sstep, int w, int h, BlurTaps t, BlurPacked pk, uint16_t* __restrict__ dst)
+{
+    blur_h4_body<R>(src, sstep, w, h, t, pk, dst);
+}
+template <int R>
+__global__ void __launch_bounds__(128)
+blur_v4_kernel(const uint16_t* __restrict__ src, int w, int h, BlurTaps t, BlurPacked pk, uint8_t* __restrict__ dst, size_t dstep)
+{
+    blur_v4_body<R>(src, w, h, t, pk, dst, dstep);
+}
+// batched: image blockIdx.z; the u16 intermediate of image z lives at tmp + z * w * h
+struct BlurBatch {
+    const uint8_t* src[32];
+    uint8_t* dst[32];
+};
+template <int R>
+__global__ void __launch_bounds__(128)
+blur_h4_batch_kernel(BlurBatch b, int w, int h, BlurTaps t, BlurPacked pk, uint16_t* __restrict__ tmp)
+{
+    blur_h4_body<R>(b.src[blockIdx.z], (size_t)w, w, h, t, pk, tmp + (size_t)blockIdx.z * w * h);
+}
+template <int R>
+__global__ void __launch_bounds__(128)
+blur_v4_batch_kernel(BlurBatch b, int w, int h, BlurTaps t, BlurPacked pk, const uint16_t* __restrict__ tmp, size_t dstep)
+{
+    blur_v4_body<R>(tmp + (size_t)blockIdx.z * w * h, w, h, t, pk, b.dst[blockIdx.z], dstep);
 }
 
 template <int R>
@@ -202,6 +232,29 @@ static void blur_pass(cudaStream_t s, const uint8_t* src, int w, int h, const Bl
     }
 }
 
+// ---- batched form: the grey images of a whole batch of sensors in ONE launch per pass (blockIdx.z = image) -------------
+// A 2-megapixel pass is a ~10 us kernel, mostly ramp and tail; 32 images per launch fill the machine.
+#define PRESMOOTH_MAX_IMAGES 32
+struct ImgBatch {
+    const uint8_t* src[PRESMOOTH_MAX_IMAGES];
+    uint8_t* dst[PRESMOOTH_MAX_IMAGES];
+};
+// BGR -> grey, four pixels per thread (three aligned words in, one word out); w % 4 == 0, rows 4-byte aligned
+__global__ void __launch_bounds__(128)
+bgr2gray4_batch_kernel(ImgBatch b, size_t sstep, int w, int h, size_t dstep)
+{
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y;
+    if (x0 >= w) return;
+    const uint32_t* p = (const uint32_t*)(b.src[blockIdx.z] + (size_t)y * sstep + (size_t)x0 * 3);
+    const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);   // B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+    auto grey = [](uint32_t bb, uint32_t gg, uint32_t rr) { return (3735u * bb + 19235u * gg + 9798u * rr + 16384u) >> 15; };
+    const uint32_t g0 = grey(w0 & 0xff, (w0 >> 8) & 0xff, (w0 >> 16) & 0xff);
+    const uint32_t g1 = grey(w0 >> 24, w1 & 0xff, (w1 >> 8) & 0xff);
+    const uint32_t g2 = grey((w1 >> 16) & 0xff, w1 >> 24, w2 & 0xff);
+    const uint32_t g3 = grey((w2 >> 8) & 0xff, (w2 >> 16) & 0xff, w2 >> 24);
+    *(uint32_t*)(b.dst[blockIdx.z] + (size_t)y * dstep + x0) = g0 | (g1 << 8) | (g2 << 16) | (g3 << 24);
+}
+
 int presmooth_dev(mvs_ctx* ctx, const char* tag, const uint8_t* src, int channels, int w, int h, size_t step,
                   double sigma, uint8_t* dst, size_t dstep)
 {
@@ -226,6 +279,64 @@ int presmooth_dev(mvs_ctx* ctx, const char* tag, const uint8_t* src, int channel
     blur_pass(s, grey, w, h, t, tmp, grey, (size_t)w);
     blur_pass(s, grey, w, h, t, tmp, dst, dstep);
     MVS_LAUNCH_CHECK_N(ctx, "blur kernels", 4);
+    return MVS_OK;
+}
+
+template <int R>
+static void blur_batch_launch(cudaStream_t s, const BlurBatch& b, int n, int w, int h, const BlurTaps& t, uint16_t* tmp, size_t dstep)
+{
+    BlurPacked pk;
+    memset(&pk, 0, sizeof(pk));
+    for (int i = 0; i < 2 * R + 1; ++i) {
+        const uint32_t k = (uint32_t)t.k[15 - R + i];
+        pk.t4[i / 4] |= k << (8 * (i % 4));
+        pk.t2[i / 2] |= k << (8 * (i % 2));
+    }
+    dim3 grid(cdiv(w, 512), h, n);
+    blur_h4_batch_kernel<R><<<grid, 128, 0, s>>>(b, w, h, t, pk, tmp);
+    blur_v4_batch_kernel<R><<<grid, 128, 0, s>>>(b, w, h, t, pk, tmp, dstep);
+}
+
+// n images of equal size (<= 32) through grey + double blur with one launch per pass; falls back to the per-image
+// path when the packed kernels do not apply (grey input, odd widths, unaligned rows, no blur)
+int presmooth_batch_dev(mvs_ctx* ctx, int n, const uint8_t* const* src, int channels, int w, int h, size_t step, double sigma,
+                        uint8_t* const* dst, size_t dstep)
+{
+    BlurTaps t;
+    memset(&t, 0, sizeof(t));
+    bool packed = channels == 3 && sigma > 0.0 && n >= 1 && n <= PRESMOOTH_MAX_IMAGES && (w % 4) == 0 && (step % 4) == 0 &&
+                  (dstep % 4) == 0 && gauss_taps_q8(sigma, &t) == 0;
+    for (int i = 0; packed && i < n; ++i) packed = ((uintptr_t)src[i] % 4) == 0 && ((uintptr_t)dst[i] % 4) == 0;
+    for (int i = t.lo; packed && i <= t.hi; ++i) packed = t.k[i] >= 0 && t.k[i] <= 255;
+    if (!packed) {
+        for (int i = 0; i < n; ++i) {
+            int rc = presmooth_dev(ctx, (i & 1) ? "r" : "l", src[i], channels, w, h, step, sigma, dst[i], dstep);
+            if (rc) return rc;
+        }
+        return MVS_OK;
+    }
+    cudaStream_t s = ctx->stream;
+    const size_t px = (size_t)w * h;
+    MVS_ARENA(ctx, uint8_t, grey, "presmooth.batch.grey", px * n);
+    MVS_ARENA(ctx, uint16_t, tmp, "presmooth.batch.tmp", px * n);
+    ImgBatch g;
+    BlurBatch p1, p2;
+    for (int i = 0; i < n; ++i) {
+        g.src[i] = src[i]; g.dst[i] = grey + px * i;
+        p1.src[i] = grey + px * i; p1.dst[i] = grey + px * i;   // pass 1: grey -> grey (through tmp)
+        p2.src[i] = grey + px * i; p2.dst[i] = dst[i];          // pass 2: grey -> dst
+    }
+    bgr2gray4_batch_kernel<<<dim3(cdiv(w, 512), h, n), 128, 0, s>>>(g, step, w, h, (size_t)w);
+    const int radius = 15 - t.lo;
+    for (int pass = 0; pass < 2; ++pass) {
+        const BlurBatch& b = pass ? p2 : p1;
+        const size_t ds = pass ? dstep : (size_t)w;
+        if (radius <= 3) blur_batch_launch<3>(s, b, n, w, h, t, tmp, ds);
+        else if (radius <= 7) blur_batch_launch<7>(s, b, n, w, h, t, tmp, ds);
+        else if (radius <= 11) blur_batch_launch<11>(s, b, n, w, h, t, tmp, ds);
+        else blur_batch_launch<15>(s, b, n, w, h, t, tmp, ds);
+    }
+    MVS_LAUNCH_CHECK_N(ctx, "presmooth batch kernels", 5);
     return MVS_OK;
 }
 

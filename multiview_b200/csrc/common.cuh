@@ -95,6 +95,9 @@ struct SgbmGeom {
 int sgbm_geom(mvs_ctx* ctx, const mvs_sgbm_params* p, int w, int h, SgbmGeom* g);
 
 // ---- device-pointer stage entry points (all asynchronous on ctx->stream) ------------------------------
+int remap_cubic_bgr8_batch_dev(mvs_ctx* ctx, int n, const uint8_t* const* src, int sw, int sh, size_t sstep, const float* const* mapx,
+                               const float* const* mapy, size_t mstep, int w, int h, const uint8_t border[3], uint8_t* const* dst,
+                               size_t dstep);
 int remap_bgr8_dev(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sstep, const float* mapx,
                    const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border[3], uint8_t* dst,
                    size_t dstep);

@@ -110,13 +110,31 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
 
     const uint8_t white[3] = {255, 255, 255};  // calc_rectified.cpp:113
     stage_begin(ctx, "rectify");
-    for (int f = 0; f < n_frames && !rc; ++f) {
-        const mvs_frame_desc* d = descs + f;
-        const size_t sstep = d->inputs_on_device ? d->sstep : (size_t)d->sw * 3;
-        const size_t mstep = d->maps_on_device ? d->mstep : (size_t)w * 4;
-        for (int i = 0; i < 2 && !rc; ++i)
-            rc = remap_bgr8_dev(ctx, sensor[f][i], d->sw, d->sh, sstep, mapx[f][i], mapy[f][i], mstep, w, h, MVS_INTER_CUBIC, white,
-                                sb[f].rect[i], (size_t)w * 3);
+    {
+        auto sstep_of = [&](const mvs_frame_desc* d) { return d->inputs_on_device ? d->sstep : (size_t)d->sw * 3; };
+        auto mstep_of = [&](const mvs_frame_desc* d) { return d->maps_on_device ? d->mstep : (size_t)w * 4; };
+        bool same_geometry = true;  // then all sensors of the batch go through one launch
+        for (int f = 1; f < n_frames; ++f)
+            same_geometry = same_geometry && descs[f].sw == d0.sw && descs[f].sh == d0.sh && sstep_of(descs + f) == sstep_of(&d0) &&
+                            mstep_of(descs + f) == mstep_of(&d0);
+        if (same_geometry) {
+            const uint8_t* ps[2 * MVS_MAX_BATCH];
+            const float *px[2 * MVS_MAX_BATCH], *py[2 * MVS_MAX_BATCH];
+            uint8_t* pd[2 * MVS_MAX_BATCH];
+            for (int f = 0; f < n_frames; ++f)
+                for (int i = 0; i < 2; ++i) {
+                    ps[2 * f + i] = sensor[f][i]; px[2 * f + i] = mapx[f][i]; py[2 * f + i] = mapy[f][i]; pd[2 * f + i] = sb[f].rect[i];
+                }
+            rc = remap_cubic_bgr8_batch_dev(ctx, 2 * n_frames, ps, d0.sw, d0.sh, sstep_of(&d0), px, py, mstep_of(&d0), w, h, white, pd,
+                                            (size_t)w * 3);
+        } else {
+            for (int f = 0; f < n_frames && !rc; ++f) {
+                const mvs_frame_desc* d = descs + f;
+                for (int i = 0; i < 2 && !rc; ++i)
+                    rc = remap_bgr8_dev(ctx, sensor[f][i], d->sw, d->sh, sstep_of(d), mapx[f][i], mapy[f][i], mstep_of(d), w, h, MVS_INTER_CUBIC,
+                                        white, sb[f].rect[i], (size_t)w * 3);
+            }
+        }
     }
     stage_end(ctx, "rectify");
     stage_begin(ctx, "presmooth");

@@ -155,8 +155,8 @@ __device__ __forceinline__ int dp2a_hi_su(uint32_t a, uint32_t b, int c)
     return d;
 }
 
-__global__ void __launch_bounds__(256)
-remap_cubic_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t sstep, const float* __restrict__ mapx,
+__device__ __forceinline__ void
+remap_cubic_bgr8_body(const uint8_t* __restrict__ src, int sw, int sh, size_t sstep, const float* __restrict__ mapx,
                         const float* __restrict__ mapy, size_t mstep, int w, int h, const int16_t* __restrict__ tab,
                         int b0, int b1, int b2, uint8_t* __restrict__ dst, size_t dstep, bool aligned4)
 {
@@ -222,6 +222,28 @@ remap_cubic_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t 
     d[0] = (uint8_t)max(0, min(255, (s0 + (1 << 14)) >> 15));
     d[1] = (uint8_t)max(0, min(255, (s1 + (1 << 14)) >> 15));
     d[2] = (uint8_t)max(0, min(255, (s2 + (1 << 14)) >> 15));
+}
+
+__global__ void __launch_bounds__(256)
+remap_cubic_bgr8_kernel(const uint8_t* __restrict__ src, int sw, int sh, size_t sstep, const float* __restrict__ mapx,
+                        const float* __restrict__ mapy, size_t mstep, int w, int h, const int16_t* __restrict__ tab,
+                        int b0, int b1, int b2, uint8_t* __restrict__ dst, size_t dstep, bool aligned4)
+{
+    remap_cubic_bgr8_body(src, sw, sh, sstep, mapx, mapy, mstep, w, h, tab, b0, b1, b2, dst, dstep, aligned4);
+}
+// batched: image blockIdx.z of up to 32 equally sized sensor images (one launch for all sensors of a frame batch)
+struct RemapBatch {
+    const uint8_t* src[32];
+    const float* mapx[32];
+    const float* mapy[32];
+    uint8_t* dst[32];
+};
+__global__ void __launch_bounds__(256)
+remap_cubic_bgr8_batch_kernel(RemapBatch b, int sw, int sh, size_t sstep, size_t mstep, int w, int h, const int16_t* __restrict__ tab,
+                              int b0, int b1, int b2, size_t dstep, bool aligned4)
+{
+    const int z = blockIdx.z;
+    remap_cubic_bgr8_body(b.src[z], sw, sh, sstep, b.mapx[z], b.mapy[z], mstep, w, h, tab, b0, b1, b2, b.dst[z], dstep, aligned4);
 }
 
 // INTER_NEAREST: cvRound + saturate_cast<short> of the coordinates, copy or border
@@ -316,6 +338,26 @@ int remap_bgr8_dev(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sste
                                                            ctx->cubic_tab_dev, border[0], border[1], border[2], dst, dstep,
                                                            ((uintptr_t)src & 3) == 0);
     MVS_LAUNCH_CHECK(ctx, "remap_cubic_bgr8_kernel");
+    return MVS_OK;
+}
+
+// n (<= 32) sensor images of equal geometry, INTER_CUBIC, one launch
+int remap_cubic_bgr8_batch_dev(mvs_ctx* ctx, int n, const uint8_t* const* src, int sw, int sh, size_t sstep, const float* const* mapx,
+                               const float* const* mapy, size_t mstep, int w, int h, const uint8_t border[3], uint8_t* const* dst,
+                               size_t dstep)
+{
+    if (n < 1 || n > 32) return mvs_fail(ctx, MVS_ERR_ARG, "remap batch of %d images (1..32)", n);
+    int rc = ensure_cubic_tab(ctx);
+    if (rc) return rc;
+    RemapBatch b;
+    bool aligned = true;
+    for (int i = 0; i < n; ++i) {
+        b.src[i] = src[i]; b.mapx[i] = mapx[i]; b.mapy[i] = mapy[i]; b.dst[i] = dst[i];
+        aligned = aligned && ((uintptr_t)src[i] & 3) == 0;
+    }
+    remap_cubic_bgr8_batch_kernel<<<dim3(cdiv(w, 32), cdiv(h, 8), n), 256, 0, ctx->stream>>>(b, sw, sh, sstep, mstep, w, h, ctx->cubic_tab_dev,
+                                                                                        border[0], border[1], border[2], dstep, aligned);
+    MVS_LAUNCH_CHECK(ctx, "remap_cubic_bgr8_batch_kernel");
     return MVS_OK;
 }
 

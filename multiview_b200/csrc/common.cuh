@@ -133,4 +133,6 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
 int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
                              int16_t* const* disp16, int16_t* raw16_tap /* F == 1 only */);
 int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16);
+int sgbm_wta_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, int F, int16_t* const* S, int16_t* const* disp16);
+int disp_to_float_batch_dev(mvs_ctx* ctx, int F, int16_t* const* d16, int w, int h, float* const* out);
 int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, const int16_t* raw16, int16_t* disp16);

@@ -160,9 +160,14 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         rc = sgbm_compute16_batch_dev(ctx, &d0.sgbm, n_frames, l, r, w, h, d16, nullptr);
     }
     stage_begin(ctx, "cloud");
+    if (!rc) {
+        int16_t* d16[MVS_MAX_BATCH];
+        float* df[MVS_MAX_BATCH];
+        for (int f = 0; f < n_frames; ++f) { d16[f] = sb[f].disp16; df[f] = sb[f].dispf; }
+        rc = disp_to_float_batch_dev(ctx, n_frames, d16, w, h, df);
+    }
     for (int f = 0; f < n_frames && !rc; ++f) {
-        rc = disp_to_float_dev(ctx, sb[f].disp16, w, h, sb[f].dispf);
-        if (!rc) rc = point_cloud_dev(ctx, &descs[f].bcam, sb[f].dispf, w, h, 1, sb[f].Xs, sb[f].xy, sb[f].lookup, sb[f].nd, sb[f].cen);
+        rc = point_cloud_dev(ctx, &descs[f].bcam, sb[f].dispf, w, h, 1, sb[f].Xs, sb[f].xy, sb[f].lookup, sb[f].nd, sb[f].cen);
     }
     stage_end(ctx, "cloud");
     stage_begin(ctx, "hist");

@@ -47,6 +47,12 @@ int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, cons
     stage_end(ctx, "aggregate");
     if (rc) return rc;
     // F == 1: "wta" and "post" are timed separately; a batch times both under "wta"
+    if (F > 1) {
+        stage_begin(ctx, "wta");
+        rc = sgbm_wta_post_batch_dev(ctx, g, p, F, S, disp16);
+        stage_end(ctx, "wta");
+        return rc;
+    }
     stage_begin(ctx, "wta");
     for (int f = 0; f < F && !rc; ++f) {
         rc = sgbm_wta_dev(ctx, g, S[f], raw);

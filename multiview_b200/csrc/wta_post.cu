@@ -92,7 +92,7 @@ wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_
     }
 }
 
-__global__ void wta_init_kernel(int16_t* raw, uint32_t* disp2key, size_t n, int inv)
+__device__ __forceinline__ void wta_init_body(int16_t* raw, uint32_t* disp2key, size_t n, int inv)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -101,7 +101,7 @@ __global__ void wta_init_kernel(int16_t* raw, uint32_t* disp2key, size_t n, int 
 }
 
 // left-right check (A.2), in place on raw
-__global__ void lr_check_kernel(int16_t* __restrict__ raw, const uint32_t* __restrict__ disp2key, SgbmGeom g)
+__device__ __forceinline__ void lr_check_body(int16_t* __restrict__ raw, const uint32_t* __restrict__ disp2key, const SgbmGeom& g)
 {
     int x = blockIdx.x * blockDim.x + threadIdx.x + g.minX1, y = blockIdx.y;
     if (x >= g.minX1 + g.W1) return;
@@ -124,7 +124,7 @@ __global__ void lr_check_kernel(int16_t* __restrict__ raw, const uint32_t* __res
 
 // ---- 3x3 median on s16, replicate border (cv::medianBlur) ---------------------------------------------
 __device__ __forceinline__ void cswap(int& a, int& b) { int t = min(a, b); b = max(a, b); a = t; }
-__global__ void median3_kernel(const int16_t* __restrict__ src, int W, int H, int16_t* __restrict__ dst)
+__device__ __forceinline__ void median3_body(const int16_t* __restrict__ src, int W, int H, int16_t* __restrict__ dst)
 {
     int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
     if (x >= W) return;
@@ -177,8 +177,8 @@ __device__ __forceinline__ void uf_union(int* L, int a, int b)
     }
 }
 // one warp per row: L[i] = index of the first pixel of i's run, cnt[run start] = run length
-__global__ void __launch_bounds__(256)
-speckle_runs_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* __restrict__ L,
+__device__ __forceinline__ void
+speckle_runs_body(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* __restrict__ L,
                     int* __restrict__ cnt)
 {
     const int lane = threadIdx.x & 31;
@@ -212,7 +212,7 @@ speckle_runs_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, i
         prev_last = __shfl_sync(0xffffffffu, v, 31);
     }
 }
-__global__ void speckle_merge_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L)
+__device__ __forceinline__ void speckle_merge_body(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y + 1;
     if (x >= W || y >= H) return;
@@ -226,7 +226,7 @@ __global__ void speckle_merge_kernel(const int16_t* __restrict__ img, int W, int
     uf_union(L, L[i], L[i - W]);
 }
 // every run start adds its run length to its component's root and then points straight at it
-__global__ void speckle_resolve_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L, int* cnt)
+__device__ __forceinline__ void speckle_resolve_body(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L, int* cnt)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
     if (x >= W) return;
@@ -241,8 +241,8 @@ __global__ void speckle_resolve_kernel(const int16_t* __restrict__ img, int W, i
         L[i] = root;
     }
 }
-__global__ void speckle_apply_kernel(int16_t* img, size_t n, int newVal, int maxSize, const int* __restrict__ L,
-                                     const int* __restrict__ cnt)
+__device__ __forceinline__ void speckle_apply_body(int16_t* img, size_t n, int newVal, int maxSize, const int* __restrict__ L,
+                                                   const int* __restrict__ cnt)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || img[i] == newVal) return;
@@ -250,13 +250,77 @@ __global__ void speckle_apply_kernel(int16_t* img, size_t n, int newVal, int max
     if (cnt[root] <= maxSize) img[i] = (int16_t)newVal;
 }
 
-__global__ void disp_to_float_kernel(const int16_t* __restrict__ d, size_t n, float* __restrict__ out)
+__device__ __forceinline__ void disp_to_float_body(const int16_t* __restrict__ d, size_t n, float* __restrict__ out)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float v = fabsf((float)d[i]) / 16.0f;
     out[i] = v > 150.0f ? 0.0f : v;
 }
+
+// ---- launchable forms: one image, or the images of a whole batch (blockIdx.z = frame) ----------------------------------
+__global__ void wta_init_kernel(int16_t* raw, uint32_t* disp2key, size_t n, int inv) { wta_init_body(raw, disp2key, n, inv); }
+__global__ void lr_check_kernel(int16_t* __restrict__ raw, const uint32_t* __restrict__ disp2key, SgbmGeom g) { lr_check_body(raw, disp2key, g); }
+__global__ void median3_kernel(const int16_t* __restrict__ src, int W, int H, int16_t* __restrict__ dst) { median3_body(src, W, H, dst); }
+__global__ void __launch_bounds__(256)
+speckle_runs_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* __restrict__ L, int* __restrict__ cnt)
+{
+    speckle_runs_body(img, W, H, newVal, maxDiff, L, cnt);
+}
+__global__ void speckle_merge_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L)
+{
+    speckle_merge_body(img, W, H, newVal, maxDiff, L);
+}
+__global__ void speckle_resolve_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L, int* cnt)
+{
+    speckle_resolve_body(img, W, H, newVal, maxDiff, L, cnt);
+}
+__global__ void speckle_apply_kernel(int16_t* img, size_t n, int newVal, int maxSize, const int* __restrict__ L, const int* __restrict__ cnt)
+{
+    speckle_apply_body(img, n, newVal, maxSize, L, cnt);
+}
+__global__ void disp_to_float_kernel(const int16_t* __restrict__ d, size_t n, float* __restrict__ out) { disp_to_float_body(d, n, out); }
+
+// Batched: raw / disp2key / L / cnt of frame z are slices of one buffer (stride n = W*H); the disparity images are the
+// callers' own buffers, handed over as a pointer table.
+struct PostBatch {
+    int16_t* disp16[MVS_MAX_BATCH];
+    float* dispf[MVS_MAX_BATCH];
+};
+__global__ void wta_init_batch_kernel(int16_t* raw, uint32_t* disp2key, size_t n, int inv)
+{
+    wta_init_body(raw + blockIdx.z * n, disp2key + blockIdx.z * n, n, inv);
+}
+__global__ void lr_check_batch_kernel(int16_t* __restrict__ raw, const uint32_t* __restrict__ disp2key, SgbmGeom g)
+{
+    const size_t n = (size_t)g.W * g.H;
+    lr_check_body(raw + blockIdx.z * n, disp2key + blockIdx.z * n, g);
+}
+__global__ void median3_batch_kernel(const int16_t* __restrict__ raw, int W, int H, PostBatch b)
+{
+    median3_body(raw + (size_t)blockIdx.z * W * H, W, H, b.disp16[blockIdx.z]);
+}
+__global__ void __launch_bounds__(256)
+speckle_runs_batch_kernel(PostBatch b, int W, int H, int newVal, int maxDiff, int* __restrict__ L, int* __restrict__ cnt)
+{
+    const size_t n = (size_t)W * H;
+    speckle_runs_body(b.disp16[blockIdx.z], W, H, newVal, maxDiff, L + blockIdx.z * n, cnt + blockIdx.z * n);
+}
+__global__ void speckle_merge_batch_kernel(PostBatch b, int W, int H, int newVal, int maxDiff, int* L)
+{
+    speckle_merge_body(b.disp16[blockIdx.z], W, H, newVal, maxDiff, L + (size_t)blockIdx.z * W * H);
+}
+__global__ void speckle_resolve_batch_kernel(PostBatch b, int W, int H, int newVal, int maxDiff, int* L, int* cnt)
+{
+    const size_t n = (size_t)W * H;
+    speckle_resolve_body(b.disp16[blockIdx.z], W, H, newVal, maxDiff, L + blockIdx.z * n, cnt + blockIdx.z * n);
+}
+__global__ void speckle_apply_batch_kernel(PostBatch b, size_t n, int newVal, int maxSize, const int* __restrict__ L,
+                                           const int* __restrict__ cnt)
+{
+    speckle_apply_body(b.disp16[blockIdx.z], n, newVal, maxSize, L + blockIdx.z * n, cnt + blockIdx.z * n);
+}
+__global__ void disp_to_float_batch_kernel(PostBatch b, size_t n) { disp_to_float_body(b.disp16[blockIdx.z], n, b.dispf[blockIdx.z]); }
 
 int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16)
 {
@@ -297,6 +361,62 @@ int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, con
         speckle_apply_kernel<<<cdiv(n, 256), 256, 0, s>>>(disp16, n, g.INV, p->speckle_win, L, cnt);
         MVS_LAUNCH_CHECK_N(ctx, "speckle kernels", 4);
     }
+    return MVS_OK;
+}
+
+// WTA + LR check + median + speckle filter for the F frames of a batch: the small per-image kernels run once per batch
+// (blockIdx.z = frame), only the WTA scan of the S volumes stays one launch per frame.
+int sgbm_wta_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, int F, int16_t* const* S, int16_t* const* disp16)
+{
+    cudaStream_t s = ctx->stream;
+    const size_t n = (size_t)g.W * g.H;
+    MVS_ARENA(ctx, int16_t, raw, "sgbm.batch.raw", n * F);
+    MVS_ARENA(ctx, uint32_t, d2, "sgbm.batch.disp2key", n * F);
+    PostBatch b;
+    memset(&b, 0, sizeof(b));
+    for (int f = 0; f < F; ++f) b.disp16[f] = disp16[f];
+    wta_init_batch_kernel<<<dim3(cdiv(n, 256), 1, F), 256, 0, s>>>(raw, d2, n, g.INV);
+    MVS_LAUNCH_CHECK(ctx, "wta_init_batch_kernel");
+    const int blocks = cdiv((long long)g.W1 * g.H, 8 * WTA_PPW);
+    const uint32_t udiv = (uint32_t)(100 - g.ur);
+    const uint32_t ur_magic = udiv <= 1 ? 0u : (uint32_t)(((1ull << 32) + udiv - 1) / udiv);
+    for (int f = 0; f < F; ++f) {
+        int16_t* rf = raw + n * f;
+        uint32_t* df = d2 + n * f;
+        switch (g.Dp / 64) {
+        case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df); break;
+        case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df); break;
+        case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df); break;
+        case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df); break;
+        default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
+        }
+        MVS_LAUNCH_CHECK(ctx, "wta_kernel");
+    }
+    lr_check_batch_kernel<<<dim3(cdiv(g.W1, 128), g.H, F), 128, 0, s>>>(raw, d2, g);
+    median3_batch_kernel<<<dim3(cdiv(g.W, 128), g.H, F), 128, 0, s>>>(raw, g.W, g.H, b);
+    MVS_LAUNCH_CHECK_N(ctx, "lr_check / median3 batch kernels", 2);
+    if (p->speckle_win > 0) {
+        MVS_ARENA(ctx, int, L, "sgbm.batch.speckle.label", n * F);
+        MVS_ARENA(ctx, int, cnt, "sgbm.batch.speckle.count", n * F);
+        const int maxDiff = 16 * p->speckle_range;
+        MVS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int) * n * F, s));
+        speckle_runs_batch_kernel<<<dim3(cdiv(g.H, 8), 1, F), 256, 0, s>>>(b, g.W, g.H, g.INV, maxDiff, L, cnt);
+        if (g.H > 1) speckle_merge_batch_kernel<<<dim3(cdiv(g.W, 128), g.H - 1, F), 128, 0, s>>>(b, g.W, g.H, g.INV, maxDiff, L);
+        speckle_resolve_batch_kernel<<<dim3(cdiv(g.W, 128), g.H, F), 128, 0, s>>>(b, g.W, g.H, g.INV, maxDiff, L, cnt);
+        speckle_apply_batch_kernel<<<dim3(cdiv(n, 256), 1, F), 256, 0, s>>>(b, n, g.INV, p->speckle_win, L, cnt);
+        MVS_LAUNCH_CHECK_N(ctx, "speckle batch kernels", 4);
+    }
+    return MVS_OK;
+}
+
+int disp_to_float_batch_dev(mvs_ctx* ctx, int F, int16_t* const* d16, int w, int h, float* const* out)
+{
+    PostBatch b;
+    memset(&b, 0, sizeof(b));
+    for (int f = 0; f < F; ++f) { b.disp16[f] = d16[f]; b.dispf[f] = out[f]; }
+    const size_t n = (size_t)w * h;
+    disp_to_float_batch_kernel<<<dim3(cdiv(n, 256), 1, F), 256, 0, ctx->stream>>>(b, n);
+    MVS_LAUNCH_CHECK(ctx, "disp_to_float_batch_kernel");
     return MVS_OK;
 }
 

@@ -66,8 +66,8 @@ __device__ __forceinline__ V3 solve3d(const mvs_bcam& b, double x0, double x1, d
 
 __device__ __forceinline__ bool pc_valid(float dx) { return isfinite(dx) && dx != 0.0f; }
 
-__global__ void __launch_bounds__(PC_BLOCK)
-pc_count_kernel(const float* __restrict__ disp, size_t n, int* __restrict__ block_counts)
+__device__ __forceinline__ void
+pc_count_body(const float* __restrict__ disp, size_t n, int* __restrict__ block_counts)
 {
     __shared__ int wsum[PC_BLOCK / 32];
     size_t base = (size_t)blockIdx.x * PC_TILE;
@@ -88,7 +88,7 @@ pc_count_kernel(const float* __restrict__ disp, size_t n, int* __restrict__ bloc
 }
 
 // single block: exclusive scan of block_counts -> block_offsets, total -> *n_out
-__global__ void __launch_bounds__(1024) pc_scan_kernel(const int* __restrict__ counts, int nb, int* __restrict__ offsets, int* n_out)
+__device__ __forceinline__ void pc_scan_body(const int* __restrict__ counts, int nb, int* __restrict__ offsets, int* n_out)
 {
     __shared__ int wsum[32];
     __shared__ int carry;
@@ -125,8 +125,8 @@ __global__ void __launch_bounds__(1024) pc_scan_kernel(const int* __restrict__ c
     if (threadIdx.x == 0) *n_out = carry;
 }
 
-__global__ void __launch_bounds__(PC_BLOCK)
-pc_emit_kernel(const float* __restrict__ disp, int w, size_t n, mvs_bcam bcam, int left_is_ref,
+__device__ __forceinline__ void
+pc_emit_body(const float* __restrict__ disp, int w, size_t n, const mvs_bcam& bcam, int left_is_ref,
                const int* __restrict__ block_offsets, double* __restrict__ Xs, int32_t* __restrict__ xy,
                int32_t* __restrict__ lookup, double* __restrict__ partial)
 {
@@ -187,7 +187,7 @@ pc_emit_kernel(const float* __restrict__ disp, int w, size_t n, mvs_bcam bcam, i
     }
 }
 
-__global__ void __launch_bounds__(256) pc_centroid_kernel(const double* __restrict__ partial, int nb, const int* n_dev, double* centroid)
+__device__ __forceinline__ void pc_centroid_body(const double* __restrict__ partial, int nb, const int* n_dev, double* centroid)
 {
     __shared__ double sh[256][3];
     double s[3] = {0, 0, 0};
@@ -201,6 +201,83 @@ __global__ void __launch_bounds__(256) pc_centroid_kernel(const double* __restri
         __syncthreads();
     }
     if (threadIdx.x < 3) centroid[threadIdx.x] = sh[0][threadIdx.x] / (double)(*n_dev);  // N == 0 -> NaN, as the reference
+}
+
+// launchable forms: one frame ...
+__global__ void __launch_bounds__(PC_BLOCK)
+pc_count_kernel(const float* __restrict__ disp, size_t n, int* __restrict__ block_counts) { pc_count_body(disp, n, block_counts); }
+__global__ void __launch_bounds__(1024) pc_scan_kernel(const int* __restrict__ counts, int nb, int* __restrict__ offsets, int* n_out)
+{
+    pc_scan_body(counts, nb, offsets, n_out);
+}
+__global__ void __launch_bounds__(PC_BLOCK)
+pc_emit_kernel(const float* __restrict__ disp, int w, size_t n, mvs_bcam bcam, int left_is_ref,
+               const int* __restrict__ block_offsets, double* __restrict__ Xs, int32_t* __restrict__ xy,
+               int32_t* __restrict__ lookup, double* __restrict__ partial)
+{
+    pc_emit_body(disp, w, n, bcam, left_is_ref, block_offsets, Xs, xy, lookup, partial);
+}
+__global__ void __launch_bounds__(256) pc_centroid_kernel(const double* __restrict__ partial, int nb, const int* n_dev, double* centroid)
+{
+    pc_centroid_body(partial, nb, n_dev, centroid);
+}
+// ... or the frames of a batch (frame = blockIdx.y, or blockIdx.x for the single-block steps); the per-frame
+// pointers and calibration sit in a small device table
+struct CloudFrame {
+    const float* disp;
+    double* Xs;
+    int32_t* xy;
+    int32_t* lookup;
+    int32_t* n_dev;
+    double* centroid;
+    mvs_bcam bcam;
+};
+__global__ void __launch_bounds__(PC_BLOCK)
+pc_count_batch_kernel(const CloudFrame* __restrict__ fr, size_t n, int nb, int* __restrict__ counts)
+{
+    pc_count_body(fr[blockIdx.y].disp, n, counts + (size_t)blockIdx.y * nb);
+}
+__global__ void __launch_bounds__(1024) pc_scan_batch_kernel(const CloudFrame* __restrict__ fr, int nb, const int* __restrict__ counts, int* __restrict__ offsets)
+{
+    pc_scan_body(counts + (size_t)blockIdx.x * nb, nb, offsets + (size_t)blockIdx.x * nb, fr[blockIdx.x].n_dev);
+}
+__global__ void __launch_bounds__(PC_BLOCK)
+pc_emit_batch_kernel(const CloudFrame* __restrict__ fr, int w, size_t n, int nb, int left_is_ref, const int* __restrict__ offsets,
+                     double* __restrict__ partial)
+{
+    const CloudFrame& f = fr[blockIdx.y];
+    pc_emit_body(f.disp, w, n, f.bcam, left_is_ref, offsets + (size_t)blockIdx.y * nb, f.Xs, f.xy, f.lookup,
+                 partial + (size_t)blockIdx.y * nb * 3);
+}
+__global__ void __launch_bounds__(256) pc_centroid_batch_kernel(const CloudFrame* __restrict__ fr, int nb, const double* __restrict__ partial)
+{
+    pc_centroid_body(partial + (size_t)blockIdx.x * nb * 3, nb, fr[blockIdx.x].n_dev, fr[blockIdx.x].centroid);
+}
+
+int point_cloud_batch_dev(mvs_ctx* ctx, int F, const mvs_bcam* const* bcam, const float* const* disp, int w, int h, int left_is_ref,
+                          double* const* Xs, int32_t* const* xy, int32_t* const* lookup, int32_t* const* n_dev, double* const* centroid_dev)
+{
+    if (F < 1 || F > MVS_MAX_BATCH) return mvs_fail(ctx, MVS_ERR_ARG, "point cloud batch of %d frames", F);
+    cudaStream_t s = ctx->stream;
+    const size_t n = (size_t)w * h;
+    const int nb = cdiv(n, PC_TILE);
+    MVS_ARENA(ctx, int, counts, "cloud.batch.counts", (size_t)nb * F);
+    MVS_ARENA(ctx, int, offsets, "cloud.batch.offsets", (size_t)nb * F);
+    MVS_ARENA(ctx, double, partial, "cloud.batch.partial", (size_t)nb * 3 * F);
+    MVS_ARENA(ctx, CloudFrame, table, "cloud.batch.table", MVS_MAX_BATCH);
+    CloudFrame host[MVS_MAX_BATCH];
+    for (int f = 0; f < F; ++f) {
+        host[f].disp = disp[f]; host[f].Xs = Xs[f]; host[f].xy = xy[f]; host[f].lookup = lookup[f];
+        host[f].n_dev = n_dev[f]; host[f].centroid = centroid_dev[f]; host[f].bcam = *bcam[f];
+    }
+    // pageable source: the runtime stages it before returning, so the stack array may go out of scope
+    MVS_CUDA(ctx, cudaMemcpyAsync(table, host, sizeof(CloudFrame) * F, cudaMemcpyHostToDevice, s));
+    pc_count_batch_kernel<<<dim3(nb, F), PC_BLOCK, 0, s>>>(table, n, nb, counts);
+    pc_scan_batch_kernel<<<F, 1024, 0, s>>>(table, nb, counts, offsets);
+    pc_emit_batch_kernel<<<dim3(nb, F), PC_BLOCK, 0, s>>>(table, w, n, nb, left_is_ref, offsets, partial);
+    pc_centroid_batch_kernel<<<F, 256, 0, s>>>(table, nb, partial);
+    MVS_LAUNCH_CHECK_N(ctx, "point cloud batch kernels", 4);
+    return MVS_OK;
 }
 
 int point_cloud_dev(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, int w, int h, int left_is_ref, double* Xs,

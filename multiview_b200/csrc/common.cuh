@@ -109,6 +109,8 @@ int presmooth_dev(mvs_ctx* ctx, const char* tag, const uint8_t* src, int channel
 int sgbm_compute16_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
                        int16_t* disp16, int16_t* raw16 /* optional pre-median tap */);
 int disp_to_float_dev(mvs_ctx* ctx, const int16_t* d16, int w, int h, float* out);
+int point_cloud_batch_dev(mvs_ctx* ctx, int F, const mvs_bcam* const* bcam, const float* const* disp, int w, int h, int left_is_ref,
+                          double* const* Xs, int32_t* const* xy, int32_t* const* lookup, int32_t* const* n_dev, double* const* centroid_dev);
 int point_cloud_dev(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, int w, int h, int left_is_ref, double* Xs,
                     int32_t* xy, int32_t* lookup, int32_t* n_dev, double* centroid_dev);
 int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],

@@ -62,7 +62,7 @@ __device__ __forceinline__ int pre_q(const uint8_t* __restrict__ r, int x, int W
     return (x <= 0 || x >= W - 1) ? ftzero : (int)r[x];
 }
 
-__global__ void prefilter_kernel(const uint8_t* __restrict__ img, int W, int H, int ftzero, uint8_t* __restrict__ planes)
+__device__ __forceinline__ void prefilter_body(const uint8_t* __restrict__ img, int W, int H, int ftzero, uint8_t* __restrict__ planes)
 {
     int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
     if (x >= W) return;
@@ -80,6 +80,17 @@ __global__ void prefilter_kernel(const uint8_t* __restrict__ img, int W, int H, 
     planes[3 * plane + o] = (uint8_t)qc;
     planes[4 * plane + o] = (uint8_t)min(qc, min(ql, qr));
     planes[5 * plane + o] = (uint8_t)max(qc, max(ql, qr));
+}
+
+__global__ void prefilter_kernel(const uint8_t* __restrict__ img, int W, int H, int ftzero, uint8_t* __restrict__ planes)
+{
+    prefilter_body(img, W, H, ftzero, planes);
+}
+// all images of a batch in one launch: image z (left images 0..F-1, right images F..2F-1) -> planes + z * 6 * W * H
+struct PrefilterBatch { const uint8_t* img[2 * MVS_MAX_BATCH]; };
+__global__ void prefilter_batch_kernel(PrefilterBatch b, int W, int H, int ftzero, uint8_t* __restrict__ planes)
+{
+    prefilter_body(b.img[blockIdx.z], W, H, ftzero, planes + (size_t)blockIdx.z * 6 * W * H);
 }
 
 // ---- per-pixel BT cost + horizontal box sum ------------------------------------------------------------------
@@ -321,20 +332,22 @@ int sgbm_cost_volume_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const uin
 {
     cudaStream_t s = ctx->stream;
     const size_t plane = (size_t)g.W * g.H;
-    MVS_ARENA(ctx, uint8_t, planes, "sgbm.planes", plane * 12);
+    MVS_ARENA(ctx, uint8_t, planes, "sgbm.planes", plane * 12 * F);   // [left images][right images] x 6 planes
     uint16_t* hsum[2];
     hsum[0] = (uint16_t*)arena_get(ctx, "sgbm.hsum", g.cells() * 2);
     hsum[1] = F > 1 ? (uint16_t*)arena_get(ctx, "sgbm.hsum.1", g.cells() * 2) : hsum[0];
     if (!hsum[0] || !hsum[1]) return MVS_ERR_NOMEM;
-    dim3 pg(cdiv(g.W, 128), g.H);
+    {
+        PrefilterBatch pb;
+        for (int f = 0; f < F; ++f) { pb.img[f] = l[f]; pb.img[F + f] = r[f]; }
+        prefilter_batch_kernel<<<dim3(cdiv(g.W, 128), g.H, 2 * F), 128, 0, s>>>(pb, g.W, g.H, g.ftzero, planes);
+        MVS_LAUNCH_CHECK(ctx, "prefilter_batch_kernel");
+    }
     for (int k = 0; k <= F; ++k) {
         CostJob j;
         memset(&j, 0, sizeof(j));
         if (k < F) {
-            prefilter_kernel<<<pg, 128, 0, s>>>(l[k], g.W, g.H, g.ftzero, planes);
-            prefilter_kernel<<<pg, 128, 0, s>>>(r[k], g.W, g.H, g.ftzero, planes + 6 * plane);
-            MVS_LAUNCH_CHECK_N(ctx, "prefilter_kernel", 2);
-            j.PL = planes; j.PR = planes + 6 * plane; j.hsum_out = (uint32_t*)hsum[k & 1];
+            j.PL = planes + (size_t)k * 6 * plane; j.PR = planes + (size_t)(F + k) * 6 * plane; j.hsum_out = (uint32_t*)hsum[k & 1];
         }
         if (k > 0) { j.hsum_in = (const uint32_t*)hsum[(k - 1) & 1]; j.C = (uint32_t*)C[k - 1]; }
         int rc = launch_cost_win(ctx, g, j, k < F, k > 0);

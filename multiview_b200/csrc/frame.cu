@@ -166,8 +166,16 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         for (int f = 0; f < n_frames; ++f) { d16[f] = sb[f].disp16; df[f] = sb[f].dispf; }
         rc = disp_to_float_batch_dev(ctx, n_frames, d16, w, h, df);
     }
-    for (int f = 0; f < n_frames && !rc; ++f) {
-        rc = point_cloud_dev(ctx, &descs[f].bcam, sb[f].dispf, w, h, 1, sb[f].Xs, sb[f].xy, sb[f].lookup, sb[f].nd, sb[f].cen);
+    if (!rc) {
+        const mvs_bcam* pb[MVS_MAX_BATCH];
+        const float* pdisp[MVS_MAX_BATCH];
+        double *pX[MVS_MAX_BATCH], *pc[MVS_MAX_BATCH];
+        int32_t *pxy[MVS_MAX_BATCH], *plk[MVS_MAX_BATCH], *pn[MVS_MAX_BATCH];
+        for (int f = 0; f < n_frames; ++f) {
+            pb[f] = &descs[f].bcam; pdisp[f] = sb[f].dispf; pX[f] = sb[f].Xs; pxy[f] = sb[f].xy; plk[f] = sb[f].lookup;
+            pn[f] = sb[f].nd; pc[f] = sb[f].cen;
+        }
+        rc = point_cloud_batch_dev(ctx, n_frames, pb, pdisp, w, h, 1, pX, pxy, plk, pn, pc);
     }
     stage_end(ctx, "cloud");
     stage_begin(ctx, "hist");

@@ -107,9 +107,14 @@ __global__ void prefilter_batch_kernel(PrefilterBatch b, int W, int H, int ftzer
 #define COST_K2 0x04000400u
 template <int WIN, int NW>
 struct CostTile {
-    static constexpr int HALF = 32 * NW;                       // disparity pairs = threads per row
-    static constexpr int ROWS = NW == 3 ? 1 : 128 / HALF;      // rows per block
-    static constexpr int THREADS = ROWS * HALF;
+    static constexpr int HALF = 32 * NW;                       // disparity pairs per row
+#ifndef COST_PPT
+#define COST_PPT 1   // measured at c2: 2 pairs per thread (shared left-image loads, 80 registers) 0.61 ms vs 0.53 ms with 1
+#endif
+    static constexpr int PPT = (NW % 2 == 0) ? COST_PPT : 1;   // pairs per thread (t and t + TPR): the left-image loads are shared
+    static constexpr int TPR = HALF / PPT;                     // threads per row
+    static constexpr int ROWS = NW == 3 ? 1 : 128 / TPR;       // rows per block
+    static constexpr int THREADS = ROWS * TPR;
     static constexpr int BODY = 2 * WIN;                       // steps per unrolled body (even, a multiple of the ring length)
     static constexpr int NS = BODY * ((128 + BODY - 1) / BODY);  // steps per tile
     static constexpr int SW = WIN / 2;
@@ -143,9 +148,9 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
                                                    uint32_t* __restrict__ hsum, int tile, int yblock)
 {
     using T = CostTile<WIN, NW>;
-    constexpr int NS = T::NS, SW = T::SW, HALF = T::HALF, KW = T::KW;
+    constexpr int NS = T::NS, SW = T::SW, HALF = T::HALF, KW = T::KW, PPT = T::PPT, TPR = T::TPR;
     extern __shared__ __align__(16) uint4 sm4[];
-    const int t = threadIdx.x % HALF, ry = threadIdx.x / HALF;
+    const int t = threadIdx.x % TPR, ry = threadIdx.x / TPR;
     const int y = yblock * T::ROWS + ry;
     const bool first = tile == 0;
     const int xs = first ? 0 : T::TX0 + (tile - 1) * T::TX - SW;   // virtual column of step 0
@@ -156,7 +161,7 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
     const int xmax = xs + NS + g.minX1 - g.minD;
     if (y < g.H) {
         const uint8_t* R = PR + (size_t)y * g.W;
-        for (int idx = t; idx < T::R4; idx += HALF) {
+        for (int idx = t; idx < T::R4; idx += TPR) {
             const int copy = idx / KW, kw = idx - copy * KW;
             const int k = 2 * kw + copy;
             const int xa = min(max(xmax - k, 0), g.W - 1), xb = min(max(xmax - k - 1, 0), g.W - 1);
@@ -170,7 +175,7 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
             myR[idx] = make_uint4(w[0], w[1], w[2], w[3]);
         }
         const uint8_t* L = PL + (size_t)y * g.W;
-        for (int idx = t; idx < T::L4; idx += HALF) {
+        for (int idx = t; idx < T::L4; idx += TPR) {
             const int k = idx >> 1, ch = idx & 1;
             const int x = min(max(xs + k, 0), g.W1 - 1) + g.minX1;
             const uint32_t u = L[(3 * ch) * plane + x], u0 = L[(3 * ch + 1) * plane + x], u1 = L[(3 * ch + 2) * plane + x];
@@ -179,22 +184,34 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
     }
     __syncthreads();
     if (y >= g.H) return;
-    const uint32_t padmask = (2 * t >= g.D ? 0u : 0xffffu) | (2 * t + 1 >= g.D ? 0u : 0xffff0000u);
-    const uint4* pR = myR + NS / 2 + t;   // element of step 0 (even copy)
+    uint32_t padmask[PPT];
+#pragma unroll
+    for (int q = 0; q < PPT; ++q) {
+        const int tq = t + q * TPR;   // this thread's q-th disparity pair
+        padmask[q] = (2 * tq >= g.D ? 0u : 0xffffu) | (2 * tq + 1 >= g.D ? 0u : 0xffff0000u);
+    }
+    const uint4* pR = myR + NS / 2 + t;   // element of step 0 (even copy) of pair t; pair t + TPR sits TPR elements further
     const uint4* pL = myL;
     const int nvalid = min(NS, g.W1 - xs);            // steps whose column lies inside the image
     const int nout = min(NS, g.W1 - xs + SW);         // steps that still produce an output column
     const int kmin = first ? SW : WIN - 1;            // first step with a complete window
-    uint32_t ring[WIN];
-    uint32_t hs = 0, pix = 0;
+    uint32_t ring[PPT][WIN];
+    uint32_t hs[PPT], pix[PPT];
 #pragma unroll
-    for (int i = 0; i < WIN; ++i) ring[i] = 0;
+    for (int q = 0; q < PPT; ++q) {
+        hs[q] = 0; pix[q] = 0;
+#pragma unroll
+        for (int i = 0; i < WIN; ++i) ring[q][i] = 0;
+    }
     if (first) {
         // columns -SW..-1 repeat column 0: they sit in the ring slots that leave the window at steps SW+1..WIN-1
-        const uint32_t pb = bt_pair_cost(pR[0], pL[0], pL[1]) & padmask;
 #pragma unroll
-        for (int i = SW + 1; i < WIN; ++i) ring[i] = pb;
-        hs = SW * pb;
+        for (int q = 0; q < PPT; ++q) {
+            const uint32_t pb = bt_pair_cost(pR[q * TPR], pL[0], pL[1]) & padmask[q];
+#pragma unroll
+            for (int i = SW + 1; i < WIN; ++i) ring[q][i] = pb;
+            hs[q] = SW * pb;
+        }
     }
     uint32_t* out = hsum + ((ptrdiff_t)y * g.W1 + (xs - SW)) * HALF + t;   // output column of step 0 (never stored when negative)
 #pragma unroll 1
@@ -204,10 +221,14 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
 #pragma unroll
             for (int i = 0; i < T::BODY; ++i) {
                 const uint4* r = pR + (i & 1) * KW - ((i + 1) >> 1);
-                pix = bt_pair_cost(r[0], pL[2 * i], pL[2 * i + 1]) & padmask;
-                hs = hs + pix - ring[i % WIN];
-                ring[i % WIN] = pix;
-                out[(size_t)i * HALF] = hs;
+                const uint4 l0 = pL[2 * i], l1 = pL[2 * i + 1];
+#pragma unroll
+                for (int q = 0; q < PPT; ++q) {
+                    pix[q] = bt_pair_cost(r[q * TPR], l0, l1) & padmask[q];
+                    hs[q] = hs[q] + pix[q] - ring[q][i % WIN];
+                    ring[q][i % WIN] = pix[q];
+                    out[(size_t)i * HALF + q * TPR] = hs[q];
+                }
             }
             pR -= T::BODY / 2;
             pL += 2 * T::BODY;
@@ -218,11 +239,15 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
         for (int i = 0; i < T::BODY; ++i) {
             const int k = kb + i;
             const uint4* r = pR + (i & 1) * KW - ((i + 1) >> 1);
-            const uint32_t c = bt_pair_cost(r[0], pL[2 * i], pL[2 * i + 1]) & padmask;
-            pix = k < nvalid ? c : pix;
-            hs = hs + pix - ring[i % WIN];
-            ring[i % WIN] = pix;
-            if (k >= kmin && k < nout) out[(size_t)i * HALF] = hs;
+            const uint4 l0 = pL[2 * i], l1 = pL[2 * i + 1];
+#pragma unroll
+            for (int q = 0; q < PPT; ++q) {
+                const uint32_t c = bt_pair_cost(r[q * TPR], l0, l1) & padmask[q];
+                pix[q] = k < nvalid ? c : pix[q];
+                hs[q] = hs[q] + pix[q] - ring[q][i % WIN];
+                ring[q][i % WIN] = pix[q];
+                if (k >= kmin && k < nout) out[(size_t)i * HALF + q * TPR] = hs[q];
+            }
         }
         pR -= T::BODY / 2;
         pL += 2 * T::BODY;

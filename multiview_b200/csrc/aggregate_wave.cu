@@ -29,10 +29,22 @@
 #include "common.cuh"
 
 #define SENT2 0x7FFF7FFFu
-#ifndef WAVE_R
-#define WAVE_R 15            // rows (compute warps) per band: with the helper 16 warps, four per scheduler
+// rows (compute warps) per band by disparity words per lane: with the helper a multiple of four warps (four
+// schedulers); narrower disparity ranges have smaller ring slots, so more rows fit and hide the per-pixel latency
+#ifndef WAVE_R4
+#define WAVE_R4 15           // Dp = 256: 16 warps
 #endif
-#define WAVE_THREADS ((WAVE_R + 1) * 32)
+#ifndef WAVE_R3
+#define WAVE_R3 19           // Dp = 192: 20 warps
+#endif
+#ifndef WAVE_R2
+#define WAVE_R2 27           // Dp = 128: 28 warps
+#endif
+#ifndef WAVE_R1
+#define WAVE_R1 15           // Dp = 64: 16 warps (31 rows measured slightly slower at 640x480)
+#endif
+template <int NW> struct WaveRows { static constexpr int R = NW == 4 ? WAVE_R4 : NW == 3 ? WAVE_R3 : NW == 2 ? WAVE_R2 : WAVE_R1; };
+static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw == 2 ? WAVE_R2 : WAVE_R1; }
 #ifndef WAVE_PUBLISH
 #define WAVE_PUBLISH 8       // inter-band progress is published every this many pixels
 #endif
@@ -155,10 +167,12 @@ struct Ring {
     static constexpr int ROW_SLOTS = 2 * D12 + D3;
     static constexpr int HD = 8;               // row above the band (helper): 8 slots per direction
     static constexpr int HELP_SLOTS = 3 * HD;
-    static constexpr int NSLOTS = HELP_SLOTS + WAVE_R * ROW_SLOTS;
+    static constexpr int R = WaveRows<NW>::R;  // rows per band
+    static constexpr int THREADS = (R + 1) * 32;
+    static constexpr int NSLOTS = HELP_SLOTS + R * ROW_SLOTS;
     static constexpr int WORDS = NSLOTS * SLOT;
     static constexpr int STAGE = 4;            // cp.async stages of the per-warp C (and S) stream
-    static constexpr int STREAM_WORDS = WAVE_R * STAGE * WPP;
+    static constexpr int STREAM_WORDS = R * STAGE * WPP;
 };
 
 template <int NW>
@@ -174,7 +188,7 @@ __device__ __forceinline__ void cp_async_lane(uint32_t smem_addr, const uint32_t
 }
 
 template <int NW, int DIRMASK, bool PAD, bool BWD>
-__global__ void __launch_bounds__(WAVE_THREADS, 1)
+__global__ void __launch_bounds__(Ring<NW>::THREADS, 1)
 wave_kernel(WaveParams p)
 {
     using RG = Ring<NW>;
@@ -185,6 +199,7 @@ wave_kernel(WaveParams p)
     __shared__ int s_item;
     // [ring row k][p mod NB]: "pixel p of ring row k written" (k = 0: by the helper, else by warp k-1) and
     // "pixel p of ring row k consumed" (by warp k); the pseudo-pixel W1 is the zero slot behind the row
+    constexpr int WAVE_R = RG::R;
     __shared__ __align__(8) uint64_t s_full[WAVE_R + 1][WAVE_NB];
     __shared__ __align__(8) uint64_t s_cons[WAVE_R + 1][WAVE_NB];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -486,12 +501,12 @@ static int launch_wave(mvs_ctx* ctx, const WaveParams& p)
     if (!per_sm) {
         MVS_CUDA(ctx, cudaFuncSetAttribute(wave_kernel<NW, DIRMASK, PAD, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         int n = 1;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wave_kernel<NW, DIRMASK, PAD, BWD>, WAVE_THREADS, smem);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wave_kernel<NW, DIRMASK, PAD, BWD>, Ring<NW>::THREADS, smem);
         per_sm = n < 1 ? 1 : n;
         per_sm_dev[dv] = per_sm;
     }
     int grid = min(p.nbands * p.F, ctx->sm_count * per_sm);
-    wave_kernel<NW, DIRMASK, PAD, BWD><<<grid, WAVE_THREADS, smem, ctx->stream>>>(p);
+    wave_kernel<NW, DIRMASK, PAD, BWD><<<grid, Ring<NW>::THREADS, smem, ctx->stream>>>(p);
     MVS_LAUNCH_CHECK(ctx, "wave_kernel");
     return MVS_OK;
 }
@@ -512,7 +527,7 @@ static int launch_wave_nw(mvs_ctx* ctx, const SgbmGeom& g, const WaveParams& p)
 int sgbm_aggregate_wave_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S)
 {
     if (F < 1 || F > MVS_MAX_BATCH) return mvs_fail(ctx, MVS_ERR_ARG, "aggregate: batch of %d frames (1..%d)", F, MVS_MAX_BATCH);
-    const int nbands = cdiv(g.H, WAVE_R);
+    const int nbands = cdiv(g.H, wave_rows(g.Dp / 64));
     const size_t wpp = (size_t)g.Dp / 2;
     const int ctl_pass = F * nbands + 2 * WAVE_CTL_PAD;
     const size_t bnd_sz = (size_t)nbands * g.W1 * 3 * (wpp + 4);

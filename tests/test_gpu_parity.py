@@ -321,3 +321,36 @@ def test_input_images_node(ctx):
         for eq in (True, False):
             got, want = api.input_images(img, eq, ctx=ctx), oracle.input_images(img, eq)
             assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+
+
+def test_frame_batch_with_mixed_sensor_sizes_and_blur(ctx):
+    """A batch whose frames differ in sensor size and presmooth sigma takes the per-image kernels instead of the
+    one-launch-per-batch ones: results must still equal the per-frame calls."""
+    W, H, D = 352, 150, 64
+    sp = _sp(D, 1)
+    hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
+    cams = [synth.make_camera(W, H, D, config=4, cam=c, n_cams=3) for c in range(3)]
+    # frame 1: sensor images padded to a wider, taller buffer (same maps: they address the original area)
+    pad = [np.ascontiguousarray(np.pad(s, ((0, 6), (0, 10), (0, 0)), mode="edge")) for s in cams[1]["sensor"]]
+    sigmas = [2.15, 2.15, 1.0]
+    descs = []
+    for i, c in enumerate(cams):
+        d = api.make_frame_desc(c, sp, hp, synth.HIST_AABB, sigma=sigmas[i])
+        if i == 1:
+            for k in range(2):
+                d.sensor[k] = pad[k].ctypes.data
+            d.sw, d.sh, d.sstep = W + 10, H + 6, (W + 10) * 3
+        descs.append(d)
+    single = []
+    for i, d in enumerate(descs):
+        res = api.frame_run(ctx, 20 + i, d)
+        single.append(api.frame_fetch(ctx, 20 + i, W, H, res.hw, res.hh))
+    res = api.frame_run_batch(ctx, 0, descs)
+    for i in range(len(descs)):
+        out = api.frame_fetch(ctx, i, W, H, res[i].hw, res[i].hh)
+        assert np.array_equal(out["disp"], single[i]["disp"]) and (out["disp"] > 0).mean() > 0.3
+        assert out["N"] == single[i]["N"] and np.array_equal(out["cam_hist"], single[i]["cam_hist"])
+    # the blur strength matters (frame 2 would differ with the default sigma)
+    d2 = api.make_frame_desc(cams[2], sp, hp, synth.HIST_AABB)
+    api.frame_run(ctx, 30, d2)
+    assert not np.array_equal(api.frame_fetch(ctx, 30, W, H, res[0].hw, res[0].hh)["disp"], single[2]["disp"])

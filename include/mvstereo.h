@@ -251,7 +251,7 @@ typedef struct {
  * one of the context's result sets (0 <= slot < 64) so that several camera-frames can be in flight. */
 int mvs_frame_run(mvs_ctx* ctx, int slot, const mvs_frame_desc* desc, mvs_frame_result* out);
 
-/* The camera-frames of one step together (1 <= n_frames <= 16, slots first_slot .. first_slot+n_frames-1; all
+/* The camera-frames of one step together (1 <= n_frames <= 32, slots first_slot .. first_slot+n_frames-1; all
  * frames must share image size, SGBM parameters and histogram bounds).  Equivalent to n_frames calls of
  * mvs_frame_run, but the SGM aggregation sweeps the whole batch in one launch per direction set, which is what
  * fills the GPU -- the reference's thread pool likewise runs the nodes of different cameras concurrently

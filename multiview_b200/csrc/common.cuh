@@ -13,7 +13,7 @@
 
 #define MVS_MAX_DEVICES 64   // per-device one-time state (function attributes are per device)
 #define MVS_MAX_SLOTS 64
-#define MVS_MAX_BATCH 16  // camera-frames per batched launch
+#define MVS_MAX_BATCH 32  // camera-frames per batched launch
 
 // Grow-only named device buffers: allocated on first use, reused on every later frame, freed with the
 // context.  Replaces the reference's per-call cudaMalloc/cudaFree (strategies/sgm_disp.cpp:36-60,173).

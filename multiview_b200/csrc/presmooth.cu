@@ -304,6 +304,14 @@ int presmooth_batch_dev(mvs_ctx* ctx, int n, const uint8_t* const* src, int chan
 {
     BlurTaps t;
     memset(&t, 0, sizeof(t));
+    if (n > PRESMOOTH_MAX_IMAGES) {  // larger batches go through in chunks
+        for (int i0 = 0; i0 < n; i0 += PRESMOOTH_MAX_IMAGES) {
+            int rc = presmooth_batch_dev(ctx, n - i0 < PRESMOOTH_MAX_IMAGES ? n - i0 : PRESMOOTH_MAX_IMAGES, src + i0, channels, w, h, step, sigma,
+                                         dst + i0, dstep);
+            if (rc) return rc;
+        }
+        return MVS_OK;
+    }
     bool packed = channels == 3 && sigma > 0.0 && n >= 1 && n <= PRESMOOTH_MAX_IMAGES && (w % 4) == 0 && (step % 4) == 0 &&
                   (dstep % 4) == 0 && gauss_taps_q8(sigma, &t) == 0;
     for (int i = 0; packed && i < n; ++i) packed = ((uintptr_t)src[i] % 4) == 0 && ((uintptr_t)dst[i] % 4) == 0;

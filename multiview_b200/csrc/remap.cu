@@ -346,7 +346,15 @@ int remap_cubic_bgr8_batch_dev(mvs_ctx* ctx, int n, const uint8_t* const* src, i
                                const float* const* mapy, size_t mstep, int w, int h, const uint8_t border[3], uint8_t* const* dst,
                                size_t dstep)
 {
-    if (n < 1 || n > 32) return mvs_fail(ctx, MVS_ERR_ARG, "remap batch of %d images (1..32)", n);
+    if (n < 1) return mvs_fail(ctx, MVS_ERR_ARG, "remap batch of %d images", n);
+    if (n > 32) {  // larger batches go through in chunks
+        for (int i0 = 0; i0 < n; i0 += 32) {
+            int rc = remap_cubic_bgr8_batch_dev(ctx, n - i0 < 32 ? n - i0 : 32, src + i0, sw, sh, sstep, mapx + i0, mapy + i0, mstep, w, h, border,
+                                                dst + i0, dstep);
+            if (rc) return rc;
+        }
+        return MVS_OK;
+    }
     int rc = ensure_cubic_tab(ctx);
     if (rc) return rc;
     RemapBatch b;

@@ -54,6 +54,12 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #ifndef WAVE_D3
 #define WAVE_D3 4            // ring depth for L3 (lock-step needs 2)
 #endif
+#ifndef WAVE_FULL_SLEEP
+#define WAVE_FULL_SLEEP 0
+#endif
+#ifndef WAVE_CONS_SLEEP
+#define WAVE_CONS_SLEEP 100
+#endif
 #define WAVE_SPIN_LIMIT (1 << 20)
 #define WAVE_NB 8            // mbarriers per ring row and kind (pixel index mod WAVE_NB)
 #define WAVE_CTL_PAD 16
@@ -277,6 +283,14 @@ wave_kernel(WaveParams p)
                     break;
                 }
                 if ((spins & 63) == 0 && *(volatile int*)p.error) { failed = true; break; }
+#if WAVE_CONS_SLEEP
+                // back-pressure waits (this warp is AHEAD of its consumer): sleep instead of polling, the issue slots
+                // go to the slower warps on the same scheduler
+                if (base != full_s) __nanosleep(WAVE_CONS_SLEEP);
+#endif
+#if WAVE_FULL_SLEEP
+                if (base == full_s) __nanosleep(WAVE_FULL_SLEEP);
+#endif
             }
         };
 

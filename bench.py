@@ -164,7 +164,7 @@ def run_reference(args, rank, world):
             "cpu_baseline": {"value": val, "unit": "frames/s", "cores": par, "kind": "reference", "sample": sample,
                              "host_cores": cores},
             "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def psutil_avail_gb():
@@ -186,9 +186,6 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # stdout carries exactly one JSON line: NCCL's version banner (NCCL_DEBUG=VERSION) would land there too
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     W, H, D = WORKLOADS[args.workload]
     B = args.batch
@@ -388,12 +385,35 @@ def run_ours(args, rank, world, local_rank):
                                           f"single-threaded inside OpenCV) + C port of cloud/hist; `--impl reference` runs one frame per core",
                                 "seconds": dt}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line: libraries that write there on their own (NCCL prints its version banner to
+    stdout on communicator creation) are sent to stderr at the file-descriptor level; emit() uses the saved descriptor."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

@@ -191,6 +191,9 @@ def run_ours(args, rank, world, local_rank):
     B = args.batch
     ctx = api.Context(local_rank)
     stream = torch.cuda.ExternalStream(ctx.lib.mvs_stream(ctx.h), device=dev)
+    # the library finishes a batch (WTA .. histogram, histogram sums) on its tail stream, overlapped with the next batch's
+    # aggregation on the main stream; the all-reduce of the histogram sum goes behind it on that stream
+    tail = torch.cuda.ExternalStream(ctx.lib.mvs_tail_stream(ctx.h), device=dev)
     sp = api.StereoSGBMParams(sg_num_disparities=D, sg_mode=args.mode)
     hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
     n_cams = world * B
@@ -216,7 +219,7 @@ def run_ours(args, rank, world, local_rank):
         ctx.check(ctx.lib.mvs_frame_hist_sum(ctx.h, first_slot, B, C.byref(ptr), C.byref(w_), C.byref(h_)), "mvs_frame_hist_sum")
         t = torch.as_tensor(_CAI(ptr.value, (hh, hw), "<f4"), device=dev)
         if world > 1:
-            with torch.cuda.stream(stream):
+            with torch.cuda.stream(tail):
                 dist.all_reduce(t)  # counts: exact in fp32 in any order
         # floor-histogram.cpp:411-434 on the summed histogram: smoothing + clip, on the same stream
         ctx.check(ctx.lib.mvs_hist_post_dev(ctx.h, ptr, hw, hh, C.c_float(hp.gaussian_sigma), C.c_float(hp.min_hist_count),
@@ -245,7 +248,7 @@ def run_ours(args, rank, world, local_rank):
         e0.record(stream)
         for _ in range(args.steps):
             hist_t = step_dev()
-        e1.record(stream)
+        e1.record(tail)   # the last work of the last step is the histogram post-step on the tail stream
         barrier()
     ms = e0.elapsed_time(e1)
     launches = ctx.launch_count() - l0

@@ -49,7 +49,9 @@ int mvs_ctx_create(int device, mvs_ctx** out);
 void mvs_ctx_destroy(mvs_ctx* ctx);
 const char* mvs_last_error(const mvs_ctx* ctx); /* never NULL */
 int mvs_sync(mvs_ctx* ctx);                     /* wait for the context's stream */
-void* mvs_stream(mvs_ctx* ctx);                 /* the cudaStream_t, for callers that enqueue their own work */
+void* mvs_stream(mvs_ctx* ctx);                 /* the main cudaStream_t (stage entry points, first half of the frame path) */
+void* mvs_tail_stream(mvs_ctx* ctx);            /* the cudaStream_t the frame path finishes a batch on (WTA .. histogram, the
+                                                   histogram sums): work that consumes frame results is enqueued here */
 const char* mvs_version(void);
 long long mvs_launch_count(const mvs_ctx* ctx); /* kernels launched through this context so far */
 

@@ -53,6 +53,7 @@ SIGNATURES = {
     "mvs_last_error": (C.c_char_p, [c_void_p]),
     "mvs_sync": (c_int, [c_void_p]),
     "mvs_stream": (c_void_p, [c_void_p]),
+    "mvs_tail_stream": (c_void_p, [c_void_p]),
     "mvs_version": (C.c_char_p, []),
     "mvs_launch_count": (C.c_longlong, [c_void_p]),
     "mvs_remap_bgr8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p, c_void_p, c_size_t, c_int, c_int,

@@ -40,6 +40,14 @@ struct mvs_ctx {
     // download of the previous one overlap the kernels of the current one (ordered by the events below).
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_h2d = nullptr;                       // uploads of the batch being enqueued are complete
+    // The frame path runs the second half of a batch (WTA, post-filters, cloud, histogram) on the tail stream so that it
+    // overlaps the aggregation sweeps of the NEXT batch on the main stream (the sweeps are latency-bound and leave issue
+    // slots, registers and thread slots free on every SM).  S volumes alternate between two sets.
+    cudaStream_t tail_stream = nullptr;
+    cudaEvent_t ev_front_done = nullptr;                // cost + aggregation of the batch being enqueued are complete
+    cudaEvent_t ev_tail_done[2] = {nullptr, nullptr};   // last tail that read S set 0 / 1
+    bool tail_done_recorded[2] = {false, false};
+    int s_set = 0;                                      // S set of the next batch
     cudaEvent_t ev_slot_done[MVS_MAX_SLOTS] = {};       // last kernel that touched the slot's buffers
     bool slot_done_recorded[MVS_MAX_SLOTS] = {};
     cudaEvent_t ev_slot_fetched[MVS_MAX_SLOTS] = {};    // last download of the slot's results
@@ -56,6 +64,13 @@ struct mvs_ctx {
 };
 
 int mvs_fail(mvs_ctx* ctx, int code, const char* fmt, ...);
+// Every stage helper launches on ctx->stream; the frame path enqueues its second half on the tail stream by swapping it in.
+struct StreamSwap {
+    mvs_ctx* c;
+    cudaStream_t saved;
+    StreamSwap(mvs_ctx* ctx, cudaStream_t s) : c(ctx), saved(ctx->stream) { ctx->stream = s; }
+    ~StreamSwap() { c->stream = saved; }
+};
 void* arena_get(mvs_ctx* ctx, const char* name, size_t bytes);  // nullptr on failure (error recorded)
 void stage_begin(mvs_ctx* ctx, const char* stage);
 void stage_end(mvs_ctx* ctx, const char* stage);
@@ -135,6 +150,10 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
 int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
                              int16_t* const* disp16, int16_t* raw16_tap /* F == 1 only */);
 int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16);
+int sgbm_front_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
+                         int sset, int16_t** S);
+int sgbm_tail_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, int w, int h, int16_t* const* S, int16_t* const* disp16,
+                        int16_t* raw16_tap);
 int sgbm_wta_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, int F, int16_t* const* S, int16_t* const* disp16);
 int disp_to_float_batch_dev(mvs_ctx* ctx, int F, int16_t* const* d16, int w, int h, float* const* out);
 int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, const int16_t* raw16, int16_t* disp16);

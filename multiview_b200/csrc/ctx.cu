@@ -87,7 +87,11 @@ extern "C" int mvs_ctx_create(int device, mvs_ctx** out)
     ctx->err[0] = 0;
     bool ok = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) == cudaSuccess &&
               cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess &&
-              cudaEventCreateWithFlags(&ctx->ev_h2d, cudaEventDisableTiming) == cudaSuccess;
+              cudaEventCreateWithFlags(&ctx->ev_h2d, cudaEventDisableTiming) == cudaSuccess &&
+              cudaStreamCreateWithFlags(&ctx->tail_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_front_done, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_tail_done[0], cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_tail_done[1], cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; ok && i < MVS_MAX_SLOTS; ++i)
         ok = cudaEventCreateWithFlags(&ctx->ev_slot_done[i], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&ctx->ev_slot_fetched[i], cudaEventDisableTiming) == cudaSuccess;
@@ -105,6 +109,7 @@ extern "C" void mvs_ctx_destroy(mvs_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->tail_stream) cudaStreamSynchronize(ctx->tail_stream);
     if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
     for (auto& kv : ctx->arena.bufs)
         if (kv.second.p) cudaFree(kv.second.p);
@@ -117,6 +122,10 @@ extern "C" void mvs_ctx_destroy(mvs_ctx* ctx)
         if (ctx->ev_slot_done[i]) cudaEventDestroy(ctx->ev_slot_done[i]);
     for (int i = 0; i < MVS_MAX_SLOTS; ++i)
         if (ctx->ev_slot_fetched[i]) cudaEventDestroy(ctx->ev_slot_fetched[i]);
+    if (ctx->ev_front_done) cudaEventDestroy(ctx->ev_front_done);
+    for (int i = 0; i < 2; ++i)
+        if (ctx->ev_tail_done[i]) cudaEventDestroy(ctx->ev_tail_done[i]);
+    if (ctx->tail_stream) cudaStreamDestroy(ctx->tail_stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -128,6 +137,7 @@ extern "C" int mvs_sync(mvs_ctx* ctx)
 {
     if (!ctx) return MVS_ERR_ARG;
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->tail_stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
     return MVS_OK;
 }
@@ -135,3 +145,4 @@ extern "C" int mvs_sync(mvs_ctx* ctx)
 extern "C" long long mvs_launch_count(const mvs_ctx* ctx) { return ctx ? ctx->launches : -1; }
 
 extern "C" void* mvs_stream(mvs_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+extern "C" void* mvs_tail_stream(mvs_ctx* ctx) { return ctx ? (void*)ctx->tail_stream : nullptr; }

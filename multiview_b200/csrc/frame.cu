@@ -104,10 +104,6 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         MVS_CUDA(ctx, cudaEventRecord(ctx->ev_h2d, cs));
         MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_h2d, 0));
     }
-    // results of these slots may still be on their way to the host (mvs_frame_fetch copies on the copy stream)
-    for (int f = 0; f < n_frames; ++f)
-        if (ctx->slot_fetch_recorded[first_slot + f]) MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_slot_fetched[first_slot + f], 0));
-
     const uint8_t white[3] = {255, 255, 255};  // calc_rectified.cpp:113
     stage_begin(ctx, "rectify");
     {
@@ -153,11 +149,31 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
                 rc = presmooth_batch_dev(ctx, 2, ps + 2 * f, 3, w, h, (size_t)w * 3, descs[f].presmooth_sigma, pd + 2 * f, (size_t)w);
     }
     stage_end(ctx, "presmooth");
-    if (!rc) {
+    int16_t* Sv[MVS_MAX_BATCH];
+    int sset = 0;
+    if (rc) return rc;
+    {
         const uint8_t *l[MVS_MAX_BATCH], *r[MVS_MAX_BATCH];
+        for (int f = 0; f < n_frames; ++f) { l[f] = sb[f].grey[0]; r[f] = sb[f].grey[1]; }
+        // first half on the main stream: cost volumes + aggregation into S set `sset`, whose previous reader must be done
+        sset = ctx->s_set;
+        ctx->s_set ^= 1;
+        if (ctx->tail_done_recorded[sset]) MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_tail_done[sset], 0));
+        rc = sgbm_front_batch_dev(ctx, &d0.sgbm, n_frames, l, r, w, h, sset, Sv);
+        if (rc) return rc;
+        MVS_CUDA(ctx, cudaEventRecord(ctx->ev_front_done, s));
+    }
+    // second half on the tail stream: it overlaps the sweeps of the next batch
+    cudaStream_t ts = ctx->tail_stream;
+    StreamSwap on_tail(ctx, ts);
+    MVS_CUDA(ctx, cudaStreamWaitEvent(ts, ctx->ev_front_done, 0));
+    // results of these slots may still be on their way to the host (mvs_frame_fetch copies on the copy stream)
+    for (int f = 0; f < n_frames; ++f)
+        if (ctx->slot_fetch_recorded[first_slot + f]) MVS_CUDA(ctx, cudaStreamWaitEvent(ts, ctx->ev_slot_fetched[first_slot + f], 0));
+    if (!rc) {
         int16_t* d16[MVS_MAX_BATCH];
-        for (int f = 0; f < n_frames; ++f) { l[f] = sb[f].grey[0]; r[f] = sb[f].grey[1]; d16[f] = sb[f].disp16; }
-        rc = sgbm_compute16_batch_dev(ctx, &d0.sgbm, n_frames, l, r, w, h, d16, nullptr);
+        for (int f = 0; f < n_frames; ++f) d16[f] = sb[f].disp16;
+        rc = sgbm_tail_batch_dev(ctx, &d0.sgbm, n_frames, w, h, Sv, d16, nullptr);
     }
     stage_begin(ctx, "cloud");
     if (!rc) {
@@ -185,8 +201,10 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     stage_end(ctx, "hist");
     if (rc) return rc;
 
+    MVS_CUDA(ctx, cudaEventRecord(ctx->ev_tail_done[sset], ts));
+    ctx->tail_done_recorded[sset] = true;
     for (int f = 0; f < n_frames; ++f) {
-        MVS_CUDA(ctx, cudaEventRecord(ctx->ev_slot_done[first_slot + f], s));
+        MVS_CUDA(ctx, cudaEventRecord(ctx->ev_slot_done[first_slot + f], ts));
         ctx->slot_done_recorded[first_slot + f] = true;
         FrameSlot& fs = ctx->slots[first_slot + f];
         fs.w = w; fs.h = h; fs.hw = hw; fs.hh = hh; fs.valid = true;
@@ -254,6 +272,7 @@ extern "C" int mvs_frame_hist_sum(mvs_ctx* ctx, int first_slot, int n_slots, flo
     char nm[48];
     snprintf(nm, sizeof(nm), "slots.hist_sum.%d", first_slot);
     MVS_ARENA(ctx, float, sum, nm, (size_t)w * h);
+    StreamSwap on_tail(ctx, ctx->tail_stream);   // behind the batch's second half; callers continue on mvs_tail_stream()
     int rc = hist_sum_dev(ctx, hists + (size_t)first_slot * w * h, n_slots, w, h, sum);
     if (rc) return rc;
     *hist_dev = sum;

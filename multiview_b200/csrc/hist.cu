@@ -262,6 +262,7 @@ extern "C" int mvs_hist_post_dev(mvs_ctx* ctx, float* hist_dev, int hw, int hh, 
     if (!ctx) return MVS_ERR_ARG;
     if (!hist_dev || hw <= 0 || hh <= 0) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_hist_post_dev: bad argument");
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    StreamSwap on_tail(ctx, ctx->tail_stream);   // consumes frame results: enqueued behind them
     return hist_post_dev(ctx, hist_dev, hw, hh, gaussian_sigma, min_hist_count, max_hist_count);
 }
 
@@ -343,6 +344,7 @@ extern "C" int mvs_localization_hists_dev(mvs_ctx* ctx, const mvs_loc_params* p,
     if (!p || !hist_dev || !motion_dev || !rhist_dev || !bg_dev || !fg0_dev || !fg_dev || hw <= 0 || hh <= 0)
         return mvs_fail(ctx, MVS_ERR_ARG, "mvs_localization_hists_dev: bad argument");
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    StreamSwap on_tail(ctx, ctx->tail_stream);   // consumes frame results: enqueued behind them
     return localization_hists_dev(ctx, p, hist_dev, hw, hh, hist_sz, motion_dev, rhist_dev, bg_dev, fg0_dev, fg_dev);
 }
 

@@ -20,24 +20,24 @@ static std::string fname(const char* base, int f)
     return buf;
 }
 
-// A batch of F pairs of equal size through the SGBM chain.  The cost volumes of all frames are built first so
-// that ONE aggregation launch per sweep covers the whole batch (its wavefronts then fill the GPU).
-int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r,
-                             int w, int h, int16_t* const* disp16, int16_t* raw16_tap)
+// A batch of F pairs of equal size through the SGBM chain, in two halves so that the frame path can run the second
+// half of one batch on another stream while the first half of the next batch occupies the main stream:
+//   front: cost volumes of all frames, then ONE aggregation launch per sweep for the whole batch (its wavefronts fill
+//          the GPU); writes the S volumes of set `sset` (0 or 1);
+//   tail:  WTA + LR check + median + speckle filter from those S volumes.
+int sgbm_front_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
+                         int sset, int16_t** S)
 {
     if (F < 1 || F > MVS_MAX_BATCH) return mvs_fail(ctx, MVS_ERR_ARG, "sgbm: batch of %d frames (1..%d)", F, MVS_MAX_BATCH);
     SgbmGeom g;
     int rc = sgbm_geom(ctx, p, w, h, &g);
     if (rc) return rc;
     int16_t* C[MVS_MAX_BATCH];
-    int16_t* S[MVS_MAX_BATCH];
     for (int f = 0; f < F; ++f) {
         C[f] = (int16_t*)arena_get(ctx, fname("sgbm.C", f).c_str(), g.cells() * 2);
-        S[f] = (int16_t*)arena_get(ctx, fname("sgbm.S", f).c_str(), g.cells() * 2);
+        S[f] = (int16_t*)arena_get(ctx, fname(sset ? "sgbm.S1" : "sgbm.S", f).c_str(), g.cells() * 2);
         if (!C[f] || !S[f]) return MVS_ERR_NOMEM;
     }
-    int16_t* raw = (F == 1 && raw16_tap) ? raw16_tap : (int16_t*)arena_get(ctx, "sgbm.raw", sizeof(int16_t) * (size_t)w * h);
-    if (!raw) return MVS_ERR_NOMEM;
     stage_begin(ctx, "cost");
     rc = sgbm_cost_volume_batch_dev(ctx, g, F, l, r, C);
     stage_end(ctx, "cost");
@@ -45,6 +45,14 @@ int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, cons
     stage_begin(ctx, "aggregate");
     rc = sgbm_aggregate_batch_dev(ctx, g, F, C, S);
     stage_end(ctx, "aggregate");
+    return rc;
+}
+
+int sgbm_tail_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, int w, int h, int16_t* const* S, int16_t* const* disp16,
+                        int16_t* raw16_tap)
+{
+    SgbmGeom g;
+    int rc = sgbm_geom(ctx, p, w, h, &g);
     if (rc) return rc;
     // F == 1: "wta" and "post" are timed separately; a batch times both under "wta"
     if (F > 1) {
@@ -53,14 +61,24 @@ int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, cons
         stage_end(ctx, "wta");
         return rc;
     }
+    int16_t* raw = raw16_tap ? raw16_tap : (int16_t*)arena_get(ctx, "sgbm.raw", sizeof(int16_t) * (size_t)w * h);
+    if (!raw) return MVS_ERR_NOMEM;
     stage_begin(ctx, "wta");
-    for (int f = 0; f < F && !rc; ++f) {
-        rc = sgbm_wta_dev(ctx, g, S[f], raw);
-        if (F == 1) { stage_end(ctx, "wta"); stage_begin(ctx, "post"); }
-        if (!rc) rc = sgbm_post_dev(ctx, g, p, raw, disp16[f]);
-    }
-    stage_end(ctx, F == 1 ? "post" : "wta");
+    rc = sgbm_wta_dev(ctx, g, S[0], raw);
+    stage_end(ctx, "wta");
+    stage_begin(ctx, "post");
+    if (!rc) rc = sgbm_post_dev(ctx, g, p, raw, disp16[0]);
+    stage_end(ctx, "post");
     return rc;
+}
+
+int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r,
+                             int w, int h, int16_t* const* disp16, int16_t* raw16_tap)
+{
+    int16_t* S[MVS_MAX_BATCH];
+    int rc = sgbm_front_batch_dev(ctx, p, F, l, r, w, h, 0, S);
+    if (rc) return rc;
+    return sgbm_tail_batch_dev(ctx, p, F, w, h, S, disp16, F == 1 ? raw16_tap : nullptr);
 }
 
 int sgbm_compute16_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,

@@ -64,6 +64,15 @@ struct mvs_ctx {
 };
 
 int mvs_fail(mvs_ctx* ctx, int code, const char* fmt, ...);
+// The stage entry points work on the main stream and share arena buffers (S volumes, scratch) with the second half of
+// the frame path, which runs on the tail stream: they order themselves behind it first.
+static inline int main_stream_waits_for_tail(mvs_ctx* ctx)
+{
+    for (int i = 0; i < 2; ++i)
+        if (ctx->tail_done_recorded[i] && cudaStreamWaitEvent(ctx->stream, ctx->ev_tail_done[i], 0) != cudaSuccess)
+            return mvs_fail(ctx, MVS_ERR_CUDA, "cudaStreamWaitEvent failed");
+    return MVS_OK;
+}
 // Every stage helper launches on ctx->stream; the frame path enqueues its second half on the tail stream by swapping it in.
 struct StreamSwap {
     mvs_ctx* c;

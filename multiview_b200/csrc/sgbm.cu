@@ -76,7 +76,9 @@ int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, cons
                              int w, int h, int16_t* const* disp16, int16_t* raw16_tap)
 {
     int16_t* S[MVS_MAX_BATCH];
-    int rc = sgbm_front_batch_dev(ctx, p, F, l, r, w, h, 0, S);
+    int rc = main_stream_waits_for_tail(ctx);
+    if (rc) return rc;
+    rc = sgbm_front_batch_dev(ctx, p, F, l, r, w, h, 0, S);
     if (rc) return rc;
     return sgbm_tail_batch_dev(ctx, p, F, w, h, S, disp16, F == 1 ? raw16_tap : nullptr);
 }

@@ -272,6 +272,7 @@ extern "C" int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float ga
     if (!ctx) return MVS_ERR_ARG;
     if (!hist || hw <= 0 || hh <= 0) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_hist_post: bad argument");
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (int wrc = main_stream_waits_for_tail(ctx)) return wrc;   // shares its scratch image with mvs_hist_post_dev
     size_t n = (size_t)hw * hh;
     MVS_ARENA(ctx, float, d, "hist.post.api", n);
     MVS_CUDA(ctx, cudaMemcpyAsync(d, hist, n * 4, cudaMemcpyHostToDevice, ctx->stream));

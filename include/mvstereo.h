@@ -152,6 +152,8 @@ typedef struct {
     float hist_sz, min_z, max_z;
     int weighting; /* MVS_WGT_* */
     int use_still; /* apply_slic_still_weights */
+    int ordered;   /* 1: sum every bin in point order like the reference's sequential loop (weighted histograms bit-exact;
+                      a stable sort by bin, slower); 0: float atomics (counts exact, weighted sums <= 1e-5 relative) */
 } mvs_hist_params;
 
 /* ensure_floor_hist_dims, cost-functions/floor-histogram.cpp:19-35.  aabb = {left, top, right, bottom}. */
@@ -163,7 +165,7 @@ int mvs_hist_dims(const double aabb[4], float hist_sz, int* hw, int* hh);
  * cam_center = translations[cam] (pipeline/nodes/floor_hist.cpp:122); labels (int32 lw x lh, row stride lw)
  * and still_score (n_labels doubles) may be NULL.  cam_hist: float hw x hh, row stride hw, overwritten.
  * Counts (MVS_WGT_NONE without still weights) are bit-exact; weighted sums are float accumulations in a
- * different order (<= 1e-5 relative). */
+ * different order (<= 1e-5 relative) unless p->ordered is set, which reproduces the reference's point order. */
 int mvs_floor_hist_camera(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
                           const double cam_center[3], const double* Xs, const int32_t* xy, int32_t n,
                           const int32_t* labels, int lw, int lh, const double* still_score, int n_labels,

@@ -24,7 +24,8 @@ class Bcam(C.Structure):
 
 
 class HistParams(C.Structure):
-    _fields_ = [("hist_sz", c_float), ("min_z", c_float), ("max_z", c_float), ("weighting", c_int), ("use_still", c_int)]
+    _fields_ = [("hist_sz", c_float), ("min_z", c_float), ("max_z", c_float), ("weighting", c_int), ("use_still", c_int),
+                ("ordered", c_int)]
 
 
 class LocParams(C.Structure):

@@ -328,9 +328,11 @@ class FloorHistogramParams:
     weighting: int = WGT_NORM
     apply_slic_still_weights: bool = True
     skip_cameras: tuple = ()
+    ordered: bool = False   # not a reference field: sum every bin in point order (weighted histograms bit-exact)
 
     def to_c(self) -> HistParams:
-        return HistParams(self.hist_sz, self.hist_min_z, self.hist_max_z, int(self.weighting), int(self.apply_slic_still_weights))
+        return HistParams(self.hist_sz, self.hist_min_z, self.hist_max_z, int(self.weighting), int(self.apply_slic_still_weights),
+                          int(self.ordered))
 
 
 def hist_dims(aabb, hist_sz):

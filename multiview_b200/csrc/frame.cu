@@ -196,7 +196,7 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     stage_end(ctx, "cloud");
     stage_begin(ctx, "hist");
     for (int f = 0; f < n_frames && !rc; ++f)
-        rc = floor_hist_camera_dev(ctx, &descs[f].hist, descs[f].et, descs[f].aabb, descs[f].cam_center, sb[f].Xs, sb[f].xy, sb[f].nd, 0,
+        rc = floor_hist_camera_dev(ctx, &descs[f].hist, descs[f].et, descs[f].aabb, descs[f].cam_center, sb[f].Xs, sb[f].xy, sb[f].nd, (int)n /* capacity */,
                                    nullptr, 0, 0, nullptr, 0, sb[f].cam_hist, hw, hh);
     stage_end(ctx, "hist");
     if (rc) return rc;

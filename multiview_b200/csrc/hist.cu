@@ -4,6 +4,8 @@
 // fp64 geometry compiled with --fmad=false (bin = round(...) flips on last-ulp differences), fp32 weights.
 #include <math.h>
 
+#include <cub/device/device_radix_sort.cuh>
+
 #include "common.cuh"
 
 struct HistArgs {
@@ -25,6 +27,45 @@ __device__ __forceinline__ Q qmul(Q a, Q b)  // quaternion.hpp:205-213
     return c;
 }
 
+// rotation.inverse() = conjugate().normalised()
+__device__ __forceinline__ Q hist_inverse_rotation(const HistArgs& a)
+{
+    Q inv = {-a.et[3], -a.et[4], -a.et[5], a.et[6]};
+    double mag2 = inv.x * inv.x + inv.y * inv.y + inv.z * inv.z + inv.w * inv.w;
+    if (fabs(mag2 - 1.0) > 1e-9) {
+        double s = 1.0 / sqrt(mag2);
+        inv.x *= s; inv.y *= s; inv.z *= s; inv.w *= s;
+    }
+    return inv;
+}
+// bin and weight of point i; false when the point does not land in the histogram
+__device__ __forceinline__ bool hist_point(const HistArgs& a, const Q& q, const Q& inv, const double* __restrict__ Xs,
+                                           const int32_t* __restrict__ xy, const int32_t* __restrict__ labels,
+                                           const double* __restrict__ still, int i, int* bin, float* weight)
+{
+    double X0 = Xs[3 * (size_t)i], X1 = Xs[3 * (size_t)i + 1], X2 = Xs[3 * (size_t)i + 2];
+    Q v = {X0 * a.et[7], X1 * a.et[7], X2 * a.et[7], 0.0};
+    Q r = qmul(qmul(q, v), inv);
+    double Yx = r.x + a.et[0], Yy = r.y + a.et[1], Yz = r.z + a.et[2];
+    double zx = (Yx - a.aabb[0]) / a.hist_sz + 1e-9, zy = (Yy - a.aabb[1]) / a.hist_sz + 1e-9;
+    // int(std::round(.)) of an out-of-int-range double is UB in the reference; clamp keeps such points out
+    double rx = round(zx), ry = round(zy);
+    if (!(rx >= 0.0 && rx < (double)a.hw && ry >= 0.0 && ry < (double)a.hh)) return false;
+    if (Yz < a.min_z || Yz > a.max_z) return false;
+    int bx = (int)rx, by = (int)ry;
+    double dx = X0 - a.cc[0], dy = X1 - a.cc[1], dz = X2 - a.cc[2];
+    double q2 = dx * dx + dy * dy + dz * dz;
+    double wgt = a.weighting == MVS_WGT_NONE ? 1.0 : (a.weighting == MVS_WGT_NORM ? sqrt(q2) : q2);
+    if (a.use_still && labels) {
+        int px = xy[2 * (size_t)i], py = xy[2 * (size_t)i + 1];
+        int label = ((unsigned)px < (unsigned)a.lw && (unsigned)py < (unsigned)a.lh) ? labels[(size_t)py * a.lw + px] : -1;
+        if (label >= 0 && label < a.n_labels) wgt *= 1.0 + 10.0 * still[label];
+    }
+    *bin = by * a.hw + bx;
+    *weight = (float)wgt;
+    return true;
+}
+
 // Per point: transform to world, bin, weight.  SMEM = true: the block accumulates into a private copy of the
 // histogram in shared memory (float atomics on-chip) and adds its non-zero bins to the global one at the end.
 template <bool SMEM>
@@ -40,34 +81,12 @@ floor_hist_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __re
         __syncthreads();
     }
     const int n = n_dev ? *n_dev : n_host;
-    // rotation.inverse() = conjugate().normalised()
-    Q q = {a.et[3], a.et[4], a.et[5], a.et[6]};
-    Q inv = {-q.x, -q.y, -q.z, q.w};
-    double mag2 = inv.x * inv.x + inv.y * inv.y + inv.z * inv.z + inv.w * inv.w;
-    if (fabs(mag2 - 1.0) > 1e-9) {
-        double s = 1.0 / sqrt(mag2);
-        inv.x *= s; inv.y *= s; inv.z *= s; inv.w *= s;
-    }
+    const Q q = {a.et[3], a.et[4], a.et[5], a.et[6]};
+    const Q inv = hist_inverse_rotation(a);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        double X0 = Xs[3 * (size_t)i], X1 = Xs[3 * (size_t)i + 1], X2 = Xs[3 * (size_t)i + 2];
-        Q v = {X0 * a.et[7], X1 * a.et[7], X2 * a.et[7], 0.0};
-        Q r = qmul(qmul(q, v), inv);
-        double Yx = r.x + a.et[0], Yy = r.y + a.et[1], Yz = r.z + a.et[2];
-        double zx = (Yx - a.aabb[0]) / a.hist_sz + 1e-9, zy = (Yy - a.aabb[1]) / a.hist_sz + 1e-9;
-        // int(std::round(.)) of an out-of-int-range double is UB in the reference; clamp keeps such points out
-        double rx = round(zx), ry = round(zy);
-        if (!(rx >= 0.0 && rx < (double)a.hw && ry >= 0.0 && ry < (double)a.hh)) continue;
-        if (Yz < a.min_z || Yz > a.max_z) continue;
-        int bx = (int)rx, by = (int)ry;
-        double dx = X0 - a.cc[0], dy = X1 - a.cc[1], dz = X2 - a.cc[2];
-        double q2 = dx * dx + dy * dy + dz * dz;
-        double wgt = a.weighting == MVS_WGT_NONE ? 1.0 : (a.weighting == MVS_WGT_NORM ? sqrt(q2) : q2);
-        if (a.use_still && labels) {
-            int px = xy[2 * (size_t)i], py = xy[2 * (size_t)i + 1];
-            int label = ((unsigned)px < (unsigned)a.lw && (unsigned)py < (unsigned)a.lh) ? labels[(size_t)py * a.lw + px] : -1;
-            if (label >= 0 && label < a.n_labels) wgt *= 1.0 + 10.0 * still[label];
-        }
-        atomicAdd((SMEM ? sh_hist : hist) + (size_t)by * a.hw + bx, (float)wgt);
+        int bin;
+        float wgt;
+        if (hist_point(a, q, inv, Xs, xy, labels, still, i, &bin, &wgt)) atomicAdd((SMEM ? sh_hist : hist) + bin, wgt);
     }
     if (SMEM) {
         __syncthreads();
@@ -76,6 +95,72 @@ floor_hist_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __re
             if (v != 0.0f) atomicAdd(hist + k, v);
         }
     }
+}
+
+// ---- order-preserving accumulation (mvs_hist_params.ordered): every bin is summed in point order, like the
+// reference's sequential `cam_hist(x, y) += weight` (floor-histogram.cpp:265-267), so weighted histograms come out
+// bit for bit.  (1) bin + weight per point (points past N and rejected points get the bin `nbins`), (2) a STABLE radix
+// sort of the weights by bin keeps point order inside a bin, (3) one thread per bin adds its segment up in order.
+__global__ void __launch_bounds__(256)
+hist_points_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __restrict__ xy, const int32_t* n_dev, int n_host,
+                   int cap, const int32_t* __restrict__ labels, const double* __restrict__ still, uint32_t* __restrict__ bins,
+                   float* __restrict__ weights)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= cap) return;
+    const int n = n_dev ? *n_dev : n_host;
+    const Q q = {a.et[3], a.et[4], a.et[5], a.et[6]};
+    const Q inv = hist_inverse_rotation(a);
+    int bin = a.hw * a.hh;
+    float wgt = 0.0f;
+    if (i < n && !hist_point(a, q, inv, Xs, xy, labels, still, i, &bin, &wgt)) bin = a.hw * a.hh;
+    bins[i] = (uint32_t)bin;
+    weights[i] = wgt;
+}
+__global__ void hist_segment_starts_kernel(const uint32_t* __restrict__ sorted_bins, int cap, int nbins, int* __restrict__ start)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= cap) return;
+    const uint32_t b = sorted_bins[j];
+    if ((int)b < nbins && (j == 0 || sorted_bins[j - 1] != b)) start[b] = j;
+}
+__global__ void hist_ordered_sum_kernel(const uint32_t* __restrict__ sorted_bins, const float* __restrict__ sorted_weights, int cap,
+                                        int nbins, const int* __restrict__ start, float* __restrict__ hist)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nbins) return;
+    float s = 0.0f;   // cam_hist.fill(0.0f), floor-histogram.cpp:200
+    const int j0 = start[b];
+    if (j0 >= 0)
+        for (int j = j0; j < cap && sorted_bins[j] == (uint32_t)b; ++j) s += sorted_weights[j];
+    hist[b] = s;
+}
+
+static int floor_hist_ordered_dev(mvs_ctx* ctx, const HistArgs& a, const double* Xs, const int32_t* xy, const int32_t* n_dev, int n_host,
+                                  int cap, const int32_t* labels, const double* still, float* cam_hist)
+{
+    cudaStream_t s = ctx->stream;
+    const int nbins = a.hw * a.hh;
+    if (cap <= 0) {
+        MVS_CUDA(ctx, cudaMemsetAsync(cam_hist, 0, sizeof(float) * (size_t)nbins, s));
+        return MVS_OK;
+    }
+    MVS_ARENA(ctx, uint32_t, bins, "hist.ordered.bins", (size_t)cap * 2);
+    MVS_ARENA(ctx, float, wts, "hist.ordered.weights", (size_t)cap * 2);
+    MVS_ARENA(ctx, int, start, "hist.ordered.start", (size_t)nbins);
+    int end_bit = 1;
+    while ((1 << end_bit) <= nbins) ++end_bit;   // keys 0 .. nbins
+    size_t tmp_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, bins, bins + cap, wts, wts + cap, cap, 0, end_bit, s);
+    MVS_ARENA(ctx, unsigned char, tmp, "hist.ordered.tmp", tmp_bytes + 16);
+    hist_points_kernel<<<cdiv(cap, 256), 256, 0, s>>>(a, Xs, xy, n_dev, n_host, cap, labels, still, bins, wts);
+    MVS_LAUNCH_CHECK(ctx, "hist_points_kernel");
+    MVS_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, bins, bins + cap, wts, wts + cap, cap, 0, end_bit, s));
+    MVS_CUDA(ctx, cudaMemsetAsync(start, 0xff, sizeof(int) * (size_t)nbins, s));
+    hist_segment_starts_kernel<<<cdiv(cap, 256), 256, 0, s>>>(bins + cap, cap, nbins, start);
+    hist_ordered_sum_kernel<<<cdiv(nbins, 128), 128, 0, s>>>(bins + cap, wts + cap, cap, nbins, start, cam_hist);
+    MVS_LAUNCH_CHECK_N(ctx, "ordered histogram kernels", 2);
+    return MVS_OK;
 }
 
 __global__ void hist_sum_kernel(const float* __restrict__ cam_hists, int n_cams, size_t n, float* __restrict__ hist)
@@ -108,6 +193,8 @@ int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double e
     a.hist_sz = (double)p->hist_sz; a.min_z = (double)p->min_z; a.max_z = (double)p->max_z;
     a.weighting = p->weighting; a.use_still = p->use_still && labels && still;
     a.lw = lw; a.lh = lh; a.n_labels = n_labels; a.hw = hw; a.hh = hh;
+    if (p->ordered)   // n_host is the capacity of Xs / xy when the count lives on the device
+        return floor_hist_ordered_dev(ctx, a, Xs, xy, n_dev, n_host, n_host, labels, still, cam_hist);
     MVS_CUDA(ctx, cudaMemsetAsync(cam_hist, 0, sizeof(float) * (size_t)hw * hh, ctx->stream));
     const size_t smem = sizeof(float) * (size_t)hw * hh;
     if (smem <= 100 * 1024) {  // two blocks per SM keep a private histogram each

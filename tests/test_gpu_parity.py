@@ -198,6 +198,37 @@ def test_floor_histogram_parity(ctx):
             assert np.allclose(fh.hist, oracle.hist_post(wsum, p.gaussian_sigma, p.min_hist_count, p.max_hist_count), rtol=1e-5, atol=1e-2)
 
 
+def test_floor_histogram_ordered_accumulation_is_bit_exact(ctx):
+    """mvs_hist_params.ordered: every bin summed in point order like the reference's sequential loop, so the weighted
+    histograms (the reference default is WGT_NORM with still weights) match the oracle bit for bit."""
+    disp, q, t, bl, K = _cloud_inputs()
+    want_pc = oracle.point_cloud(oracle.bcam_init(q, t, bl, K), disp)
+    aabb = synth.HIST_AABB
+    n_cams = 2
+    ets = [synth.camera_extrinsics(c, n_cams) for c in range(n_cams)]
+    pcs = []
+    for c in range(n_cams):
+        pc = api.PointCloud()
+        pc.Xs, pc.xy = want_pc["Xs"] * (1.0 + 0.1 * c), want_pc["xy"]
+        pcs.append(pc)
+    rng = np.random.default_rng(14)
+    labels = rng.integers(-1, 50, disp.shape).astype(np.int32)
+    still = rng.random(40)
+    for weighting, use_still in [(api.WGT_NORM, True), (api.WGT_QUADRANCE, False), (api.WGT_NONE, True)]:
+        p = api.FloorHistogramParams(weighting=weighting, apply_slic_still_weights=use_still, ordered=True)
+        fh = api.FloorHistogram()
+        api.FloorHistogram.calculate(p, aabb, n_cams, ets, pcs, [e[:3] for e in ets], fh,
+                                     slic_lookups=[labels] * n_cams if use_still else None,
+                                     still_scores=[still] * n_cams if use_still else None, ctx=ctx)
+        hp = oracle.HistParams(p.hist_sz, p.hist_min_z, p.hist_max_z, weighting, int(use_still))
+        want = [oracle.floor_hist_camera(hp, ets[c], aabb, ets[c][:3], pcs[c].Xs, pcs[c].xy,
+                                         labels if use_still else None, still if use_still else None) for c in range(n_cams)]
+        for c in range(n_cams):
+            assert (want[c] > 0).sum() > 10 and want[c].max() > 50
+            assert np.array_equal(fh.camera_hists[c], want[c])
+        assert np.array_equal(fh.hist_raw, oracle.hist_sum(np.stack(want)))
+
+
 def test_frame_path_matches_stagewise_oracle(ctx):
     W, H, D = 384, 240, 64
     cam = synth.make_camera(W, H, D, config=2, cam=1, n_cams=4)

@@ -254,6 +254,13 @@ def test_frame_path_matches_stagewise_oracle(ctx):
     ohp = oracle.HistParams(hp.hist_sz, hp.hist_min_z, hp.hist_max_z, 0, 0)
     wh = oracle.floor_hist_camera(ohp, cam["et"], synth.HIST_AABB, cam["et"][:3], wpc["Xs"], wpc["xy"])
     assert np.array_equal(out["cam_hist"], wh) and wh.sum() > 100
+    # the reference's default weighting (distance to the camera) through the frame path, summed in point order
+    hp2 = api.FloorHistogramParams(weighting=api.WGT_NORM, apply_slic_still_weights=False, ordered=True)
+    res2 = api.frame_run(ctx, 1, api.make_frame_desc(cam, sp, hp2, synth.HIST_AABB))
+    out2 = api.frame_fetch(ctx, 1, W, H, res2.hw, res2.hh)
+    ohp2 = oracle.HistParams(hp2.hist_sz, hp2.hist_min_z, hp2.hist_max_z, api.WGT_NORM, 0)
+    wh2 = oracle.floor_hist_camera(ohp2, cam["et"], synth.HIST_AABB, cam["et"][:3], out2["Xs"], out2["xy"])
+    assert np.array_equal(out2["cam_hist"], wh2) and wh2.sum() > wh.sum()
     # oracle's own calibration restatement agrees with the host-side numpy one to rounding
     assert np.allclose(np.array(ob.krr_inv[1][:]), np.array(ob2.krr_inv[1][:]), rtol=1e-9, atol=1e-12)
 

@@ -23,7 +23,6 @@ UNITS = {
     "remap.cu": [],
     "presmooth.cu": [],
     "cost.cu": os.environ.get("MVS_COST_FLAGS", "").split(),
-    "aggregate.cu": [],
     # tuning experiments: MVS_WAVE_FLAGS="-DWAVE_R=15 -DWAVE_D12=7" python -m multiview_b200.build --force
     "aggregate_wave.cu": os.environ.get("MVS_WAVE_FLAGS", "").split(),
     "wta_post.cu": [],

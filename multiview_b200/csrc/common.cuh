@@ -109,6 +109,10 @@ void stage_end(mvs_ctx* ctx, const char* stage);
 static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 // ---- geometry of the SGBM volumes ------------------------------------------------------------------
+// Device cost volumes C and S are uint16 [H][W1][Dp] in the SPLIT layout: the 32-bit word w (0 <= w < Dp/2) of a
+// pixel holds disparity w in its low half and disparity w + Dp/2 in its high half.  In packed u16x2 arithmetic the
+// d-1 / d+1 neighbours of a word are then the previous / next WORD (no byte permutes in the aggregation sweep).
+__host__ __device__ static inline int split_index(int d, int Dp) { return d >= Dp / 2 ? 2 * (d - Dp / 2) + 1 : 2 * d; }  // halfword of disparity d
 struct SgbmGeom {
     int W, H, D, minD, minX1, W1;
     int Dp;  // disparities per pixel in the device volumes (D rounded up to a multiple of 64)
@@ -151,10 +155,7 @@ int sgbm_cost_volume_dev(mvs_ctx* ctx, const SgbmGeom& g, const uint8_t* l, cons
 int sgbm_cost_volume_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const uint8_t* const* l, const uint8_t* const* r,
                                int16_t* const* C);
 int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);       // fused wavefront sweeps
-int sgbm_aggregate_paths_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S); // one kernel per direction (debug/A-B)
-int sgbm_aggregate_wave_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);
 int sgbm_aggregate_wave_status(mvs_ctx* ctx, cudaStream_t stream = nullptr);  // nullptr: the compute stream
-int sgbm_aggregate_wave_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S);
 int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S);
 int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
                              int16_t* const* disp16, int16_t* raw16_tap /* F == 1 only */);

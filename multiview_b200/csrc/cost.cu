@@ -2,7 +2,7 @@
 // cost-functions/disparity/strategies/stereosgbm_disp.cpp:121-125; algorithm: SURVEY.md A.1):
 //   x-Sobel prefilter clipped to [0, 2*ftzero] + raw intensity, Birchfield-Tomasi sampling-insensitive
 //   cost on both channels, then a blockSize x blockSize box sum with replicate clamping in the
-//   valid-column (W1) domain.  16-bit, d fastest, Dp = D rounded up to 64 per pixel (pad = 0).
+//   valid-column (W1) domain.  16-bit, Dp = D rounded up to 64 disparities per pixel (pad = 0), split layout (common.cuh).
 #include "common.cuh"
 
 extern "C" int mvs_sgbm_check(const mvs_sgbm_params* p, int w, int h)
@@ -98,9 +98,10 @@ __global__ void prefilter_batch_kernel(PrefilterBatch b, int W, int H, int ftzer
 // disparities (u16x2) and walks along x keeping the last WIN pixel costs in a register ring, so the row box sum is
 // a sliding window (one add, one subtract per step).  Step k of a tile is the virtual column xs + k; columns left
 // of the image are folded into the ring's initial state, columns right of it repeat the last pixel cost
-// (replicate clamping).  The right image's prefilter planes are staged reversed in shared memory, one 16-byte
-// element {2 pixels x 3 planes x 2 channels, as bytes} per position, so that the element of disparity pair t at step
-// k sits at (NS/2 + t - ceil(k/2)) of the copy of k's parity (the odd copy is shifted by one pixel): every address of
+// (replicate clamping).  A pair is the two disparities that share a 32-bit word of the volume: t and t + Dp/2 (the
+// split layout, common.cuh).  The right image's prefilter planes are staged reversed in shared memory, one 16-byte
+// element {2 pixels Dp/2 apart x 3 planes x 2 channels, as bytes} per position, so that the element of pair t at step
+// k sits at NS + t - k: every address of
 // the unrolled loop is a running pointer plus an immediate, and a step costs one 16-byte load per thread (the
 // kernel is bound by shared-memory wavefronts, so the bytes are widened to u16x2 with PRMT in registers).  All arithmetic is packed 16-bit with a +1024 bias so that the
 // Birchfield-Tomasi differences never go negative (plain 32-bit adds/subs then act per halfword).
@@ -120,8 +121,7 @@ struct CostTile {
     static constexpr int SW = WIN / 2;
     static constexpr int TX = NS - (WIN - 1);                  // output columns of an inner tile
     static constexpr int TX0 = NS - SW;                        // output columns of the first tile (its left window half is folded)
-    static constexpr int KW = (NS + 2 * HALF + 2) / 2;         // staged right-image elements per copy
-    static constexpr int R4 = 2 * KW;                          // uint4 per row: [copy E/O][KW]
+    static constexpr int R4 = NS + HALF;                       // staged right-image elements (uint4) per row
     static constexpr int L4 = 2 * NS;                          // uint4 per row: [step][channel]
     static constexpr size_t SMEM = (size_t)ROWS * (R4 + L4) * 16;
 };
@@ -148,7 +148,7 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
                                                    uint32_t* __restrict__ hsum, int tile, int yblock)
 {
     using T = CostTile<WIN, NW>;
-    constexpr int NS = T::NS, SW = T::SW, HALF = T::HALF, KW = T::KW, PPT = T::PPT, TPR = T::TPR;
+    constexpr int NS = T::NS, SW = T::SW, HALF = T::HALF, PPT = T::PPT, TPR = T::TPR;
     extern __shared__ __align__(16) uint4 sm4[];
     const int t = threadIdx.x % TPR, ry = threadIdx.x / TPR;
     const int y = yblock * T::ROWS + ry;
@@ -157,14 +157,13 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
     const size_t plane = (size_t)g.W * g.H;
     uint4* myR = sm4 + (size_t)ry * (T::R4 + T::L4);
     uint4* myL = myR + T::R4;
-    // reversed right row: E[k] = R[xmax - k]; pair t at step k needs halfwords E[k0], E[k0 + 1], k0 = NS + 2t - k
+    // reversed right row: E[i] = R[xmax - i]; pair t (disparities t and t + HALF, the split layout) at step k needs
+    // E[i] and E[i + HALF] with i = NS + t - k: staged element i = {E[i], E[i + HALF]}
     const int xmax = xs + NS + g.minX1 - g.minD;
     if (y < g.H) {
         const uint8_t* R = PR + (size_t)y * g.W;
         for (int idx = t; idx < T::R4; idx += TPR) {
-            const int copy = idx / KW, kw = idx - copy * KW;
-            const int k = 2 * kw + copy;
-            const int xa = min(max(xmax - k, 0), g.W - 1), xb = min(max(xmax - k - 1, 0), g.W - 1);
+            const int xa = min(max(xmax - idx, 0), g.W - 1), xb = min(max(xmax - idx - HALF, 0), g.W - 1);
             uint32_t w[4];
 #pragma unroll
             for (int ch = 0; ch < 2; ++ch) {
@@ -188,9 +187,9 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
 #pragma unroll
     for (int q = 0; q < PPT; ++q) {
         const int tq = t + q * TPR;   // this thread's q-th disparity pair
-        padmask[q] = (2 * tq >= g.D ? 0u : 0xffffu) | (2 * tq + 1 >= g.D ? 0u : 0xffff0000u);
+        padmask[q] = (tq >= g.D ? 0u : 0xffffu) | (tq + HALF >= g.D ? 0u : 0xffff0000u);
     }
-    const uint4* pR = myR + NS / 2 + t;   // element of step 0 (even copy) of pair t; pair t + TPR sits TPR elements further
+    const uint4* pR = myR + NS + t;       // element of step 0 of pair t; pair t + TPR sits TPR elements further
     const uint4* pL = myL;
     const int nvalid = min(NS, g.W1 - xs);            // steps whose column lies inside the image
     const int nout = min(NS, g.W1 - xs + SW);         // steps that still produce an output column
@@ -220,7 +219,7 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
             // interior body: every step is inside the image and produces an output (nvalid <= nout)
 #pragma unroll
             for (int i = 0; i < T::BODY; ++i) {
-                const uint4* r = pR + (i & 1) * KW - ((i + 1) >> 1);
+                const uint4* r = pR - i;
                 const uint4 l0 = pL[2 * i], l1 = pL[2 * i + 1];
 #pragma unroll
                 for (int q = 0; q < PPT; ++q) {
@@ -230,7 +229,7 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
                     out[(size_t)i * HALF + q * TPR] = hs[q];
                 }
             }
-            pR -= T::BODY / 2;
+            pR -= T::BODY;
             pL += 2 * T::BODY;
             out += (size_t)T::BODY * HALF;
             continue;
@@ -238,7 +237,7 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
 #pragma unroll
         for (int i = 0; i < T::BODY; ++i) {
             const int k = kb + i;
-            const uint4* r = pR + (i & 1) * KW - ((i + 1) >> 1);
+            const uint4* r = pR - i;
             const uint4 l0 = pL[2 * i], l1 = pL[2 * i + 1];
 #pragma unroll
             for (int q = 0; q < PPT; ++q) {
@@ -249,7 +248,7 @@ __device__ __forceinline__ void pixcost_hsum_block(const uint8_t* __restrict__ P
                 if (k >= kmin && k < nout) out[(size_t)i * HALF + q * TPR] = hs[q];
             }
         }
-        pR -= T::BODY / 2;
+        pR -= T::BODY;
         pL += 2 * T::BODY;
         out += (size_t)T::BODY * HALF;
     }

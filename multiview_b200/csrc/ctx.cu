@@ -26,8 +26,11 @@ void* arena_get(mvs_ctx* ctx, const char* name, size_t bytes)
     if (bytes == 0) bytes = 256;
     if (b.cap >= bytes) return b.p;
     if (b.p) {
-        // growing: earlier work on the stream may still use the old block
+        // growing: earlier work on any of the context's streams may still use the old block (ctx->stream may be the
+        // swapped-in tail stream here, so name all three)
         cudaStreamSynchronize(ctx->stream);
+        if (ctx->tail_stream) cudaStreamSynchronize(ctx->tail_stream);
+        if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
         cudaFree(b.p);
         ctx->arena.total -= b.cap;
         b.p = nullptr;
@@ -139,7 +142,9 @@ extern "C" int mvs_sync(mvs_ctx* ctx)
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->tail_stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
-    return MVS_OK;
+    // the device-resident frame path never copies anything back, so this is where it learns that a bounded wait of
+    // the aggregation sweeps expired (results invalid)
+    return sgbm_aggregate_wave_status(ctx);
 }
 
 extern "C" long long mvs_launch_count(const mvs_ctx* ctx) { return ctx ? ctx->launches : -1; }

@@ -3,14 +3,14 @@
 // cost-functions/disparity/disparity.cpp:68-182).
 #include "common.cuh"
 
-// unpadded copy [h][w1][D] <- device volume [h][w1][Dp]
+// unpadded copy [h][w1][D] (d fastest) <- device volume [h][w1][Dp] in the split layout (common.cuh)
 __global__ void unpad_kernel(const int16_t* __restrict__ src, size_t npix, int D, int Dp, int16_t* __restrict__ dst)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npix * (size_t)D) return;
     size_t p = i / D;
     int d = (int)(i - p * D);
-    dst[i] = src[p * Dp + d];
+    dst[i] = src[p * Dp + split_index(d, Dp)];
 }
 
 static std::string fname(const char* base, int f)

@@ -30,12 +30,15 @@ wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_
             for (int j = 0; j < NW; ++j) wall[q][j] = __ldcs(Sp + j);
         }
     }
+    // split layout (common.cuh): word w of a pixel holds disparity w (low half) and w + Dp/2 (high half)
+    constexpr uint32_t HALF = NW * 32;
     uint32_t padbits[NW];
 #pragma unroll
     for (int j = 0; j < NW; ++j) {
-        const uint32_t d0 = (uint32_t)(lane * NW + j) * 2;
-        padbits[j] = (d0 >= (uint32_t)g.D ? 0xffffu : 0u) | (d0 + 1 >= (uint32_t)g.D ? 0xffff0000u : 0u);
+        const uint32_t d0 = (uint32_t)(lane * NW + j);
+        padbits[j] = (d0 >= (uint32_t)g.D ? 0xffffu : 0u) | (d0 + HALF >= (uint32_t)g.D ? 0xffff0000u : 0u);
     }
+    auto hw_index = [](int d) -> int { return d >= (int)HALF ? 2 * (d - (int)HALF) + 1 : 2 * d; };  // halfword of disparity d in the staged copy
     uint32_t* mysh = sh[wib];
     uint16_t* hw = (uint16_t*)mysh;
     // lane q keeps the outcome of pixel q; the divisions, the atomic and the store happen once per warp at the end
@@ -49,8 +52,8 @@ wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_
         __syncwarp();  // the previous pixel's staged copy has been read by every lane
 #pragma unroll
         for (int j = 0; j < NW; ++j) {
-            const uint32_t d0 = (uint32_t)(lane * NW + j) * 2;
-            key = min(key, min(w[j] * 65536u + d0, (w[j] & 0xffff0000u) | (d0 + 1)));
+            const uint32_t d0 = (uint32_t)(lane * NW + j);
+            key = min(key, min(w[j] * 65536u + d0, (w[j] & 0xffff0000u) | (d0 + HALF)));
             // staged copy for the uniqueness test: padding is taken out of it (0xFFFF never counts)
             mysh[lane * NW + j] = w[j] | padbits[j];
         }
@@ -63,9 +66,9 @@ wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_
         // and the warp takes one packed minimum over what is left.
         int sm = 0, sp = 0;
         if (lane == q) {
-            if (best > 0) { sm = hw[best - 1]; hw[best - 1] = 0xffffu; }
-            if (best < g.D - 1) { sp = hw[best + 1]; hw[best + 1] = 0xffffu; }
-            hw[best] = 0xffffu;
+            if (best > 0) { sm = hw[hw_index(best - 1)]; hw[hw_index(best - 1)] = 0xffffu; }
+            if (best < g.D - 1) { sp = hw[hw_index(best + 1)]; hw[hw_index(best + 1)] = 0xffffu; }
+            hw[hw_index(best)] = 0xffffu;
         }
         __syncwarp();
         uint32_t m = 0xffffffffu;

@@ -29,7 +29,8 @@
 //     plain vectors, no headers) written by warp r-1;
 //   * C (and S in the backward sweep) are loaded straight into registers WAVE_PF pixels ahead (one 16-byte load per
 //     lane and pixel), S is stored from registers: no shared-memory staging, so the rings get all of it;
-//   * the pixel loop is unrolled by WAVE_UNROLL: slot offsets, barrier addresses and global offsets are immediates;
+//   * the pixel loop is unrolled by four: slot offsets, barrier addresses and global offsets are immediates (plus a
+//     per-trip base that selects the half of the eight-deep rings);
 //   * neighbouring warps are coupled only by mbarriers: per ring row eight "pixel p written" and eight "pixel p
 //     consumed" barriers (index p mod 8, phase parity (p / 8) & 1; producer and consumer are never eight pixels
 //     apart, so a parity is never ambiguous).  arrive has release and try_wait acquire semantics at CTA scope: no
@@ -64,11 +65,12 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #define WAVE_D3 8            // ring depth for L3 (4 or 8; lock-step needs 2); L1 and L2 are 8 deep
 #endif
 #ifndef WAVE_PF
-#define WAVE_PF 4            // pixels of C / S prefetched into registers (a power of two <= 8)
+#define WAVE_PF 4            // pixels of C / S prefetched into registers (= WAVE_UNROLL)
 #endif
 #ifndef WAVE_CONS_SLEEP
 #define WAVE_CONS_SLEEP 100
 #endif
+#define WAVE_UNROLL 4        // pixels per trip of the sweep loop = WAVE_PF = half the ring depth
 #ifndef WAVE_FMA_ADDS
 #define WAVE_FMA_ADDS 1      // plain adds on the FMA pipe (IMAD) instead of the ALU pipe
 #endif
@@ -119,6 +121,15 @@ __device__ __forceinline__ void mbar_inval(uint32_t saddr) { asm volatile("mbarr
 __device__ __forceinline__ void mbar_arrive(uint32_t saddr)  // release at CTA scope
 {
     asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(saddr) : "memory");
+}
+// the same, executed by the lanes with on != 0 only, without a branch around it
+__device__ __forceinline__ void mbar_arrive_if(uint32_t saddr, uint32_t on)
+{
+    asm volatile("{ .reg .b64 st; .reg .pred q; setp.ne.u32 q, %1, 0; @q mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(saddr), "r"(on) : "memory");
+}
+__device__ __forceinline__ void st_release_if(int* p, int v, uint32_t on)
+{
+    asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q st.release.gpu.global.s32 [%0], %1; }" ::"l"(p), "r"(v), "r"(on) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint32_t saddr, uint32_t parity)  // acquire at CTA scope; may suspend the warp
 {
@@ -206,40 +217,6 @@ __device__ __forceinline__ uint32_t addf(uint32_t a, uint32_t b, uint32_t one)
 #endif
 }
 
-// One path step.  a[] = Ln of the predecessor pixel (this lane's words).  Computes L = C + min(Ln(d), Ln(d+-1) + P1)
-// into l[], the normalised clamped vector min(L - min L, P2) into ln[].
-template <int NW, bool PAD>
-__device__ __forceinline__ void step_dir(const uint32_t (&a)[NW], const uint32_t (&Cw)[NW], const LaneConst& k,
-                                         const uint32_t (&padsent)[NW], uint32_t (&l)[NW], uint32_t (&ln)[NW])
-{
-    uint32_t ap[NW];
-#pragma unroll
-    for (int j = 0; j < NW; ++j) ap[j] = addf(a[j], k.P1x2, k.one);
-    // neighbours across the lane edge: word NW-1 of lane-1 holds d-1 of this lane's word 0 (both halves), except in
-    // lane 0, where the low half's neighbour is d = -1 (sentinel) and the high half's is lane 31's LOW half (d = Dp/2 - 1)
-    const uint32_t apl = __byte_perm(__shfl_sync(0xffffffffu, ap[NW - 1], k.lm1), SENT2, k.selL);
-    const uint32_t apr = __byte_perm(__shfl_sync(0xffffffffu, ap[0], k.lp1), SENT2, k.selR);
-    uint32_t m = SENT2;
-#pragma unroll
-    for (int j = 0; j < NW; ++j) {
-        const uint32_t lo = j == 0 ? apl : ap[j == 0 ? 0 : j - 1];
-        const uint32_t hi = j == NW - 1 ? apr : ap[j == NW - 1 ? j : j + 1];
-        const uint32_t t = __vimin3_u16x2(lo, hi, a[j]);
-        uint32_t v = addf(t, Cw[j], k.one);      // per half <= P2 + Cmax <= 32767 (mvs_sgbm_check)
-        if (PAD) v |= padsent[j];                // padding disparities (d >= D) act as the reference's d = D sentinel
-        l[j] = v;
-    }
-    if (NW == 4) m = __vminu2(__vimin3_u16x2(l[0], l[1 % NW], l[2 % NW]), l[3 % NW]);
-    else if (NW == 3) m = __vimin3_u16x2(l[0], l[1 % NW], l[2 % NW]);
-    else if (NW == 2) m = __vminu2(l[0], l[1 % NW]);
-    else m = l[0];
-    m = __vminu2(m, __byte_perm(m, m, 0x1032));                 // min of the two halves, in both halves
-    m = __reduce_min_sync(0xffffffffu, m);                      // (v << 16 | v) is monotone in v: the result is duplicated too
-    const uint32_t negm = __byte_perm(0u - m, 0u, 0x1010);      // -min per half (the low half of the 32-bit negation)
-#pragma unroll
-    for (int j = 0; j < NW; ++j) ln[j] = __viaddmin_s16x2(l[j], negm, k.P2x2);
-}
-
 template <int K> struct IC { static constexpr int value = K; };
 
 template <int NW, int DIRMASK, bool PAD, bool BWD>
@@ -318,9 +295,6 @@ wave_kernel(WaveParams p)
         // time: a wait that expires, here or anywhere else in the grid, raises the error flag and ends all waiting (results
         // are then invalid and the host reports an error), so a logic fault cannot hang the GPU.
         auto wait_bar = [&](uint32_t bar, uint32_t par, int kind, int pixel) {
-#ifdef WAVE_DBG_NOWAIT   // timing experiment: wrong results
-            return;
-#endif
             if (mbar_try_wait(bar, par)) return;
             if (failed) return;
             unsigned long long t0 = 0;
@@ -341,6 +315,32 @@ wave_kernel(WaveParams p)
                 if (kind == 2) __nanosleep(WAVE_CONS_SLEEP);
 #endif
             }
+        };
+        // the two waits of a pixel in one loop (one slow path per pixel in the unrolled body): okf / okc hold what the early
+        // tests saw and are left non-zero
+        auto wait_both = [&](uint32_t bf, uint32_t pf, uint32_t& okf, uint32_t bc, uint32_t pc, uint32_t& okc, int pixel) {
+            if (failed) { okf = okc = 1u; return; }
+            unsigned long long t0 = 0;
+            int spins = 0;
+            for (;;) {
+                if (!okf) okf = mbar_try_wait(bf, pf);
+                if (okf && !okc) okc = mbar_try_wait(bc, pc);
+                if (okf && okc) break;
+                if ((++spins & 127) == 0) {
+                    if (*(volatile int*)p.error) { failed = true; break; }
+                    const unsigned long long t = global_ns();
+                    if (!t0) t0 = t;
+                    else if (t - t0 > WAVE_TIMEOUT_NS) {
+                        atomicCAS(p.error, 0, ((okf ? 2 : 1) << 28) | ((r & 31) << 23) | ((band & 127) << 16) | (pixel & 0xffff));
+                        failed = true;
+                        break;
+                    }
+                }
+#if WAVE_CONS_SLEEP
+                if (okf) __nanosleep(WAVE_CONS_SLEEP);   // only the back-pressure wait is left: this warp is ahead
+#endif
+            }
+            okf = okc = 1u;
         };
 
         // zero slots prepared before anybody runs: the row above the image, and "x = -1" of the row each warp reads
@@ -407,116 +407,174 @@ wave_kernel(WaveParams p)
             const int ys = ys0 + r;
             const int y = BWD ? p.H - 1 - ys : ys;
             const size_t gbase = ((size_t)y * W1 + (BWD ? W1 - 1 : 0)) * WPP + lane * NW;
-            const uint32_t* cptr = fr.C + gbase;       // pixel x8 of this row (this lane's words)
+            const uint32_t* cptr = fr.C + gbase;       // pixel x4 of this row (this lane's words)
             const uint32_t* sptr = BWD ? fr.Sin + gbase : nullptr;
             uint32_t* optr = fr.Sout + gbase;
-            uint32_t* gout = bout + lane * NW;         // this lane's words of boundary pixel x8, direction 1
+            uint32_t* gout = bout + lane * NW;         // this lane's words of boundary pixel x4, direction 1
             // register prefetch ring: pixel q lives in slot q % PF
             uint32_t Cq[PF][NW], Sq[PF][NW];
 #pragma unroll
             for (int q = 0; q < PF; ++q) {
 #pragma unroll
-                for (int j = 0; j < NW; ++j) { Cq[q][j] = 0; Sq[q][j] = 0; }
-                if (q < W1) {
-                    ldg_stream<NW>(cptr + q * GS, Cq[q]);
-                    if (BWD) ldg_stream<NW>(sptr + q * GS, Sq[q]);
-                }
+                for (int j = 0; j < NW; ++j) Sq[q][j] = 0;
+                ldg_stream<NW>(cptr + q * GS, Cq[q]);
+                if (BWD) ldg_stream<NW>(sptr + q * GS, Sq[q]);
             }
+            const uint32_t lane0 = lane == 0 ? 1u : 0u, lane0_ring = lane == 0 && to_ring ? 1u : 0u;
+            // Barrier tests for the coming pixel are issued one pixel early (their ~90 cycles of latency overlap the
+            // arithmetic); a direction that has nothing to wait for counts as passed.  Pixel 0 starts untested.
+            uint32_t ok_full = wait_above ? 0u : 1u, ok_cons = to_ring ? 0u : 1u;
 
-            for (int x8 = 0; x8 < W1; x8 += WAVE_NB) {
-                const int rem = W1 - x8;                          // pixels left in the row, this trip included
-                const uint32_t par = (uint32_t)(x8 >> 3) & 1u;    // phase parity of pixels x8 .. x8 + 7
+            // The pixel loop is unrolled by UN = 4 (the prefetch depth; half the ring depth: the instruction footprint of
+            // an unroll by eight does not fit the instruction cache).  Trip t covers pixels 4t .. 4t+3, which live in
+            // half h = t & 1 of the eight-deep rings and barrier sets: "c" pointers address the current half, "o"
+            // pointers the other one; par is the phase parity of the current block of eight pixels.
+            constexpr int UN = WAVE_UNROLL, WAR = WAVE_WAR;
+            for (int x4 = 0; x4 < W1; x4 += UN) {
+                const int rem = W1 - x4;                          // pixels left in the row, this trip included
+                const uint32_t h = (uint32_t)(x4 >> 2) & 1u, par = (uint32_t)(x4 >> 3) & 1u;
+                const int hw = h ? 4 * WPP : 0;                   // word offset of the current half of a ring
+                const uint32_t hb = h ? 32u : 0u;                 // byte offset of the current half of a barrier set
+                const uint32_t* rdc = rd + hw;
+                const uint32_t* rdo = rd + (4 * WPP - hw);
+                uint32_t* wrc = wr + hw;
+                const uint32_t fullc = my_full + hb, fullo = my_full + (32u - hb);
+                const uint32_t consc = dn_cons + hb, conso = dn_cons + (32u - hb);
+                const uint32_t arr_full = dn_full + hb, arr_cons = my_cons + hb;
                 auto body = [&](auto kk) {
                     constexpr int k = decltype(kk)::value;
                     if (k >= rem) return;
-                    const int x = x8 + k;
-                    // operands of this pixel; the freed prefetch slot is refilled with pixel x + PF
-                    uint32_t Cw[NW], Sw[NW];
+                    const int x = x4 + k;
+                    uint32_t (&Cw)[NW] = Cq[k % PF];   // operands of this pixel: loaded PF pixels ago
+                    uint32_t (&Sw)[NW] = Sq[k % PF];
+#ifndef WAVE_DBG_NOWAIT   // (timing experiment: wrong results)
+                    // (1) the row above is written through pixel x + 1; (2) the slots about to be overwritten were read:
+                    // pixel x - WAR - 1 of the row below is finished.  For x <= WAR that barrier is still in its first
+                    // phase and the wait on the opposite parity passes at once (the row below cannot finish pixel
+                    // x - WAR + 7 before this row has written x - WAR + 8 > x).
+                    if (__builtin_expect((ok_full & ok_cons) == 0u, 0)) {
+                        const uint32_t bf = k == 3 ? fullo : fullc + (k + 1) * 8u, pf = k == 3 ? par ^ h : par;
+                        const uint32_t bc = WAR == 6 ? (k == 3 ? conso : consc + (k + 1) * 8u) : (k == 0 ? consc + 24u : conso + (k - 1) * 8u);
+                        const uint32_t pc = WAR == 6 ? pf ^ 1u : (k == 0 ? par ^ 1u : par ^ h ^ 1u);
+                        wait_both(bf, pf, ok_full, bc, pc, ok_cons, x);
+                    }
+#endif
+                    // All directions advance together, phase by phase, so that the warp always has four independent
+                    // dependency chains in flight (a direction alone is one chain of ~15 dependent operations with a
+                    // shuffle and a warp reduction in it; the sweep is bound by that latency, not by issue slots).
+                    constexpr bool on[4] = {(DIRMASK & 1) != 0, (DIRMASK & 2) != 0, (DIRMASK & 4) != 0, (DIRMASK & 8) != 0};
+                    uint32_t a[4][NW], ap[4][NW], el[4], er[4], l[4][NW], m[4], acc[NW];
 #pragma unroll
-                    for (int j = 0; j < NW; ++j) { Cw[j] = Cq[k % PF][j]; Sw[j] = Sq[k % PF][j]; }
-                    {
-                        // (beyond the row's end the slot's contents are never used: it is left undefined rather than preserved)
-                        uint32_t nc[NW], ns[NW];
+                    for (int j = 0; j < NW; ++j) a[0][j] = L0[j];
+                    if (on[1]) ldw<NW>(k == 0 ? rdo + 3 * WPP : rdc + (k - 1) * WPP, a[1]);                   // L1 of pixel x - 1
+                    if (on[2]) ldw<NW>(rdc + RG::O2 + k * WPP, a[2]);                                         // L2 of pixel x
+                    if (on[3]) ldw<NW>(RG::D3 == 8 ? (k == 3 ? rdo + RG::O3 : rdc + RG::O3 + (k + 1) * WPP)   // L3 of pixel x + 1
+                                                   : rd + RG::O3 + ((k + 1) & 3) * WPP, a[3]);
+#ifndef WAVE_DBG_NOWAIT
+                    // test the NEXT pixel's two barriers now (looked at when the next pixel starts)
+                    if (VERT && k + 1 < rem) {
+                        const uint32_t bf = k >= 2 ? fullo + (k - 2) * 8u : fullc + (k + 2) * 8u, pf = k >= 2 ? par ^ h : par;
+                        const uint32_t bc = WAR == 6 ? (k >= 2 ? conso + (k - 2) * 8u : consc + (k + 2) * 8u) : conso + k * 8u;
+                        const uint32_t pc = WAR == 6 ? pf ^ 1u : par ^ h ^ 1u;
+                        if (wait_above) ok_full = mbar_try_wait(bf, pf);
+                        if (to_ring) ok_cons = mbar_try_wait(bc, pc);
+                    }
+#endif
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) { asm("" : "=r"(nc[j])); asm("" : "=r"(ns[j])); }
-                        if (k + PF < rem) {
-                            ldg_stream<NW>(cptr + (k + PF) * GS, nc);
-                            if (BWD) ldg_stream<NW>(sptr + (k + PF) * GS, ns);
+                    for (int d = 0; d < 4; ++d)
+                        if (on[d]) {
+#pragma unroll
+                            for (int j = 0; j < NW; ++j) ap[d][j] = addf(a[d][j], kc.P1x2, kc.one);
+                        }
+                    // neighbours across the lane edge: word NW-1 of lane-1 holds d-1 of this lane's word 0 (both halves), except
+                    // in lane 0, where the low half's neighbour is d = -1 (sentinel) and the high half's is lane 31's LOW half
+#pragma unroll
+                    for (int d = 0; d < 4; ++d)
+                        if (on[d]) {
+                            el[d] = __shfl_sync(0xffffffffu, ap[d][NW - 1], kc.lm1);
+                            er[d] = __shfl_sync(0xffffffffu, ap[d][0], kc.lp1);
                         }
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) { Cq[k % PF][j] = nc[j]; Sq[k % PF][j] = ns[j]; }
-                    }
-                    // the row above is written through pixel x + 1
-                    if (wait_above) wait_bar(my_full + (uint32_t)((k + 1) & 7) * 8u, k + 1 >= 8 ? par ^ 1u : par, 1, x);
-                    // the slots about to be overwritten were read (pixel x - WAR - 1 of the row below is finished).  For
-                    // x <= WAR the barrier is still in its first phase and the wait on the opposite parity passes at once
-                    // (the row below cannot finish pixel x - WAR + 7 before this row has written x - WAR + 8 > x)
-                    if (to_ring)
-                        wait_bar(dn_cons + (uint32_t)((k + 8 - WAVE_WAR - 1) & 7) * 8u, k >= WAVE_WAR + 1 ? par : par ^ 1u, 2, x);
-                    uint32_t acc[NW], l[NW], ln[NW];
-                    if (DIRMASK & 1) {  // direction 0: predecessor (x-1, y), kept in registers
-                        step_dir<NW, PAD>(L0, Cw, kc, padsent, acc, ln);
+                    for (int d = 0; d < 4; ++d)
+                        if (on[d]) {
+                            el[d] = __byte_perm(el[d], SENT2, kc.selL);
+                            er[d] = __byte_perm(er[d], SENT2, kc.selR);
+                        }
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) L0[j] = ln[j];
-                    } else {
+                    for (int d = 0; d < 4; ++d)
+                        if (on[d]) {
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = 0;
-                    }
-                    if (DIRMASK & 2) {  // direction 1: predecessor (x-1, y-1)
-                        uint32_t a[NW];
-                        ldw<NW>(rd + ((k + 7) & 7) * WPP, a);
-                        step_dir<NW, PAD>(a, Cw, kc, padsent, l, ln);
+                            for (int j = 0; j < NW; ++j) {
+                                const uint32_t lo = j == 0 ? el[d] : ap[d][j == 0 ? 0 : j - 1];
+                                const uint32_t hi = j == NW - 1 ? er[d] : ap[d][j == NW - 1 ? j : j + 1];
+                                uint32_t v = addf(__vimin3_u16x2(lo, hi, a[d][j]), Cw[j], kc.one);   // per half <= P2 + Cmax <= 32767
+                                if (PAD) v |= padsent[j];   // padding disparities (d >= D) act as the reference's d = D sentinel
+                                l[d][j] = v;
+                            }
+                        }
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], l[j], SENT2);
-                        if (to_ring) stw<NW>(wr + k * WPP, ln);
-                        if (to_global) stg_stream<NW>(gout + k * 3 * WPP, ln);
-                    }
-                    if (DIRMASK & 4) {  // direction 2: predecessor (x, y-1)
-                        uint32_t a[NW];
-                        ldw<NW>(rd + RG::O2 + k * WPP, a);
-                        step_dir<NW, PAD>(a, Cw, kc, padsent, l, ln);
+                    for (int d = 0; d < 4; ++d)
+                        if (on[d]) {
+                            uint32_t mm;
+                            if (NW == 4) mm = __vminu2(__vimin3_u16x2(l[d][0], l[d][1 % NW], l[d][2 % NW]), l[d][3 % NW]);
+                            else if (NW == 3) mm = __vimin3_u16x2(l[d][0], l[d][1 % NW], l[d][2 % NW]);
+                            else if (NW == 2) mm = __vminu2(l[d][0], l[d][1 % NW]);
+                            else mm = l[d][0];
+                            m[d] = __vminu2(mm, __byte_perm(mm, mm, 0x1032));   // min of the two halves, in both halves
+                        }
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], l[j], SENT2);
-                        if (to_ring) stw<NW>(wr + RG::O2 + k * WPP, ln);
-                        if (to_global) stg_stream<NW>(gout + (k * 3 + 1) * WPP, ln);
-                    }
-                    if (DIRMASK & 8) {  // direction 3: predecessor (x+1, y-1)
-                        uint32_t a[NW];
-                        ldw<NW>(rd + RG::O3 + ((k + 1) & (RG::D3 - 1)) * WPP, a);
-                        step_dir<NW, PAD>(a, Cw, kc, padsent, l, ln);
+                    for (int d = 0; d < 4; ++d)
+                        if (on[d]) m[d] = __reduce_min_sync(0xffffffffu, m[d]);   // (v << 16 | v) is monotone in v: still duplicated
+                    // S accumulation (the reference saturates once per pass; all terms are non-negative, so clamping as we go is the same)
 #pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(acc[j], l[j], SENT2);
-                        if (to_ring) stw<NW>(wr + RG::O3 + (k & (RG::D3 - 1)) * WPP, ln);
-                        if (to_global) stg_stream<NW>(gout + (k * 3 + 2) * WPP, ln);
-                    }
-                    // S = min(S_in + sum L, 32767)
-                    if (BWD) {
-#pragma unroll
-                        for (int j = 0; j < NW; ++j) acc[j] = __viaddmin_u16x2(Sw[j], acc[j], SENT2);
+                    for (int j = 0; j < NW; ++j) {
+                        uint32_t s = on[1] ? __viaddmin_u16x2(l[0][j], l[1][j], SENT2) : l[0][j];
+                        if (on[2] && on[3]) s = __viaddmin_u16x2(s, __viaddmin_u16x2(l[2][j], l[3][j], SENT2), SENT2);
+                        else if (on[2]) s = __viaddmin_u16x2(s, l[2][j], SENT2);
+                        if (BWD) s = __viaddmin_u16x2(Sw[j], s, SENT2);   // S = min(S_in + sum L, 32767)
+                        acc[j] = s;
                     }
                     stg_stream<NW>(optr + k * GS, acc);
-                    if (to_global && (k == WAVE_NB - 1 || k + 1 == rem)) {
+                    // Refill the prefetch slot with pixel x + PF, AFTER its last use, so that the load can target the same
+                    // registers (issued earlier it gets temporaries, and the move into place waits for the load one pixel
+                    // later).  Unconditional: beyond the row's end it reads up to PF pixels of the neighbouring row or of
+                    // the guard band the volumes are allocated with (MVS_VOLUME_GUARD); those values are never used.
+                    ldg_stream<NW>(cptr + (k + PF) * GS, Cq[k % PF]);
+                    if (BWD) ldg_stream<NW>(sptr + (k + PF) * GS, Sq[k % PF]);
+#pragma unroll
+                    for (int d = 0; d < 4; ++d)
+                        if (on[d]) {
+                            const uint32_t negm = __byte_perm(0u - m[d], 0u, 0x1010);   // -min per half (low half of the 32-bit negation)
+#pragma unroll
+                            for (int j = 0; j < NW; ++j) l[d][j] = __viaddmin_s16x2(l[d][j], negm, kc.P2x2);   // l now holds Ln
+                        }
+#pragma unroll
+                    for (int j = 0; j < NW; ++j) L0[j] = l[0][j];
+                    if (on[1]) { if (to_ring) stw<NW>(wrc + k * WPP, l[1]); if (to_global) stg_stream<NW>(gout + k * 3 * WPP, l[1]); }
+                    if (on[2]) { if (to_ring) stw<NW>(wrc + RG::O2 + k * WPP, l[2]); if (to_global) stg_stream<NW>(gout + (k * 3 + 1) * WPP, l[2]); }
+                    if (on[3]) {
+                        if (to_ring) stw<NW>((RG::D3 == 8 ? wrc : wr) + RG::O3 + k * WPP, l[3]);
+                        if (to_global) stg_stream<NW>(gout + (k * 3 + 2) * WPP, l[3]);
+                    }
+                    if (to_global && ((k == UN - 1 && h) || k + 1 == rem)) {
                         // the warp barrier orders every lane's boundary stores before lane 0's release store
                         // (release is cumulative over what the warp barrier made visible to lane 0)
                         __syncwarp();
-                        if (lane == 0) st_release(my_progress, x + 1);
+                        st_release_if(my_progress, x + 1, lane0);
                     }
                     if (VERT) {
                         // publish: ring row r+1 holds pixel x; ring row r has been read for pixel x.  The warp barrier
                         // puts every lane's ring reads and writes before lane 0's arrivals (release).
                         __syncwarp();
-                        if (lane == 0) {
-                            if (to_ring) mbar_arrive(dn_full + (uint32_t)k * 8u);
-                            mbar_arrive(my_cons + (uint32_t)k * 8u);
-                        }
+                        mbar_arrive_if(arr_full + (uint32_t)k * 8u, lane0_ring);
+                        mbar_arrive_if(arr_cons + (uint32_t)k * 8u, lane0);
                     }
                 };
                 body(IC<0>()); body(IC<1>()); body(IC<2>()); body(IC<3>());
-                body(IC<4>()); body(IC<5>()); body(IC<6>()); body(IC<7>());
-                cptr += WAVE_NB * GS;
-                if (BWD) sptr += WAVE_NB * GS;
-                optr += WAVE_NB * GS;
-                gout += WAVE_NB * 3 * WPP;
+                cptr += UN * GS;
+                if (BWD) sptr += UN * GS;
+                optr += UN * GS;
+                gout += UN * 3 * WPP;
             }
             if (to_ring) {
                 // zero vector "x = W1" for direction 3 of the row below (its predecessor is outside the image);

@@ -113,6 +113,9 @@ static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b)
 // pixel holds disparity w in its low half and disparity w + Dp/2 in its high half.  In packed u16x2 arithmetic the
 // d-1 / d+1 neighbours of a word are then the previous / next WORD (no byte permutes in the aggregation sweep).
 __host__ __device__ static inline int split_index(int d, int Dp) { return d >= Dp / 2 ? 2 * (d - Dp / 2) + 1 : 2 * d; }  // halfword of disparity d
+// The aggregation sweep prefetches a few pixels past the end of a row without a bounds test: the volumes are allocated
+// with this many bytes of guard on either side (never used as data).
+#define MVS_VOLUME_GUARD 4096
 struct SgbmGeom {
     int W, H, D, minD, minX1, W1;
     int Dp;  // disparities per pixel in the device volumes (D rounded up to a multiple of 64)
@@ -121,6 +124,7 @@ struct SgbmGeom {
     size_t cells() const { return (size_t)H * W1 * Dp; }
 };
 int sgbm_geom(mvs_ctx* ctx, const mvs_sgbm_params* p, int w, int h, SgbmGeom* g);
+int16_t* sgbm_volume(mvs_ctx* ctx, const char* name, const SgbmGeom& g);   // arena volume with guard bands; nullptr on failure
 
 // ---- device-pointer stage entry points (all asynchronous on ctx->stream) ------------------------------
 int remap_cubic_bgr8_batch_dev(mvs_ctx* ctx, int n, const uint8_t* const* src, int sw, int sh, size_t sstep, const float* const* mapx,

@@ -13,6 +13,12 @@ __global__ void unpad_kernel(const int16_t* __restrict__ src, size_t npix, int D
     dst[i] = src[p * Dp + split_index(d, Dp)];
 }
 
+int16_t* sgbm_volume(mvs_ctx* ctx, const char* name, const SgbmGeom& g)
+{
+    char* p = (char*)arena_get(ctx, name, g.cells() * 2 + 2 * MVS_VOLUME_GUARD);
+    return p ? (int16_t*)(p + MVS_VOLUME_GUARD) : nullptr;
+}
+
 static std::string fname(const char* base, int f)
 {
     char buf[64];
@@ -34,8 +40,8 @@ int sgbm_front_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const ui
     if (rc) return rc;
     int16_t* C[MVS_MAX_BATCH];
     for (int f = 0; f < F; ++f) {
-        C[f] = (int16_t*)arena_get(ctx, fname("sgbm.C", f).c_str(), g.cells() * 2);
-        S[f] = (int16_t*)arena_get(ctx, fname(sset ? "sgbm.S1" : "sgbm.S", f).c_str(), g.cells() * 2);
+        C[f] = sgbm_volume(ctx, fname("sgbm.C", f).c_str(), g);
+        S[f] = sgbm_volume(ctx, fname(sset ? "sgbm.S1" : "sgbm.S", f).c_str(), g);
         if (!C[f] || !S[f]) return MVS_ERR_NOMEM;
     }
     stage_begin(ctx, "cost");
@@ -166,7 +172,7 @@ extern "C" int mvs_sgbm_volumes(mvs_ctx* ctx, const mvs_sgbm_params* p, const ui
     int16_t* outs[2] = {C, S};
     for (int k = 0; k < 2; ++k) {
         if (!outs[k]) continue;
-        const int16_t* src = (const int16_t*)arena_get(ctx, names[k], g.cells() * 2);
+        const int16_t* src = sgbm_volume(ctx, names[k], g);
         unpad_kernel<<<cdiv(npix * g.D, 256), 256, 0, ctx->stream>>>(src, npix, g.D, g.Dp, tmp);
         MVS_LAUNCH_CHECK(ctx, "unpad_kernel");
         MVS_CUDA(ctx, cudaMemcpyAsync(outs[k], tmp, npix * g.D * 2, cudaMemcpyDeviceToHost, ctx->stream));

@@ -138,6 +138,26 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t saddr, uint32_t parity)  
                  : "=r"(ok) : "r"(saddr), "r"(parity) : "memory");
     return ok != 0;
 }
+// Early barrier tests: the test is issued in the middle of one pixel and its outcome is read when the next pixel starts,
+// so the ~90 cycles a try_wait takes (even on a completed phase) overlap the arithmetic.  The outcome stays in a PTX
+// predicate in between (reading it into a register right away would wait for it): wave_kernel declares the predicates
+// wave_pf / wave_pc once at function scope and these helpers name them.
+__device__ __forceinline__ void early_test_full(uint32_t saddr, uint32_t parity)
+{
+    asm volatile("mbarrier.try_wait.parity.shared::cta.b64 wave_pf, [%0], %1;" ::"r"(saddr), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void early_test_cons(uint32_t saddr, uint32_t parity)
+{
+    asm volatile("mbarrier.try_wait.parity.shared::cta.b64 wave_pc, [%0], %1;" ::"r"(saddr), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void early_set(uint32_t full_passed, uint32_t cons_passed)
+{
+    asm volatile("setp.ne.u32 wave_pf, %0, 0; setp.ne.u32 wave_pc, %1, 0;" ::"r"(full_passed), "r"(cons_passed) : "memory");
+}
+__device__ __forceinline__ void early_read(uint32_t& full_passed, uint32_t& cons_passed)
+{
+    asm volatile("selp.u32 %0, 1, 0, wave_pf; selp.u32 %1, 1, 0, wave_pc;" : "=r"(full_passed), "=r"(cons_passed)::"memory");
+}
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gmem)
 {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
@@ -224,6 +244,7 @@ __global__ void __launch_bounds__(Ring<NW>::THREADS, 1)
 wave_kernel(WaveParams p)
 {
     using RG = Ring<NW>;
+    asm volatile(".reg .pred wave_pf, wave_pc;");   // outcomes of the early barrier tests (see early_test_full)
     constexpr bool VERT = (DIRMASK & 0xE) != 0;
     constexpr int WAVE_R = RG::R, WPP = RG::WPP, PF = WAVE_PF;
     constexpr int GS = BWD ? -WPP : WPP;   // word step from pixel to pixel along the sweep
@@ -423,7 +444,7 @@ wave_kernel(WaveParams p)
             const uint32_t lane0 = lane == 0 ? 1u : 0u, lane0_ring = lane == 0 && to_ring ? 1u : 0u;
             // Barrier tests for the coming pixel are issued one pixel early (their ~90 cycles of latency overlap the
             // arithmetic); a direction that has nothing to wait for counts as passed.  Pixel 0 starts untested.
-            uint32_t ok_full = wait_above ? 0u : 1u, ok_cons = to_ring ? 0u : 1u;
+            early_set(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
 
             // The pixel loop is unrolled by UN = 4 (the prefetch depth; half the ring depth: the instruction footprint of
             // an unroll by eight does not fit the instruction cache).  Trip t covers pixels 4t .. 4t+3, which live in
@@ -452,6 +473,8 @@ wave_kernel(WaveParams p)
                     // pixel x - WAR - 1 of the row below is finished.  For x <= WAR that barrier is still in its first
                     // phase and the wait on the opposite parity passes at once (the row below cannot finish pixel
                     // x - WAR + 7 before this row has written x - WAR + 8 > x).
+                    uint32_t ok_full, ok_cons;
+                    early_read(ok_full, ok_cons);
                     if (__builtin_expect((ok_full & ok_cons) == 0u, 0)) {
                         const uint32_t bf = k == 3 ? fullo : fullc + (k + 1) * 8u, pf = k == 3 ? par ^ h : par;
                         const uint32_t bc = WAR == 6 ? (k == 3 ? conso : consc + (k + 1) * 8u) : (k == 0 ? consc + 24u : conso + (k - 1) * 8u);
@@ -476,8 +499,10 @@ wave_kernel(WaveParams p)
                         const uint32_t bf = k >= 2 ? fullo + (k - 2) * 8u : fullc + (k + 2) * 8u, pf = k >= 2 ? par ^ h : par;
                         const uint32_t bc = WAR == 6 ? (k >= 2 ? conso + (k - 2) * 8u : consc + (k + 2) * 8u) : conso + k * 8u;
                         const uint32_t pc = WAR == 6 ? pf ^ 1u : par ^ h ^ 1u;
-                        if (wait_above) ok_full = mbar_try_wait(bf, pf);
-                        if (to_ring) ok_cons = mbar_try_wait(bc, pc);
+                        if (wait_above) early_test_full(bf, pf);
+                        if (to_ring) early_test_cons(bc, pc);
+                    } else if (VERT) {
+                        early_set(wait_above ? 0u : 1u, to_ring ? 0u : 1u);   // the next row starts untested
                     }
 #endif
 #pragma unroll

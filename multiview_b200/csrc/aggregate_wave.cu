@@ -38,7 +38,7 @@
 //   * image borders need no branches: the slots "x = -1" and "x = W1" are zero vectors (Lr = 0, minLr = 0 outside
 //     the image, as the reference initialises its Lr buffers; a zero vector is its own normalised form);
 //   * bands are chained through global memory: the last warp of a band streams its vectors to a boundary buffer and
-//     publishes its progress every eight pixels; a helper warp of the next band waits for that progress and copies
+//     publishes its progress every WAVE_PUBLISH pixels; a helper warp of the next band waits for that progress and copies
 //     the boundary row into ring row 0 with cp.async a few pixels ahead of its consumer;
 //   * a launch covers a batch of frames; (frame, band) items are handed out by an atomic ticket in dependency
 //     order, so the band a CTA waits for is always running or finished (no co-residency assumption); every wait
@@ -69,6 +69,12 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #endif
 #ifndef WAVE_CONS_SLEEP
 #define WAVE_CONS_SLEEP 100
+#endif
+#ifndef WAVE_PUBLISH
+#define WAVE_PUBLISH 16      // a band's last row publishes its progress every this many pixels (a power of two >= 4;
+#endif                       // measured: 8 and 32 are slower)
+#ifndef WAVE_HELPER_LAG
+#define WAVE_HELPER_LAG 3    // boundary copies in flight in the helper warp (4 measured the same, 5 stalls)
 #endif
 #define WAVE_UNROLL 4        // pixels per trip of the sweep loop = WAVE_PF = half the ring depth
 #ifndef WAVE_FMA_ADDS
@@ -304,7 +310,13 @@ wave_kernel(WaveParams p)
         const WaveFrame& fr = p.f[fi];
         const int ys0 = band * WAVE_R;  // first sweep row of the band
         const int rows = min(WAVE_R, p.H - ys0);
+#if defined(WAVE_DBG_NOCHAIN)           // timing experiment (wrong results): every band behaves like the first and the last one
+        const bool first_band = true, last_band = true;
+#elif defined(WAVE_DBG_NOCHAIN_STORE)   // timing experiment (wrong results): nobody reads the boundary rows, but they are written
+        const bool first_band = true, last_band = band == p.nbands - 1;
+#else
         const bool first_band = band == 0, last_band = band == p.nbands - 1;
+#endif
         const uint32_t* bin = fr.bnd + (size_t)(first_band ? 0 : band - 1) * W1 * 3 * WPP;  // written by the previous band
         uint32_t* bout = fr.bnd + (size_t)band * W1 * 3 * WPP;
         int* my_progress = p.progress + (size_t)fi * p.nbands + band;
@@ -378,7 +390,8 @@ wave_kernel(WaveParams p)
             if (VERT && !first_band) {  // (first band: everything above the image is zero, warp 0 does not wait)
                 // boundary row of the previous band -> ring row 0, a few pixels ahead of publication
                 int seen = 0;
-                for (int xp = 0; xp <= W1 + 2; ++xp) {
+                constexpr int HL = WAVE_HELPER_LAG;   // copy groups in flight behind the newest one
+                for (int xp = 0; xp <= W1 + HL; ++xp) {
                     if (xp <= W1) {
                         // the slots of pixel xp last held pixels xp - 8 (L1: read by warp 0 at its pixel xp - 7) and xp - D3
                         // (L3: read at xp - D3 - 1)
@@ -412,10 +425,10 @@ wave_kernel(WaveParams p)
                         }
                     }
                     cp_async_commit();
-                    cp_async_wait<2>();  // the group of pixel xp - 2 has landed
-                    if (xp >= 2) {
-                        __syncwarp();  // all lanes' copies are in; lane 0 publishes pixel xp - 2
-                        if (lane == 0) mbar_arrive(full_s + (uint32_t)((xp - 2) & 7) * 8u);
+                    cp_async_wait<HL>();  // the group of pixel xp - HL has landed
+                    if (xp >= HL) {
+                        __syncwarp();  // all lanes' copies are in; lane 0 publishes pixel xp - HL
+                        if (lane == 0) mbar_arrive(full_s + (uint32_t)((xp - HL) & 7) * 8u);
                     }
                 }
             }
@@ -581,7 +594,7 @@ wave_kernel(WaveParams p)
                         if (to_ring) stw<NW>((RG::D3 == 8 ? wrc : wr) + RG::O3 + k * WPP, l[3]);
                         if (to_global) stg_stream<NW>(gout + (k * 3 + 2) * WPP, l[3]);
                     }
-                    if (to_global && ((k == UN - 1 && h) || k + 1 == rem)) {
+                    if (to_global && ((k == UN - 1 && ((x + 1) & (WAVE_PUBLISH - 1)) == 0) || k + 1 == rem)) {
                         // the warp barrier orders every lane's boundary stores before lane 0's release store
                         // (release is cumulative over what the warp barrier made visible to lane 0)
                         __syncwarp();

@@ -131,13 +131,18 @@ int mvs_point_cloud(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, size_
  * streams), or an application whose own pool already owns all GPU memory (cudaMalloc would fail).
  *   - All pointers are DEVICE pointers supplied by the caller: disp_dev (w*h floats, tightly packed), Xs_dev
  *     (capacity w*h*3 doubles), xy_dev (capacity w*h*2 int32), lookup_dev (w*h int32), n_dev (one int32),
- *     centroid_dev (3 doubles).  The call is asynchronous on the context's stream (mvs_sync to wait).
+ *     centroid_dev (3 doubles).  The call is asynchronous on the context's MAIN stream, mvs_stream() (mvs_sync to
+ *     wait).  That stream is not ordered behind the frame path's second half: a disparity taken from
+ *     mvs_frame_result.disp_dev is produced on mvs_tail_stream(), so make the main stream wait for it first
+ *     (an event recorded on the tail stream, or mvs_sync).
  *   - It performs no cudaMalloc/cudaFree and calls nothing that allocates.  Its compaction scratch is a fixed
  *     288 KiB device array inside the library, resident on every GPU that loads the library until exit.
  *   - Limit: w*h <= MVS_STATIC_CLOUD_MAX_PIXELS (4096 x 2304); larger images return MVS_ERR_UNSUPPORTED and
  *     mvs_last_error says so -- use mvs_point_cloud for those.
- *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that
- *     first call before starting any stream capture on that device.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress) and, with CUDA's
+ *     default lazy module loading, is also the call that loads the four point-cloud kernels onto the device (a
+ *     driver-side allocation outside this library's control); make that first call before starting any stream
+ *     capture on that device, and before the phase in which nothing may allocate.
  *   - All calls on a device share the one array.  Its contents are whatever the previous call left; a call
  *     overwrites every entry before reading it, so nothing needs clearing, but two calls whose kernels overlap
  *     on the GPU (two contexts / streams on the same device) race on it: serialise them. */
@@ -179,7 +184,9 @@ int mvs_hist_sum(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int h
  * cv::GaussianBlur(CV_32F, ksize = ceil(sigma)*4 | 1, sigma, BORDER_DEFAULT) when gaussian_sigma is finite and > 0,
  * then clip (values < min_hist_count -> 0, values > max_hist_count -> max_hist_count).  Applied to the summed
  * histogram (after the cross-GPU sum).  Float arithmetic: within 1e-6 relative of OpenCV (whose own result varies by
- * an ulp with its SIMD dispatch).  mvs_hist_post takes a host image, mvs_hist_post_dev a device image (asynchronous). */
+ * an ulp with its SIMD dispatch).  mvs_hist_post takes a host image, mvs_hist_post_dev a device image (asynchronous, on
+ * mvs_tail_stream()).  Limit: gaussian_sigma <= 8 (a 33-tap kernel); larger values return MVS_ERR_UNSUPPORTED (the
+ * reference accepts any finite sigma; its default is 0.5). */
 int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float gaussian_sigma, float min_hist_count, float max_hist_count);
 int mvs_hist_post_dev(mvs_ctx* ctx, float* hist_dev, int hw, int hh, float gaussian_sigma, float min_hist_count,
                       float max_hist_count);
@@ -235,6 +242,19 @@ typedef struct {
     double et[8];
     double aabb[4];
     double cam_center[3];
+    /* Per-call knobs of the nodes (set them: a zeroed struct means NEAREST / right-is-reference):
+     * interp = calc_rectified::Params::interpolation_method (calc_rectified.hpp:17-22,34; the default is MVS_INTER_CUBIC),
+     * left_is_ref = the argument of PointCloud::init (geometry/point-cloud.cpp:48-58; the pipeline passes true). */
+    int interp;
+    int left_is_ref;
+    /* Inputs of the reference's DEFAULT histogram weighting (apply_slic_still_weights, floor-histogram.hpp:34-35,
+     * floor-histogram.cpp:239-251): the camera's SLIC label image (int32 w x h, byte step lstep; create_slic_lookup's result)
+     * and ImageFeatures2d::slic_info[].still_score (n_labels doubles).  NULL / 0 when hist.use_still is 0. */
+    const int32_t* labels;
+    size_t lstep;
+    const double* still_score;
+    int n_labels;
+    int labels_on_device; /* labels and still_score: 0 = host pointers (copied in), 1 = device pointers */
 } mvs_frame_desc;
 
 /* Device-side results of the last mvs_frame_run on this context slot (valid until the next run on it). */
@@ -269,6 +289,22 @@ int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame_desc* desc
 int mvs_frame_fetch(mvs_ctx* ctx, int slot, float* disp, size_t dstep, double* Xs, int32_t* xy, int32_t* lookup,
                     int32_t* n_out, double centroid[3], float* cam_hist);
 
+/* The same for n slots at once (first_slot .. first_slot + n - 1) with ONE blocking point per batch instead of two per
+ * frame: all copies are enqueued on the copy stream, the host waits once, and only when a point cloud is requested does it
+ * wait a second time (the clouds' sizes N are known after the first wait).  d[i] holds the destination pointers of slot
+ * first_slot + i (any may be NULL). */
+typedef struct {
+    float* disp;
+    size_t dstep;
+    double* Xs;
+    int32_t* xy;
+    int32_t* lookup;
+    int32_t* n_out;
+    double* centroid; /* 3 doubles */
+    float* cam_hist;
+} mvs_fetch_desc;
+int mvs_frame_fetch_batch(mvs_ctx* ctx, int first_slot, int n, const mvs_fetch_desc* d);
+
 /* Sum the per-camera histograms of slots [first_slot, first_slot + n_slots) in slot order into a device buffer owned by the
  * context (floor-histogram.cpp:296-300); returns its device address (hw*hh floats).  This buffer is what
  * a multi-GPU caller hands to ncclAllReduce / ncclAllGather. */
@@ -279,6 +315,11 @@ int mvs_frame_hist_sum(mvs_ctx* ctx, int first_slot, int n_slots, float** hist_d
  * Either output may be NULL. */
 int mvs_sgbm_volumes(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,
                      size_t step, int16_t* C, int16_t* S, int16_t* raw_disp16);
+
+/* Raise the error flag that an expired wait of the aggregation sweeps raises (the sweeps' waits are bounded: two
+ * seconds).  The next mvs_sync / mvs_frame_fetch(_batch) / host-buffer SGBM call then fails with MVS_ERR_CUDA and clears
+ * the flag.  Device-only callers (mvs_frame_run_batch + NCCL on mvs_tail_stream) learn of a failed sweep from mvs_sync. */
+int mvs_test_raise_wave_error(mvs_ctx* ctx, int code);
 
 /* Time (ms, CUDA events on the context stream) spent in the named stage during the last sgbm call:
  * "cost", "aggregate", "wta", "post".  Returns < 0 when unknown. */

@@ -38,7 +38,14 @@ class FrameDesc(C.Structure):
                 ("sw", c_int), ("sh", c_int), ("w", c_int), ("h", c_int),
                 ("sstep", c_size_t), ("mstep", c_size_t), ("inputs_on_device", c_int), ("maps_on_device", c_int),
                 ("sgbm", SgbmParams), ("presmooth_sigma", c_double), ("bcam", Bcam), ("hist", HistParams),
-                ("et", c_double * 8), ("aabb", c_double * 4), ("cam_center", c_double * 3)]
+                ("et", c_double * 8), ("aabb", c_double * 4), ("cam_center", c_double * 3),
+                ("interp", c_int), ("left_is_ref", c_int), ("labels", c_void_p), ("lstep", c_size_t), ("still_score", c_void_p),
+                ("n_labels", c_int), ("labels_on_device", c_int)]
+
+
+class FetchDesc(C.Structure):
+    _fields_ = [("disp", c_void_p), ("dstep", c_size_t), ("Xs", c_void_p), ("xy", c_void_p), ("lookup", c_void_p),
+                ("n_out", C.POINTER(C.c_int32)), ("centroid", c_void_p), ("cam_hist", c_void_p)]
 
 
 class FrameResult(C.Structure):
@@ -84,9 +91,11 @@ SIGNATURES = {
     "mvs_frame_run_batch": (c_int, [c_void_p, c_int, C.POINTER(FrameDesc), c_int, C.POINTER(FrameResult)]),
     "mvs_frame_fetch": (c_int, [c_void_p, c_int, c_void_p, c_size_t, c_void_p, c_void_p, c_void_p, C.POINTER(C.c_int32),
                                 c_void_p, c_void_p]),
+    "mvs_frame_fetch_batch": (c_int, [c_void_p, c_int, c_int, C.POINTER(FetchDesc)]),
     "mvs_frame_hist_sum": (c_int, [c_void_p, c_int, c_int, C.POINTER(c_void_p), C.POINTER(c_int), C.POINTER(c_int)]),
     "mvs_sgbm_volumes": (c_int, [c_void_p, C.POINTER(SgbmParams), c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p,
                                  c_void_p, c_void_p]),
+    "mvs_test_raise_wave_error": (c_int, [c_void_p, c_int]),
     "mvs_stage_ms": (c_float, [c_void_p, C.c_char_p]),
 }
 

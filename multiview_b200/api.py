@@ -399,9 +399,17 @@ class FloorHistogram:
 
 # ---------------------------------------------------------------------------------------------- frame path
 def make_frame_desc(cam: dict, sgbm: StereoSGBMParams, hist: FloorHistogramParams, aabb, sigma=2.15, on_device=False,
-                    dev_ptrs=None) -> FrameDesc:
-    """Build a mvs_frame_desc from a synth.make_camera() dict (host pointers) or device pointers."""
+                    dev_ptrs=None, interpolation_method=INTER_CUBIC, left_is_reference=True, slic_lookup=None,
+                    still_score=None) -> FrameDesc:
+    """Build a mvs_frame_desc from a synth.make_camera() dict (host pointers) or device pointers.  slic_lookup (int32 h x w)
+    and still_score (float64 per label) are the inputs of the reference's default histogram weighting; the caller keeps
+    them (and the camera's arrays) alive while the descriptor is in use."""
     d = FrameDesc()
+    d.interp, d.left_is_ref = int(interpolation_method), int(bool(left_is_reference))
+    if slic_lookup is not None and still_score is not None:
+        assert slic_lookup.dtype == np.int32 and slic_lookup.flags.c_contiguous and still_score.dtype == np.float64
+        d.labels, d.lstep = slic_lookup.ctypes.data, slic_lookup.strides[0]
+        d.still_score, d.n_labels, d.labels_on_device = still_score.ctypes.data, int(still_score.size), 0
     w, h = cam["W"], cam["H"]
     if on_device:
         for i in range(2):
@@ -457,6 +465,31 @@ def frame_fetch(ctx: Context, slot: int, w: int, h: int, hw: int, hh: int, want_
     if want_cloud:
         out["Xs"], out["xy"] = Xs[:n.value], xy[:n.value]
     return out
+
+
+def frame_fetch_batch(ctx: Context, first_slot: int, n: int, w: int, h: int, hw: int, hh: int, want_cloud=True):
+    """mvs_frame_fetch_batch into fresh numpy arrays: one blocking point per batch (two with clouds)."""
+    from ._lib import FetchDesc
+
+    outs, descs, ns = [], (FetchDesc * n)(), [C.c_int32(0) for _ in range(n)]
+    for i in range(n):
+        o = {"disp": np.empty((h, w), np.float32), "lookup": np.empty((h, w), np.int32), "C": np.empty(3, np.float64),
+             "cam_hist": np.empty((hh, hw), np.float32)}
+        if want_cloud:
+            o["Xs"], o["xy"] = np.empty((h * w, 3), np.float64), np.empty((h * w, 2), np.int32)
+        descs[i].disp, descs[i].dstep, descs[i].lookup = o["disp"].ctypes.data, w * 4, o["lookup"].ctypes.data
+        descs[i].centroid, descs[i].cam_hist = o["C"].ctypes.data, o["cam_hist"].ctypes.data
+        descs[i].n_out = C.pointer(ns[i])
+        if want_cloud:
+            descs[i].Xs, descs[i].xy = o["Xs"].ctypes.data, o["xy"].ctypes.data
+        outs.append(o)
+    ctx.check(ctx.lib.mvs_frame_fetch_batch(ctx.h, first_slot, n, descs), "mvs_frame_fetch_batch")
+    ctx.sync()
+    for i, o in enumerate(outs):
+        o["N"] = ns[i].value
+        if want_cloud:
+            o["Xs"], o["xy"] = o["Xs"][:o["N"]], o["xy"][:o["N"]]
+    return outs
 
 
 # ---------------------------------------------------------------------------------------- localization (front half)

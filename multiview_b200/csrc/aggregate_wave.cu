@@ -724,3 +724,16 @@ int sgbm_aggregate_wave_status(mvs_ctx* ctx, cudaStream_t stream)
     }
     return MVS_OK;
 }
+
+// Test tap: raise the flag a bounded wait would raise, so that the host-side reporting path (mvs_sync, the fetch entry
+// points) can be checked without provoking a real timeout.
+extern "C" int mvs_test_raise_wave_error(mvs_ctx* ctx, int code)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    MVS_ARENA(ctx, int, err, "sgbm.wave.err", 1);
+    ctx->wave_err_cleared = true;
+    MVS_CUDA(ctx, cudaMemcpyAsync(err, &code, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MVS_OK;
+}

@@ -151,7 +151,7 @@ int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double e
                           const double* still, int n_labels, float* cam_hist, int hw, int hh);
 int disp_merge_ref_dev(mvs_ctx* ctx, float* disp, const float* ref, const int32_t* labels, const uint8_t* still_cutoff,
                        int n_labels, int w, int h);
-int hist_post_dev(mvs_ctx* ctx, float* hist, int hw, int hh, float sigma, float minc, float maxc);
+int hist_post_dev(mvs_ctx* ctx, float* hist, int hw, int hh, float sigma, float minc, float maxc, const char* scratch);
 int hist_sum_dev(mvs_ctx* ctx, const float* cam_hists, int n_cams, int hw, int hh, float* hist);
 
 // stage kernels of the SGBM chain (cost.cu, aggregate.cu, wta_post.cu)

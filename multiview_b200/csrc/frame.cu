@@ -22,6 +22,8 @@ struct SlotBufs {
     int32_t *xy, *lookup, *nd;
     double* cen;
     float* cam_hist;
+    const int32_t* labels;   // device, packed w x h (nullptr: no still weights)
+    const double* still;
 };
 
 extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame_desc* descs, int n_frames,
@@ -50,6 +52,9 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     int rc = sgbm_geom(ctx, &d0.sgbm, w, h, &g);
     if (rc) return rc;
     // per-camera histograms of all slots live in one array so that the camera sum is one kernel
+    // (slots filled with another histogram size index this array differently: they are no longer fetchable)
+    for (int i = 0; i < MVS_MAX_SLOTS; ++i)
+        if (ctx->slots[i].valid && (ctx->slots[i].hw != hw || ctx->slots[i].hh != hh)) ctx->slots[i].valid = false;
     float* hists = (float*)arena_get(ctx, "slots.cam_hists", sizeof(float) * (size_t)hw * hh * MVS_MAX_SLOTS);
     if (!hists) return MVS_ERR_NOMEM;
 
@@ -61,7 +66,9 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     for (int f = 0; f < n_frames; ++f) {
         const mvs_frame_desc* d = descs + f;
         const int slot = first_slot + f;
-        if ((!d->inputs_on_device || !d->maps_on_device)) {
+        const bool use_labels = d->hist.use_still && d->labels && d->still_score && d->n_labels > 0;
+        if (use_labels && d->lstep < (size_t)d->w * 4) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d: lstep too small", f);
+        if ((!d->inputs_on_device || !d->maps_on_device || (use_labels && !d->labels_on_device))) {
             any_upload = true;
             // the slot's input buffers may still be read by the kernels of the previous frame that used this slot
             if (ctx->slot_done_recorded[slot]) MVS_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_slot_done[slot], 0));
@@ -98,6 +105,21 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         sb[f].cen = (double*)arena_get(ctx, slot_name(slot, "centroid").c_str(), 24);
         if (!sb[f].disp16 || !sb[f].dispf || !sb[f].Xs || !sb[f].xy || !sb[f].lookup || !sb[f].nd || !sb[f].cen) return MVS_ERR_NOMEM;
         sb[f].cam_hist = hists + (size_t)slot * hw * hh;
+        sb[f].labels = nullptr; sb[f].still = nullptr;
+        if (use_labels) {
+            if (d->labels_on_device && d->lstep == (size_t)w * 4) {
+                sb[f].labels = d->labels; sb[f].still = d->still_score;
+            } else {
+                int32_t* dl = (int32_t*)arena_get(ctx, slot_name(slot, "labels").c_str(), n * 4);
+                double* dsc = (double*)arena_get(ctx, slot_name(slot, "still").c_str(), (size_t)d->n_labels * 8);
+                if (!dl || !dsc) return MVS_ERR_NOMEM;
+                const cudaMemcpyKind kind = d->labels_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+                MVS_CUDA(ctx, cudaMemcpy2DAsync(dl, (size_t)w * 4, d->labels, d->lstep, (size_t)w * 4, h, kind, cs));
+                MVS_CUDA(ctx, cudaMemcpyAsync(dsc, d->still_score, (size_t)d->n_labels * 8, kind, cs));
+                sb[f].labels = dl; sb[f].still = dsc;
+                any_upload = true;
+            }
+        }
     }
 
     if (any_upload) {
@@ -112,8 +134,8 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         bool same_geometry = true;  // then all sensors of the batch go through one launch
         for (int f = 1; f < n_frames; ++f)
             same_geometry = same_geometry && descs[f].sw == d0.sw && descs[f].sh == d0.sh && sstep_of(descs + f) == sstep_of(&d0) &&
-                            mstep_of(descs + f) == mstep_of(&d0);
-        if (same_geometry) {
+                            mstep_of(descs + f) == mstep_of(&d0) && descs[f].interp == d0.interp;
+        if (same_geometry && d0.interp == MVS_INTER_CUBIC) {
             const uint8_t* ps[2 * MVS_MAX_BATCH];
             const float *px[2 * MVS_MAX_BATCH], *py[2 * MVS_MAX_BATCH];
             uint8_t* pd[2 * MVS_MAX_BATCH];
@@ -127,7 +149,7 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
             for (int f = 0; f < n_frames && !rc; ++f) {
                 const mvs_frame_desc* d = descs + f;
                 for (int i = 0; i < 2 && !rc; ++i)
-                    rc = remap_bgr8_dev(ctx, sensor[f][i], d->sw, d->sh, sstep_of(d), mapx[f][i], mapy[f][i], mstep_of(d), w, h, MVS_INTER_CUBIC,
+                    rc = remap_bgr8_dev(ctx, sensor[f][i], d->sw, d->sh, sstep_of(d), mapx[f][i], mapy[f][i], mstep_of(d), w, h, d->interp,
                                         white, sb[f].rect[i], (size_t)w * 3);
             }
         }
@@ -191,13 +213,19 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
             pb[f] = &descs[f].bcam; pdisp[f] = sb[f].dispf; pX[f] = sb[f].Xs; pxy[f] = sb[f].xy; plk[f] = sb[f].lookup;
             pn[f] = sb[f].nd; pc[f] = sb[f].cen;
         }
-        rc = point_cloud_batch_dev(ctx, n_frames, pb, pdisp, w, h, 1, pX, pxy, plk, pn, pc);
+        bool same_ref = true;
+        for (int f = 1; f < n_frames; ++f) same_ref = same_ref && (descs[f].left_is_ref != 0) == (d0.left_is_ref != 0);
+        if (same_ref)
+            rc = point_cloud_batch_dev(ctx, n_frames, pb, pdisp, w, h, d0.left_is_ref != 0, pX, pxy, plk, pn, pc);
+        else
+            for (int f = 0; f < n_frames && !rc; ++f)
+                rc = point_cloud_batch_dev(ctx, 1, pb + f, pdisp + f, w, h, descs[f].left_is_ref != 0, pX + f, pxy + f, plk + f, pn + f, pc + f);
     }
     stage_end(ctx, "cloud");
     stage_begin(ctx, "hist");
     for (int f = 0; f < n_frames && !rc; ++f)
         rc = floor_hist_camera_dev(ctx, &descs[f].hist, descs[f].et, descs[f].aabb, descs[f].cam_center, sb[f].Xs, sb[f].xy, sb[f].nd, (int)n /* capacity */,
-                                   nullptr, 0, 0, nullptr, 0, sb[f].cam_hist, hw, hh);
+                                   sb[f].labels, w, h, sb[f].still, descs[f].n_labels, sb[f].cam_hist, hw, hh);
     stage_end(ctx, "hist");
     if (rc) return rc;
 
@@ -255,6 +283,52 @@ extern "C" int mvs_frame_fetch(mvs_ctx* ctx, int slot, float* disp, size_t dstep
     MVS_CUDA(ctx, cudaStreamSynchronize(s));
     if (n_out) *n_out = nh;
     return sgbm_aggregate_wave_status(ctx, s);  // read behind the slot's kernels, without waiting for later batches
+}
+
+extern "C" int mvs_frame_fetch_batch(mvs_ctx* ctx, int first_slot, int n, const mvs_fetch_desc* d)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!d || n < 1 || first_slot < 0 || first_slot + n > MVS_MAX_SLOTS) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_fetch_batch: bad argument");
+    for (int i = 0; i < n; ++i) {
+        const FrameSlot& fs = ctx->slots[first_slot + i];
+        if (!fs.valid) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_fetch_batch: slot %d is empty", first_slot + i);
+        if (d[i].disp && d[i].dstep < (size_t)fs.w * 4) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_fetch_batch: dstep too small");
+    }
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->copy_stream;
+    std::vector<int32_t> nh((size_t)n, 0);
+    float* hists = (float*)arena_get(ctx, "slots.cam_hists", 0);
+    bool want_cloud = false;
+    for (int i = 0; i < n; ++i) {
+        const int slot = first_slot + i;
+        const FrameSlot& fs = ctx->slots[slot];
+        const size_t px = (size_t)fs.w * fs.h;
+        if (ctx->slot_done_recorded[slot]) MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_slot_done[slot], 0));
+        MVS_CUDA(ctx, cudaMemcpyAsync(&nh[i], arena_get(ctx, slot_name(slot, "n").c_str(), 4), 4, cudaMemcpyDeviceToHost, s));
+        if (d[i].disp)
+            MVS_CUDA(ctx, cudaMemcpy2DAsync(d[i].disp, d[i].dstep, arena_get(ctx, slot_name(slot, "disp").c_str(), px * 4), (size_t)fs.w * 4,
+                                            (size_t)fs.w * 4, fs.h, cudaMemcpyDeviceToHost, s));
+        if (d[i].lookup) MVS_CUDA(ctx, cudaMemcpyAsync(d[i].lookup, arena_get(ctx, slot_name(slot, "lookup").c_str(), px * 4), px * 4, cudaMemcpyDeviceToHost, s));
+        if (d[i].centroid) MVS_CUDA(ctx, cudaMemcpyAsync(d[i].centroid, arena_get(ctx, slot_name(slot, "centroid").c_str(), 24), 24, cudaMemcpyDeviceToHost, s));
+        if (d[i].cam_hist)
+            MVS_CUDA(ctx, cudaMemcpyAsync(d[i].cam_hist, hists + (size_t)slot * fs.hw * fs.hh, sizeof(float) * (size_t)fs.hw * fs.hh, cudaMemcpyDeviceToHost, s));
+        want_cloud = want_cloud || d[i].Xs || d[i].xy;
+    }
+    MVS_CUDA(ctx, cudaStreamSynchronize(s));   // the one blocking point of a batch without clouds
+    if (want_cloud) {
+        for (int i = 0; i < n; ++i) {
+            const int slot = first_slot + i;
+            const size_t px = (size_t)ctx->slots[slot].w * ctx->slots[slot].h;
+            if (nh[i] > 0 && d[i].Xs) MVS_CUDA(ctx, cudaMemcpyAsync(d[i].Xs, arena_get(ctx, slot_name(slot, "Xs").c_str(), px * 24), (size_t)nh[i] * 24, cudaMemcpyDeviceToHost, s));
+            if (nh[i] > 0 && d[i].xy) MVS_CUDA(ctx, cudaMemcpyAsync(d[i].xy, arena_get(ctx, slot_name(slot, "xy").c_str(), px * 8), (size_t)nh[i] * 8, cudaMemcpyDeviceToHost, s));
+        }
+    }
+    for (int i = 0; i < n; ++i) {
+        MVS_CUDA(ctx, cudaEventRecord(ctx->ev_slot_fetched[first_slot + i], s));
+        ctx->slot_fetch_recorded[first_slot + i] = true;
+        if (d[i].n_out) *d[i].n_out = nh[i];
+    }
+    return sgbm_aggregate_wave_status(ctx, s);  // (synchronises the copy stream: the second blocking point when clouds were asked for)
 }
 
 extern "C" int mvs_frame_hist_sum(mvs_ctx* ctx, int first_slot, int n_slots, float** hist_dev, int* hw, int* hh)

@@ -313,7 +313,7 @@ __global__ void hist_blur_v_clip_kernel(const float* __restrict__ src, int w, in
     dst[(size_t)y * w + x] = s;
 }
 
-int hist_post_dev(mvs_ctx* ctx, float* hist, int hw, int hh, float sigma, float minc, float maxc)
+int hist_post_dev(mvs_ctx* ctx, float* hist, int hw, int hh, float sigma, float minc, float maxc, const char* scratch)
 {
     HistBlurTaps t;
     memset(&t, 0, sizeof(t));
@@ -328,7 +328,7 @@ int hist_post_dev(mvs_ctx* ctx, float* hist, int hw, int hh, float sigma, float 
         for (int i = 0; i < n; ++i) { double x = i - (n - 1) * 0.5; kd[i] = exp(s2 * x * x); sum += kd[i]; }
         for (int i = 0; i <= t.r; ++i) t.k[i] = (float)(kd[t.r + i] / sum);
     }
-    MVS_ARENA(ctx, float, tmp, "hist.post.tmp", (size_t)hw * hh);
+    MVS_ARENA(ctx, float, tmp, scratch, (size_t)hw * hh);   // one scratch image per calling stream (main / tail)
     dim3 grid(cdiv(hw, 128), hh);
     const float* src = hist;
     if (blur) {
@@ -350,7 +350,7 @@ extern "C" int mvs_hist_post_dev(mvs_ctx* ctx, float* hist_dev, int hw, int hh, 
     if (!hist_dev || hw <= 0 || hh <= 0) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_hist_post_dev: bad argument");
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
     StreamSwap on_tail(ctx, ctx->tail_stream);   // consumes frame results: enqueued behind them
-    return hist_post_dev(ctx, hist_dev, hw, hh, gaussian_sigma, min_hist_count, max_hist_count);
+    return hist_post_dev(ctx, hist_dev, hw, hh, gaussian_sigma, min_hist_count, max_hist_count, "hist.post.tmp.tail");
 }
 
 extern "C" int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float gaussian_sigma, float min_hist_count,
@@ -359,11 +359,10 @@ extern "C" int mvs_hist_post(mvs_ctx* ctx, float* hist, int hw, int hh, float ga
     if (!ctx) return MVS_ERR_ARG;
     if (!hist || hw <= 0 || hh <= 0) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_hist_post: bad argument");
     MVS_CUDA(ctx, cudaSetDevice(ctx->device));
-    if (int wrc = main_stream_waits_for_tail(ctx)) return wrc;   // shares its scratch image with mvs_hist_post_dev
     size_t n = (size_t)hw * hh;
     MVS_ARENA(ctx, float, d, "hist.post.api", n);
     MVS_CUDA(ctx, cudaMemcpyAsync(d, hist, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-    int rc = hist_post_dev(ctx, d, hw, hh, gaussian_sigma, min_hist_count, max_hist_count);
+    int rc = hist_post_dev(ctx, d, hw, hh, gaussian_sigma, min_hist_count, max_hist_count, "hist.post.tmp.main");
     if (rc) return rc;
     MVS_CUDA(ctx, cudaMemcpyAsync(hist, d, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

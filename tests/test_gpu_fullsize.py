@@ -15,8 +15,11 @@ def _rect_pair(W, H, D, seed):
     return l, r
 
 
+# BASELINE.json configs c1 / c2 and the largest shapes of the c5 sweep (at 3840x2160x256 a cost volume is 3.96 GB,
+# the sweep has 144 bands per frame and the volumes' word offsets pass 2^30)
 @pytest.mark.parametrize("W,H,D,mode", [(1920, 1080, 256, 1), (896, 672, 128, 1), (896, 672, 128, 3), (896, 672, 128, 0),
-                                        (1280, 720, 96, 1)])
+                                        (1280, 720, 96, 1), (2560, 1440, 256, 1), (3840, 2160, 256, 1), (3840, 2160, 256, 3),
+                                        (640, 480, 64, 1)])
 def test_disparity_matches_cv2_at_full_size(ctx, W, H, D, mode):
     cv2 = pytest.importorskip("cv2")
     from oracle import SgbmParams, cv2ref
@@ -50,3 +53,100 @@ def test_batch_is_deterministic_and_order_independent_at_c2(ctx):
         valid = a[i]["disp"] > 0
         assert a[i]["N"] == int(valid.sum()) and np.array_equal(a[i]["lookup"] >= 0, valid)
         assert (a[i]["disp"][valid] >= 1.0).all() and (a[i]["disp"] <= 150.0).all()  # minDisparity .. max_disparity clamp
+
+
+def _labels_and_still(W, H, seed):
+    """A synthetic SLIC lookup (32 x 32 pixel cells, a few unlabelled pixels) and still scores."""
+    rng = np.random.default_rng(seed)
+    gx, gy = (W + 31) // 32, (H + 31) // 32
+    lab = (np.arange(H)[:, None] // 32) * gx + (np.arange(W)[None, :] // 32)
+    lab = lab.astype(np.int32)
+    lab[rng.random((H, W)) < 0.01] = -1
+    return np.ascontiguousarray(lab), rng.uniform(0.0, 1.0, gx * gy)
+
+
+@pytest.mark.parametrize("W,H,D", [(896, 672, 128), (1920, 1080, 256)])
+def test_frame_path_matches_cv2_and_oracle_at_baseline_sizes(ctx, W, H, D):
+    """c1 / c2: the frame path's disparity against cv2, then xy / lookup / N / Xs / cam_hist against the C oracle fed with
+    that disparity: once in count mode and once with the reference's default weighting (WGT_NORM, SLIC still weights),
+    summed in point order."""
+    pytest.importorskip("cv2")
+    import oracle
+    from oracle import cv2ref
+
+    cv2ref.set_threads(8)
+    cam = synth.make_camera(W, H, D, config=2, cam=1, n_cams=4)
+    sp = api.StereoSGBMParams(sg_num_disparities=D, sg_mode=1)
+    lab, still = _labels_and_still(W, H, 7)
+    hp0 = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
+    hp1 = api.FloorHistogramParams(weighting=api.WGT_NORM, apply_slic_still_weights=True, ordered=True)
+    descs = [api.make_frame_desc(cam, sp, hp0, synth.HIST_AABB),
+             api.make_frame_desc(cam, sp, hp1, synth.HIST_AABB, slic_lookup=lab, still_score=still)]
+    res = api.frame_run_batch(ctx, 0, descs)
+    outs = api.frame_fetch_batch(ctx, 0, 2, W, H, res[0].hw, res[0].hh)
+    rect = [cv2ref.remap_cubic_bgr8(cam["sensor"][i], cam["mapx"][i], cam["mapy"][i]) for i in range(2)]
+    want_d = cv2ref.disparity_calculate(oracle.SgbmParams.reference_defaults(D, 1), rect[0], rect[1], 2.15)
+    ob = oracle.Bcam()
+    for i in range(2):
+        for k in range(9):
+            ob.krr_inv[i][k] = descs[0].bcam.krr_inv[i][k]
+        for k in range(3):
+            ob.c[i][k] = descs[0].bcam.c[i][k]
+    wpc = oracle.point_cloud(ob, want_d)
+    for out in outs:
+        assert np.array_equal(out["disp"], want_d)
+        assert out["N"] == wpc["N"] and np.array_equal(out["xy"], wpc["xy"]) and np.array_equal(out["lookup"], wpc["lookup"])
+        assert np.abs(out["Xs"] - wpc["Xs"]).max() <= 1e-4 * np.abs(wpc["Xs"]).max()
+        assert np.allclose(out["C"], wpc["C"], rtol=1e-4, atol=0)
+    wh0 = oracle.floor_hist_camera(oracle.HistParams(hp0.hist_sz, hp0.hist_min_z, hp0.hist_max_z, 0, 0), cam["et"], synth.HIST_AABB,
+                                   cam["et"][:3], wpc["Xs"], wpc["xy"])
+    assert np.array_equal(outs[0]["cam_hist"], wh0) and wh0.sum() > 1000
+    # weighted: bit-exact against the oracle's sequential loop over the SAME points (the GPU's Xs equal the oracle's to 1e-4;
+    # weights depend on them, so the oracle is fed the GPU's cloud here and the cloud itself is checked above)
+    wh1 = oracle.floor_hist_camera(oracle.HistParams(hp1.hist_sz, hp1.hist_min_z, hp1.hist_max_z, api.WGT_NORM, 1), cam["et"],
+                                   synth.HIST_AABB, cam["et"][:3], outs[1]["Xs"], outs[1]["xy"], lab, still)
+    assert np.array_equal(outs[1]["cam_hist"], wh1) and wh1.sum() > wh0.sum()
+
+
+def test_frame_path_interpolation_and_reference_side(ctx):
+    """calc_rectified's interpolation_method and PointCloud::init's left_is_reference reach the frame path."""
+    import oracle
+
+    W, H, D = 384, 240, 64
+    cam = synth.make_camera(W, H, D, config=2, cam=0, n_cams=2)
+    sp = api.StereoSGBMParams(sg_num_disparities=D, sg_mode=1)
+    hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
+    for slot, (interp, lref) in enumerate([(api.INTER_LINEAR, True), (api.INTER_CUBIC, False), (api.INTER_NEAREST, True)]):
+        desc = api.make_frame_desc(cam, sp, hp, synth.HIST_AABB, interpolation_method=interp, left_is_reference=lref)
+        res = api.frame_run(ctx, slot, desc)
+        out = api.frame_fetch(ctx, slot, W, H, res.hw, res.hh)
+        rect = [oracle.remap_bgr8(cam["sensor"][i], cam["mapx"][i], cam["mapy"][i], interp) for i in range(2)]
+        want_d = oracle.disp_to_float(oracle.sgbm_compute(oracle.SgbmParams.reference_defaults(D, 1), oracle.presmooth(rect[0]),
+                                                          oracle.presmooth(rect[1])))
+        assert np.array_equal(out["disp"], want_d)
+        ob = oracle.Bcam()
+        for i in range(2):
+            for k in range(9):
+                ob.krr_inv[i][k] = desc.bcam.krr_inv[i][k]
+            for k in range(3):
+                ob.c[i][k] = desc.bcam.c[i][k]
+        wpc = oracle.point_cloud(ob, want_d, left_is_ref=lref)
+        assert out["N"] == wpc["N"] and np.array_equal(out["xy"], wpc["xy"])
+        assert np.abs(out["Xs"] - wpc["Xs"]).max() <= 1e-4 * np.abs(wpc["Xs"]).max()
+
+
+def test_expired_sweep_wait_is_reported_by_sync(ctx):
+    """The device-resident path copies nothing back: mvs_sync is where it learns that an aggregation wait expired."""
+    W, H, D = 352, 150, 64
+    cam = synth.make_camera(W, H, D, config=2, cam=0, n_cams=2)
+    desc = api.make_frame_desc(cam, api.StereoSGBMParams(sg_num_disparities=D, sg_mode=1),
+                               api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False), synth.HIST_AABB)
+    api.frame_run(ctx, 0, desc)
+    ctx.sync()
+    assert ctx.lib.mvs_test_raise_wave_error(ctx.h, (1 << 28) | (3 << 23) | (5 << 16) | 77) == 0
+    rc = ctx.lib.mvs_sync(ctx.h)
+    assert rc == -2 and b"bounded wait expired" in ctx.lib.mvs_last_error(ctx.h)
+    assert b"ring row 3, band 5, pixel 77" in ctx.lib.mvs_last_error(ctx.h)
+    assert ctx.lib.mvs_sync(ctx.h) == 0   # reported once, then cleared
+    res = api.frame_run(ctx, 0, desc)     # and the context keeps working
+    assert api.frame_fetch(ctx, 0, W, H, res.hw, res.hh)["N"] > 100

@@ -25,15 +25,44 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WORKLOADS = {  # name -> (W, H, D)
+WORKLOADS = {  # name -> (W, H, D); c1..c4 are BASELINE.json configs[0..3], the rest the corners of the configs[4] sweep
     "c1": (896, 672, 128),
     "c2": (1920, 1080, 256),
+    "c3": (1920, 1080, 256),    # 8-camera scene, ONE camera per GPU; a step is --batch consecutive frames of that camera
+    "c4": (896, 672, 128),      # 16 cameras x 300 frames, FIXED total work sharded by camera/frame (strong scaling)
     "vga64": (640, 480, 64),
     "720p128": (1280, 720, 128),
     "1440p256": (2560, 1440, 256),
     "4k256": (3840, 2160, 256),
 }
+C4_CAMS, C4_FRAMES, C4_FRAMES_PER_STEP = 16, 300, 2   # a c4 step = 2 frame times of all 16 cameras = 32 camera-frames, whatever N is
 METRIC = "stereo frames/s (rectify+SGM+cloud+floor_hist)"
+
+
+def config_dict(args, world):
+    """The `config` object of the JSON line: the same for both arms (the driver compares them)."""
+    W, H, D = WORKLOADS[args.workload]
+    mode_name = {1: "8-path MODE_HH", 3: "4-path MODE_HH4", 0: "5-path MODE_SGBM"}[args.mode]
+    cells = sgbm_cells(W, H, D)
+    if args.workload == "c4":
+        what = (f"{C4_CAMS} cameras x {C4_FRAMES} frames, a step = {C4_FRAMES_PER_STEP} frame times of all cameras = "
+                f"{C4_CAMS * C4_FRAMES_PER_STEP} camera-frames sharded camera-major over the GPUs (fixed total work)")
+    elif args.workload == "c3":
+        what = f"one camera per GPU, a step = {args.batch} consecutive frames of it"
+    else:
+        what = f"{args.batch} camera-frames per GPU per step"
+    return {"workload": f"{args.workload}: {W}x{H} stereo pair, {D} disparities, mode {args.mode} ({mode_name}), "
+                        f"full disp_map+cloud+floor_hist; {what}",
+            "mode": args.mode, "batch_per_gpu": units_per_rank(args, world),
+            "parallelism": f"camera/frame-sharded x{world}, NCCL all-reduce of floor histograms",
+            "l2": f"no flush: each cost volume is {cells * 2 / 1e6:.0f} MB > 126 MB L2",
+            "distinct_inputs_per_gpu": min(args.distinct, units_per_rank(args, world))}
+
+
+def units_per_rank(args, world):
+    if args.workload == "c4":
+        return max(1, C4_CAMS * C4_FRAMES_PER_STEP // world)
+    return args.batch
 
 
 def peaks():
@@ -128,7 +157,8 @@ def run_reference(args, rank, world):
     cores = os.cpu_count() or 1
     # cv2's MODE_HH / MODE_SGBM are single-threaded inside OpenCV, so the multi-core baseline is one
     # camera-frame per thread (cv2 releases the GIL), as the reference's thread pool runs cameras in parallel.
-    par = max(1, min(cores, args.ref_threads, int(psutil_avail_gb() // (6.0 * W * H * D / (1920 * 1080 * 256) + 0.5)) or 1))
+    want = args.ref_threads if args.ref_threads > 0 else cores   # default: every host core
+    par = max(1, min(cores, want, int(psutil_avail_gb() // (6.0 * W * H * D / (1920 * 1080 * 256) + 0.5)) or 1))
     cv2ref.set_threads(1 if par > 1 else cores)
     cams = [synth.make_camera(W, H, D, config=2, cam=i % 2, frame=0, n_cams=2) for i in range(min(par, 2))]
     rows = H
@@ -156,12 +186,12 @@ def run_reference(args, rank, world):
               f"rows/H), D={D}, mode={args.mode}; cv2 {cv2ref._cv2().__version__} remap+cvtColor+2xGaussianBlur+StereoSGBM "
               f"(the reference's OpenCV calls, IPP off) + C port of PointCloud::init / floor_hist")
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1000 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1000 * dt / args.steps, "higher_is_better": True,
+            "scaling": "strong" if args.workload == "c4" else "weak",
             "vs_baseline": None, "dtype": "u16", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {W}x{H} stereo pair, {D} disparities, mode {args.mode}, full disp_map+cloud+floor_hist",
-                       "batch_per_step": par},
+            "config": config_dict(args, args.gpus),
             "gpix_disp_per_s": val * W * H * D / 1e9,
-            "cpu_baseline": {"value": val, "unit": "frames/s", "cores": par, "kind": "reference", "sample": sample,
+            "cpu_baseline": {"value": val, "unit": "frames/s", "cores": par, "kind": "cv2+port", "sample": sample,
                              "host_cores": cores},
             "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
@@ -188,7 +218,16 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     W, H, D = WORKLOADS[args.workload]
-    B = args.batch
+    B = units_per_rank(args, world)
+    # keep the host threads of a rank on their own share of the cores (8 ranks share one host)
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = max(1, len(cores) // max(world, 1))
+        mine = cores[local_rank * per:(local_rank + 1) * per] if world > 1 else cores
+        if mine:
+            os.sched_setaffinity(0, mine)
+    except (AttributeError, OSError):
+        pass
     ctx = api.Context(local_rank)
     stream = torch.cuda.ExternalStream(ctx.lib.mvs_stream(ctx.h), device=dev)
     # the library finishes a batch (WTA .. histogram, histogram sums) on its tail stream, overlapped with the next batch's
@@ -196,9 +235,19 @@ def run_ours(args, rank, world, local_rank):
     tail = torch.cuda.ExternalStream(ctx.lib.mvs_tail_stream(ctx.h), device=dev)
     sp = api.StereoSGBMParams(sg_num_disparities=D, sg_mode=args.mode)
     hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
-    n_cams = world * B
-    my_cams = shard.cameras_for_rank(n_cams, world, rank)  # camera c lives on rank c % world
-    cams = [synth.make_camera(W, H, D, config=2, cam=c, frame=0, n_cams=n_cams) for c in my_cams[:min(B, args.distinct)]]
+    # the (camera, frame) units of one step that this rank owns (camera c lives on rank c % world)
+    if args.workload == "c4":
+        n_cams = C4_CAMS
+        units = shard.units_for_rank(C4_CAMS, C4_FRAMES_PER_STEP, world, rank)
+    elif args.workload == "c3":
+        n_cams = world
+        units = [(rank, f) for f in range(B)]
+    else:
+        n_cams = world * B
+        units = [(c, 0) for c in shard.cameras_for_rank(n_cams, world, rank)]
+    assert len(units) == B, (len(units), B)
+    cfg_id = {"c1": 1, "c2": 2, "c3": 3, "c4": 4}.get(args.workload, 5)
+    cams = [synth.make_camera(W, H, D, config=cfg_id, cam=c, frame=f, n_cams=n_cams) for (c, f) in units[:min(B, args.distinct)]]
 
     # pinned host copies (e2e) and device-resident copies (value)
     host, devt, descs_dev, descs_host = [], [], [], []
@@ -256,7 +305,7 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     ms = float(tmax.item())
-    frames = world * B * args.steps
+    frames = (C4_CAMS * C4_FRAMES_PER_STEP if args.workload == "c4" else world * B) * args.steps
     value = frames / (ms / 1000.0)
     hist_total = float(hist_t.sum().item())
 
@@ -272,14 +321,35 @@ def run_ours(args, rank, world, local_rank):
             acc[s_].append(ctx.stage_ms(s_))
     stage_ms = {s_: float(np.mean(v)) / B for s_, v in acc.items()}
     stage_ms["wta+post"] = stage_ms.pop("wta")
-    # (b) one camera-frame alone (latency mode)
+    # (b) one camera-frame alone (latency mode); the first two calls load the single-frame kernels and are not counted
     acc1 = {s_: [] for s_ in stages + ["post"]}
-    for _ in range(3):
+    for it in range(5):
         api.frame_run(ctx, 0, descs_dev[0])
         ctx.sync()
+        if it < 2:
+            continue
         for s_ in acc1:
             acc1[s_].append(ctx.stage_ms(s_))
     stage_ms_single = {s_: float(np.mean(v)) for s_, v in acc1.items()}
+    # (c) the histogram stage in the reference's DEFAULT mode (WGT_NORM, SLIC still weights, floor-histogram.hpp:34-35),
+    #     summed in point order (bit-exact): a stable sort by bin per camera-frame; synthetic 32x32-pixel label cells
+    gx, gy = (W + 31) // 32, (H + 31) // 32
+    lab = ((np.arange(H)[:, None] // 32) * gx + (np.arange(W)[None, :] // 32)).astype(np.int32)
+    still = np.random.default_rng(5).uniform(0.0, 1.0, gx * gy)
+    lab_t, still_t = torch.from_numpy(lab).to(dev), torch.from_numpy(still).to(dev)
+    hp_ref = api.FloorHistogramParams(weighting=api.WGT_NORM, apply_slic_still_weights=True, ordered=True)
+    batch_ref = (api.FrameDesc * B)(*[descs_dev[b % len(descs_dev)] for b in range(B)])
+    for b in range(B):
+        batch_ref[b].hist = hp_ref.to_c()
+        batch_ref[b].labels, batch_ref[b].lstep = lab_t.data_ptr(), W * 4
+        batch_ref[b].still_score, batch_ref[b].n_labels, batch_ref[b].labels_on_device = still_t.data_ptr(), int(still.size), 1
+    hacc = []
+    for it in range(4):
+        api.frame_run_batch(ctx, 0, batch_ref)
+        ctx.sync()
+        if it:
+            hacc.append(ctx.stage_ms("hist"))
+    stage_ms["hist_reference_default_ordered"] = float(np.mean(hacc)) / B
     cells = sgbm_cells(W, H, D)
     peak, peak_src = peaks()
     agg_bytes = 8.0 * cells  # read C + write S forward, read C + read S backward
@@ -293,12 +363,12 @@ def run_ours(args, rank, world, local_rank):
 
     # DRAM traffic of the same two launches from the committed ncu --set full capture (per camera-frame, like
     # algorithmic_bytes_per_frame); only quoted when the capture is of this workload
-    tpath = os.path.join(ROOT, "profiles", "r01_wave_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r02_wave_traffic.json")
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
         if tj.get("workload") == args.workload and args.mode == 1:
             roofline["traffic"] = tj["traffic_bytes_per_frame"]
-            roofline["traffic_source"] = "profiles/r01_wave_traffic.json (ncu dram__bytes_read+write, batch %d)" % tj["batch"]
+            roofline["traffic_source"] = "profiles/r02_wave_traffic.json (ncu dram__bytes_read+write, batch %d)" % tj["batch"]
 
     # ---- e2e: host buffers in, host results out, through the C ABI ----------------------------------------------
     descs_host = []
@@ -313,64 +383,88 @@ def run_ours(args, rank, world, local_rank):
             d.mapy[i] = devt[b]["mapy"][i].data_ptr()
     # two slot ranges alternate: while batch k's kernels run, batch k+1's sensor images upload and batch k-1's
     # results download on the library's copy stream
+    from multiview_b200._lib import FetchDesc
+
     out_disp = [[torch.empty((H, W), dtype=torch.float32).pin_memory() for _ in range(B)] for _ in range(2)]
     out_hist = [[torch.empty((hh, hw), dtype=torch.float32).pin_memory() for _ in range(B)] for _ in range(2)]
-    out_cen = np.empty(3)
-    nout = C.c_int32()
+    out_cen = [np.empty((B, 3)) for _ in range(2)]
+    nouts = [[C.c_int32() for _ in range(B)] for _ in range(2)]
     batch_host = (api.FrameDesc * B)(*[descs_host[b % len(descs_host)] for b in range(B)])
     for b in range(B):
         batch_host[b].inputs_on_device, batch_host[b].maps_on_device = 0, 1  # host (pinned) sensor images, resident maps
-    pending = []
 
-    def e2e_submit(k):
-        first = (k & 1) * B
-        api.frame_run_batch(ctx, first, batch_host)
-        hist_reduce(first)
-        pending.append(k)
+    def make_fetch(with_cloud):
+        # one descriptor table per slot range; with_cloud adds the host PointCloud (Xs, xy, lookup) a consumer of
+        # disp_map_update::Result receives (pipeline/nodes/disp_map_update.cpp:115-119)
+        tabs, keep = [], []
+        for half in range(2):
+            t = (FetchDesc * B)()
+            for b in range(B):
+                t[b].disp, t[b].dstep = out_disp[half][b].data_ptr(), W * 4
+                t[b].cam_hist = out_hist[half][b].data_ptr()
+                t[b].centroid = out_cen[half][b].ctypes.data
+                t[b].n_out = C.pointer(nouts[half][b])
+                if with_cloud:
+                    xs = torch.empty((H * W, 3), dtype=torch.float64).pin_memory()
+                    xy = torch.empty((H * W, 2), dtype=torch.int32).pin_memory()
+                    lk = torch.empty((H, W), dtype=torch.int32).pin_memory()
+                    keep.append((xs, xy, lk))
+                    t[b].Xs, t[b].xy, t[b].lookup = xs.data_ptr(), xy.data_ptr(), lk.data_ptr()
+            tabs.append(t)
+        return tabs, keep
 
-    def e2e_collect():
-        k = pending.pop(0)
-        first = (k & 1) * B
-        for b in range(B):
-            ctx.check(ctx.lib.mvs_frame_fetch(ctx.h, first + b, C.c_void_p(out_disp[k & 1][b].data_ptr()), W * 4, None, None, None,
-                                              C.byref(nout), C.c_void_p(out_cen.ctypes.data), C.c_void_p(out_hist[k & 1][b].data_ptr())),
-                      "mvs_frame_fetch")
-
-    def run_e2e(n):
+    def run_e2e(n, tabs):
+        # two slot ranges alternate: batch k+1 is enqueued (uploads on the copy stream) before batch k is fetched
+        pending = []
         for k in range(n):
-            e2e_submit(k)
+            first = (k & 1) * B
+            api.frame_run_batch(ctx, first, batch_host)
+            hist_reduce(first)
+            pending.append(k)
             if len(pending) > 1:
-                e2e_collect()
+                j = pending.pop(0)
+                ctx.check(ctx.lib.mvs_frame_fetch_batch(ctx.h, (j & 1) * B, B, tabs[j & 1]), "mvs_frame_fetch_batch")
         while pending:
-            e2e_collect()
+            j = pending.pop(0)
+            ctx.check(ctx.lib.mvs_frame_fetch_batch(ctx.h, (j & 1) * B, B, tabs[j & 1]), "mvs_frame_fetch_batch")
         torch.cuda.synchronize()
 
-    run_e2e(min(args.warmup, 3))
-    barrier()
-    t0 = time.perf_counter()
-    run_e2e(args.steps)
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    t2 = torch.tensor([e2e_s], device=dev)
-    if world > 1:
-        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-    e2e_val = frames / float(t2.item())
+    def time_e2e(tabs):
+        run_e2e(min(args.warmup, 3), tabs)
+        barrier()
+        t0 = time.perf_counter()
+        run_e2e(args.steps, tabs)
+        barrier()
+        t2 = torch.tensor([time.perf_counter() - t0], device=dev)
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        return frames / float(t2.item())
+
+    tabs, _ = make_fetch(False)
+    e2e_val = time_e2e(tabs)
     h2d = B * 2 * H * W * 3
     d2h = B * (H * W * 4 + hh * hw * 4 + 4 + 24)
+    e2e_cloud = None
+    if not args.no_cloud_e2e:
+        tabs_c, keep_c = make_fetch(True)
+        e2e_cloud_val = time_e2e(tabs_c)
+        n_pts = int(np.mean([v.value for v in nouts[0]]))
+        e2e_cloud = {"value": e2e_cloud_val, "unit": "frames/s", "d2h_bytes_per_step": d2h + B * (n_pts * 32 + H * W * 4),
+                     "note": "as e2e, plus the host PointCloud of every frame (Xs, xy, lookup), copied by exact size N"}
+        del keep_c
 
     line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16",
-            "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {W}x{H} stereo pair, {D} disparities, mode {args.mode} "
-                                   f"({'8-path MODE_HH' if args.mode == 1 else 'mode ' + str(args.mode)}), full disp_map+cloud+floor_hist",
-                       "batch_per_gpu": B, "parallelism": f"camera-sharded x{world}, NCCL all-reduce of floor histograms",
-                       "l2": f"no flush: each cost volume is {cells * 2 / 1e6:.0f} MB > 126 MB L2"},
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if args.workload == "c4" else "weak",
+            "vs_baseline": None, "dtype": "u16", "data": "synthetic",
+            "config": config_dict(args, world),
             "gpix_disp_per_s": value * W * H * D / 1e9,
             "roofline": roofline, "stage_ms": stage_ms, "stage_ms_single_frame": stage_ms_single, "gpu_launches": int(launches),
             "e2e": {"value": e2e_val, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "note": "sensor images H2D from pinned memory + float disparity, floor histogram, N, centroid D2H every frame; "
                             "the point cloud stays on the device (its consumer floor_hist runs there)"},
             "clocks": clk.summary(), "hist_mass_after_smoothing": hist_total}
+    if e2e_cloud:
+        line["e2e_with_cloud"] = e2e_cloud
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import cv2ref
@@ -382,7 +476,7 @@ def run_ours(args, rank, world, local_rank):
         t0 = time.perf_counter()
         cpu_frame(c, D, args.mode, synth.HIST_AABB)
         dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": (rows / H) / dt, "unit": "frames/s", "cores": cores, "kind": "reference",
+        line["cpu_baseline"] = {"value": (rows / H) / dt, "unit": "frames/s", "cores": cores, "kind": "cv2+port",
                                 "sample": f"one camera-frame, first {rows} of {H} rows ({W}x{rows}, D={D}, mode {args.mode}), scaled by rows/H; "
                                           f"cv2 {cv2ref._cv2().__version__} with setNumThreads({cores}) (StereoSGBM MODE_HH itself is "
                                           f"single-threaded inside OpenCV) + C port of cloud/hist; `--impl reference` runs one frame per core",
@@ -425,8 +519,9 @@ def main():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--mode", type=int, default=1, help="StereoSGBM mode: 1 = MODE_HH (8-path, headline), 3 = HH4, 0 = SGBM")
     ap.add_argument("--batch", type=int, default=16, help="camera-frames per GPU per step (<= 32; 32 measured no faster than 16)")
-    ap.add_argument("--distinct", type=int, default=2, help="distinct synthetic camera-frames generated per rank")
-    ap.add_argument("--ref-threads", type=int, default=16)
+    ap.add_argument("--distinct", type=int, default=4, help="distinct synthetic camera-frames generated per rank")
+    ap.add_argument("--ref-threads", type=int, default=0, help="reference arm: camera-frames in parallel (0 = every host core)")
+    ap.add_argument("--no-cloud-e2e", action="store_true", help="skip the second end-to-end measurement (point clouds to the host)")
     ap.add_argument("--cpu-rows", type=int, default=1080)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -159,13 +159,21 @@ typedef struct {
     int use_still; /* apply_slic_still_weights */
     int ordered;   /* 1: sum every bin in point order like the reference's sequential loop (weighted histograms bit-exact;
                       a stable sort by bin, slower); 0: float atomics (counts exact, weighted sums <= 1e-5 relative) */
+    float super_pixel_min_z; /* FloorHistogram::Params::super_pixel_min_z (floor-histogram.hpp:39, default 0.25f): only
+                                used by the super-pixel table */
 } mvs_hist_params;
+
+/* SparseHistCell, geometry/sparse-hist-cell.hpp:8-17: histogram cell of a super-pixel's centroid and its "count". */
+typedef struct {
+    int32_t x, y;  /* {-1, -1} when no point of the super-pixel landed in the histogram */
+    float count;
+} mvs_sparse_hist_cell;
 
 /* ensure_floor_hist_dims, cost-functions/floor-histogram.cpp:19-35.  aabb = {left, top, right, bottom}. */
 int mvs_hist_dims(const double aabb[4], float hist_sz, int* hw, int* hh);
 
 /* Replaces process_camera_i inside FloorHistogram::calculate, cost-functions/floor-histogram.cpp:197-275
- * (histogram part; the super-pixel centroid table :269-286 is out of scope).
+ * (histogram part; mvs_floor_hist_camera_cells adds the super-pixel centroid table).
  * et = {tx,ty,tz, qx,qy,qz,qw, scale} of EuclideanTransform (geometry/euclidean-transform.hpp:121-124);
  * cam_center = translations[cam] (pipeline/nodes/floor_hist.cpp:122); labels (int32 lw x lh, row stride lw)
  * and still_score (n_labels doubles) may be NULL.  cam_hist: float hw x hh, row stride hw, overwritten.
@@ -175,6 +183,17 @@ int mvs_floor_hist_camera(mvs_ctx* ctx, const mvs_hist_params* p, const double e
                           const double cam_center[3], const double* Xs, const int32_t* xy, int32_t n,
                           const int32_t* labels, int lw, int lh, const double* still_score, int n_labels,
                           float* cam_hist, int hw, int hh);
+
+/* The same, plus camera_info[cam].slic_to_hist_xy (floor-histogram.cpp:222-225,269-286): per super-pixel, in point order,
+ * sC += Vector4f(to_vec3f(Y) * float(weight), sC.w + weight) over the points that landed in the histogram with
+ * label >= 0 and Y.z >= super_pixel_min_z -- exactly as written there, so the fourth component roughly doubles at every
+ * point and overflows to +inf beyond ~128 points (the centroid then comes out as the world origin and count as inf) --
+ * then xy = round(project_to_histogram(sC.xyz / sC.w)), count = round(sC.w).  slic_to_hist_xy: n_labels cells, bit-exact
+ * with the CPU restatement (labels >= n_labels are skipped; the reference would index past its vector).  NULL skips it. */
+int mvs_floor_hist_camera_cells(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
+                                const double cam_center[3], const double* Xs, const int32_t* xy, int32_t n,
+                                const int32_t* labels, int lw, int lh, const double* still_score, int n_labels,
+                                float* cam_hist, int hw, int hh, mvs_sparse_hist_cell* slic_to_hist_xy);
 
 /* Replaces `hist += camera_info[cam].hist` over cameras, cost-functions/floor-histogram.cpp:296-300.
  * cam_hists: n_cams consecutive hw x hh float images, summed in camera order. */
@@ -269,6 +288,8 @@ typedef struct {
     const int32_t* n_dev;            /* N (device scalar) */
     const double* centroid_dev;      /* 3 doubles */
     int hw, hh;
+    const mvs_sparse_hist_cell* slic_to_hist_xy_dev; /* n_labels cells (NULL when the frame had no label image) */
+    int n_labels;
 } mvs_frame_result;
 
 /* Enqueue the whole path for one camera-frame on the context's stream (asynchronous).  `slot` selects
@@ -302,6 +323,7 @@ typedef struct {
     int32_t* n_out;
     double* centroid; /* 3 doubles */
     float* cam_hist;
+    mvs_sparse_hist_cell* slic_to_hist_xy; /* n_labels cells of the slot's frame (skipped when it had no label image) */
 } mvs_fetch_desc;
 int mvs_frame_fetch_batch(mvs_ctx* ctx, int first_slot, int n, const mvs_fetch_desc* d);
 

@@ -25,7 +25,11 @@ class Bcam(C.Structure):
 
 class HistParams(C.Structure):
     _fields_ = [("hist_sz", c_float), ("min_z", c_float), ("max_z", c_float), ("weighting", c_int), ("use_still", c_int),
-                ("ordered", c_int)]
+                ("ordered", c_int), ("super_pixel_min_z", c_float)]
+
+
+class SparseHistCell(C.Structure):
+    _fields_ = [("x", C.c_int32), ("y", C.c_int32), ("count", c_float)]
 
 
 class LocParams(C.Structure):
@@ -45,13 +49,13 @@ class FrameDesc(C.Structure):
 
 class FetchDesc(C.Structure):
     _fields_ = [("disp", c_void_p), ("dstep", c_size_t), ("Xs", c_void_p), ("xy", c_void_p), ("lookup", c_void_p),
-                ("n_out", C.POINTER(C.c_int32)), ("centroid", c_void_p), ("cam_hist", c_void_p)]
+                ("n_out", C.POINTER(C.c_int32)), ("centroid", c_void_p), ("cam_hist", c_void_p), ("slic_to_hist_xy", c_void_p)]
 
 
 class FrameResult(C.Structure):
     _fields_ = [("rectified_dev", c_void_p * 2), ("disp16_dev", c_void_p), ("disp_dev", c_void_p), ("Xs_dev", c_void_p),
                 ("xy_dev", c_void_p), ("lookup_dev", c_void_p), ("cam_hist_dev", c_void_p), ("n_dev", c_void_p),
-                ("centroid_dev", c_void_p), ("hw", c_int), ("hh", c_int)]
+                ("centroid_dev", c_void_p), ("hw", c_int), ("hh", c_int), ("slic_to_hist_xy_dev", c_void_p), ("n_labels", c_int)]
 
 
 # name -> (restype, argtypes); must list every symbol include/mvstereo.h declares
@@ -80,6 +84,8 @@ SIGNATURES = {
     "mvs_hist_dims": (c_int,[c_void_p, c_float, C.POINTER(c_int), C.POINTER(c_int)]),
     "mvs_floor_hist_camera": (c_int, [c_void_p, C.POINTER(HistParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                       C.c_int32, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int]),
+    "mvs_floor_hist_camera_cells": (c_int, [c_void_p, C.POINTER(HistParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                            C.c_int32, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p]),
     "mvs_hist_sum": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "mvs_hist_post": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_float]),
     "mvs_hist_post_dev": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_float]),

@@ -328,11 +328,12 @@ class FloorHistogramParams:
     weighting: int = WGT_NORM
     apply_slic_still_weights: bool = True
     skip_cameras: tuple = ()
+    super_pixel_min_z: float = 0.25
     ordered: bool = False   # not a reference field: sum every bin in point order (weighted histograms bit-exact)
 
     def to_c(self) -> HistParams:
         return HistParams(self.hist_sz, self.hist_min_z, self.hist_max_z, int(self.weighting), int(self.apply_slic_still_weights),
-                          int(self.ordered))
+                          int(self.ordered), self.super_pixel_min_z)
 
 
 def hist_dims(aabb, hist_sz):
@@ -467,7 +468,7 @@ def frame_fetch(ctx: Context, slot: int, w: int, h: int, hw: int, hh: int, want_
     return out
 
 
-def frame_fetch_batch(ctx: Context, first_slot: int, n: int, w: int, h: int, hw: int, hh: int, want_cloud=True):
+def frame_fetch_batch(ctx: Context, first_slot: int, n: int, w: int, h: int, hw: int, hh: int, want_cloud=True, n_labels=0):
     """mvs_frame_fetch_batch into fresh numpy arrays: one blocking point per batch (two with clouds)."""
     from ._lib import FetchDesc
 
@@ -482,6 +483,9 @@ def frame_fetch_batch(ctx: Context, first_slot: int, n: int, w: int, h: int, hw:
         descs[i].n_out = C.pointer(ns[i])
         if want_cloud:
             descs[i].Xs, descs[i].xy = o["Xs"].ctypes.data, o["xy"].ctypes.data
+        if n_labels:
+            o["_cells"] = (_lib.SparseHistCell * n_labels)()
+            descs[i].slic_to_hist_xy = C.cast(o["_cells"], C.c_void_p)
         outs.append(o)
     ctx.check(ctx.lib.mvs_frame_fetch_batch(ctx.h, first_slot, n, descs), "mvs_frame_fetch_batch")
     ctx.sync()
@@ -489,6 +493,8 @@ def frame_fetch_batch(ctx: Context, first_slot: int, n: int, w: int, h: int, hw:
         o["N"] = ns[i].value
         if want_cloud:
             o["Xs"], o["xy"] = o["Xs"][:o["N"]], o["xy"][:o["N"]]
+        if n_labels:   # (n_labels, 3) float64: x, y, count of every SparseHistCell
+            o["slic_to_hist_xy"] = np.array([(c.x, c.y, c.count) for c in o.pop("_cells")], np.float64).reshape(n_labels, 3)
     return outs
 
 

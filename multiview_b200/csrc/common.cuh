@@ -29,7 +29,7 @@ struct StageTimer {
 };
 
 struct FrameSlot {
-    int w = 0, h = 0, hw = 0, hh = 0;
+    int w = 0, h = 0, hw = 0, hh = 0, n_labels = 0;   // n_labels > 0: the slot holds a super-pixel table
     bool valid = false;
 };
 
@@ -148,7 +148,8 @@ int point_cloud_dev(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, int w
 int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
                           const double cam_center[3], const double* Xs, const int32_t* xy, const int32_t* n_dev,
                           int n_host /* used when n_dev == nullptr */, const int32_t* labels, int lw, int lh,
-                          const double* still, int n_labels, float* cam_hist, int hw, int hh);
+                          const double* still, int n_labels, float* cam_hist, int hw, int hh,
+                          mvs_sparse_hist_cell* cells = nullptr /* slic_to_hist_xy, n_labels entries, optional */);
 int disp_merge_ref_dev(mvs_ctx* ctx, float* disp, const float* ref, const int32_t* labels, const uint8_t* still_cutoff,
                        int n_labels, int w, int h);
 int hist_post_dev(mvs_ctx* ctx, float* hist, int hw, int hh, float sigma, float minc, float maxc, const char* scratch);

@@ -24,6 +24,8 @@ struct SlotBufs {
     float* cam_hist;
     const int32_t* labels;   // device, packed w x h (nullptr: no still weights)
     const double* still;
+    mvs_sparse_hist_cell* cells;   // slic_to_hist_xy (nullptr without labels)
+    int n_labels;
 };
 
 extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame_desc* descs, int n_frames,
@@ -66,7 +68,8 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     for (int f = 0; f < n_frames; ++f) {
         const mvs_frame_desc* d = descs + f;
         const int slot = first_slot + f;
-        const bool use_labels = d->hist.use_still && d->labels && d->still_score && d->n_labels > 0;
+        // the label image feeds the still weights (when enabled) and, always, the super-pixel table
+        const bool use_labels = d->labels && d->n_labels > 0 && (!d->hist.use_still || d->still_score);
         if (use_labels && d->lstep < (size_t)d->w * 4) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d: lstep too small", f);
         if ((!d->inputs_on_device || !d->maps_on_device || (use_labels && !d->labels_on_device))) {
             any_upload = true;
@@ -105,8 +108,11 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         sb[f].cen = (double*)arena_get(ctx, slot_name(slot, "centroid").c_str(), 24);
         if (!sb[f].disp16 || !sb[f].dispf || !sb[f].Xs || !sb[f].xy || !sb[f].lookup || !sb[f].nd || !sb[f].cen) return MVS_ERR_NOMEM;
         sb[f].cam_hist = hists + (size_t)slot * hw * hh;
-        sb[f].labels = nullptr; sb[f].still = nullptr;
+        sb[f].labels = nullptr; sb[f].still = nullptr; sb[f].cells = nullptr; sb[f].n_labels = 0;
         if (use_labels) {
+            sb[f].n_labels = d->n_labels;
+            sb[f].cells = (mvs_sparse_hist_cell*)arena_get(ctx, slot_name(slot, "cells").c_str(), sizeof(mvs_sparse_hist_cell) * (size_t)d->n_labels);
+            if (!sb[f].cells) return MVS_ERR_NOMEM;
             if (d->labels_on_device && d->lstep == (size_t)w * 4) {
                 sb[f].labels = d->labels; sb[f].still = d->still_score;
             } else {
@@ -115,8 +121,8 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
                 if (!dl || !dsc) return MVS_ERR_NOMEM;
                 const cudaMemcpyKind kind = d->labels_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
                 MVS_CUDA(ctx, cudaMemcpy2DAsync(dl, (size_t)w * 4, d->labels, d->lstep, (size_t)w * 4, h, kind, cs));
-                MVS_CUDA(ctx, cudaMemcpyAsync(dsc, d->still_score, (size_t)d->n_labels * 8, kind, cs));
-                sb[f].labels = dl; sb[f].still = dsc;
+                if (d->still_score) MVS_CUDA(ctx, cudaMemcpyAsync(dsc, d->still_score, (size_t)d->n_labels * 8, kind, cs));
+                sb[f].labels = dl; sb[f].still = d->still_score ? dsc : nullptr;
                 any_upload = true;
             }
         }
@@ -225,7 +231,7 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     stage_begin(ctx, "hist");
     for (int f = 0; f < n_frames && !rc; ++f)
         rc = floor_hist_camera_dev(ctx, &descs[f].hist, descs[f].et, descs[f].aabb, descs[f].cam_center, sb[f].Xs, sb[f].xy, sb[f].nd, (int)n /* capacity */,
-                                   sb[f].labels, w, h, sb[f].still, descs[f].n_labels, sb[f].cam_hist, hw, hh);
+                                   sb[f].labels, w, h, sb[f].still, descs[f].n_labels, sb[f].cam_hist, hw, hh, sb[f].cells);
     stage_end(ctx, "hist");
     if (rc) return rc;
 
@@ -235,13 +241,14 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         MVS_CUDA(ctx, cudaEventRecord(ctx->ev_slot_done[first_slot + f], ts));
         ctx->slot_done_recorded[first_slot + f] = true;
         FrameSlot& fs = ctx->slots[first_slot + f];
-        fs.w = w; fs.h = h; fs.hw = hw; fs.hh = hh; fs.valid = true;
+        fs.w = w; fs.h = h; fs.hw = hw; fs.hh = hh; fs.n_labels = sb[f].n_labels; fs.valid = true;
         if (out) {
             mvs_frame_result* o = out + f;
             o->rectified_dev[0] = sb[f].rect[0]; o->rectified_dev[1] = sb[f].rect[1];
             o->disp16_dev = sb[f].disp16; o->disp_dev = sb[f].dispf; o->Xs_dev = sb[f].Xs; o->xy_dev = sb[f].xy;
             o->lookup_dev = sb[f].lookup; o->cam_hist_dev = sb[f].cam_hist; o->n_dev = sb[f].nd; o->centroid_dev = sb[f].cen;
             o->hw = hw; o->hh = hh;
+            o->slic_to_hist_xy_dev = sb[f].cells; o->n_labels = sb[f].n_labels;
         }
     }
     return MVS_OK;
@@ -312,6 +319,9 @@ extern "C" int mvs_frame_fetch_batch(mvs_ctx* ctx, int first_slot, int n, const 
         if (d[i].centroid) MVS_CUDA(ctx, cudaMemcpyAsync(d[i].centroid, arena_get(ctx, slot_name(slot, "centroid").c_str(), 24), 24, cudaMemcpyDeviceToHost, s));
         if (d[i].cam_hist)
             MVS_CUDA(ctx, cudaMemcpyAsync(d[i].cam_hist, hists + (size_t)slot * fs.hw * fs.hh, sizeof(float) * (size_t)fs.hw * fs.hh, cudaMemcpyDeviceToHost, s));
+        if (d[i].slic_to_hist_xy && fs.n_labels > 0)
+            MVS_CUDA(ctx, cudaMemcpyAsync(d[i].slic_to_hist_xy, arena_get(ctx, slot_name(slot, "cells").c_str(), 0),
+                                          sizeof(mvs_sparse_hist_cell) * (size_t)fs.n_labels, cudaMemcpyDeviceToHost, s));
         want_cloud = want_cloud || d[i].Xs || d[i].xy;
     }
     MVS_CUDA(ctx, cudaStreamSynchronize(s));   // the one blocking point of a batch without clouds

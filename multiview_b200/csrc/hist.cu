@@ -4,8 +4,6 @@
 // fp64 geometry compiled with --fmad=false (bin = round(...) flips on last-ulp differences), fp32 weights.
 #include <math.h>
 
-#include <cub/device/device_radix_sort.cuh>
-
 #include "common.cuh"
 
 struct HistArgs {
@@ -41,7 +39,8 @@ __device__ __forceinline__ Q hist_inverse_rotation(const HistArgs& a)
 // bin and weight of point i; false when the point does not land in the histogram
 __device__ __forceinline__ bool hist_point(const HistArgs& a, const Q& q, const Q& inv, const double* __restrict__ Xs,
                                            const int32_t* __restrict__ xy, const int32_t* __restrict__ labels,
-                                           const double* __restrict__ still, int i, int* bin, float* weight)
+                                           const double* __restrict__ still, int i, int* bin, float* weight,
+                                           int* label_out = nullptr, double* Y_out = nullptr)
 {
     double X0 = Xs[3 * (size_t)i], X1 = Xs[3 * (size_t)i + 1], X2 = Xs[3 * (size_t)i + 2];
     Q v = {X0 * a.et[7], X1 * a.et[7], X2 * a.et[7], 0.0};
@@ -56,11 +55,14 @@ __device__ __forceinline__ bool hist_point(const HistArgs& a, const Q& q, const 
     double dx = X0 - a.cc[0], dy = X1 - a.cc[1], dz = X2 - a.cc[2];
     double q2 = dx * dx + dy * dy + dz * dz;
     double wgt = a.weighting == MVS_WGT_NONE ? 1.0 : (a.weighting == MVS_WGT_NORM ? sqrt(q2) : q2);
-    if (a.use_still && labels) {
+    int label = -1;
+    if (labels) {   // slic_lookup.in_bounds(x) ? slic_lookup(x) : -1 (floor-histogram.cpp:236)
         int px = xy[2 * (size_t)i], py = xy[2 * (size_t)i + 1];
-        int label = ((unsigned)px < (unsigned)a.lw && (unsigned)py < (unsigned)a.lh) ? labels[(size_t)py * a.lw + px] : -1;
-        if (label >= 0 && label < a.n_labels) wgt *= 1.0 + 10.0 * still[label];
+        label = ((unsigned)px < (unsigned)a.lw && (unsigned)py < (unsigned)a.lh) ? labels[(size_t)py * a.lw + px] : -1;
+        if (a.use_still && label >= 0 && label < a.n_labels) wgt *= 1.0 + 10.0 * still[label];
     }
+    if (label_out) *label_out = label;
+    if (Y_out) { Y_out[0] = Yx; Y_out[1] = Yy; Y_out[2] = Yz; }
     *bin = by * a.hw + bx;
     *weight = (float)wgt;
     return true;
@@ -97,70 +99,208 @@ floor_hist_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __re
     }
 }
 
-// ---- order-preserving accumulation (mvs_hist_params.ordered): every bin is summed in point order, like the
-// reference's sequential `cam_hist(x, y) += weight` (floor-histogram.cpp:265-267), so weighted histograms come out
-// bit for bit.  (1) bin + weight per point (points past N and rejected points get the bin `nbins`), (2) a STABLE radix
-// sort of the weights by bin keeps point order inside a bin, (3) one thread per bin adds its segment up in order.
+// ---- order-preserving accumulation (mvs_hist_params.ordered; the super-pixel table) -------------------------------
+// The reference adds weights to a bin, and centroids to a super-pixel, in point order with float arithmetic
+// (floor-histogram.cpp:265-273), so a bit-exact result needs every key's contributions summed in that order:
+//   (1) key (bin or label) and values per point, in parallel; rejected points and points past N get the key `nkeys`;
+//   (2) a STABLE least-significant-digit radix sort of the point indices by key (8 bits per pass, two passes for up to
+//       65535 keys): stability keeps the point order inside a key;
+//   (3) the values gathered into sorted order, segment bounds per key, and one thread per key adding its segment up
+//       front to back (independent loads eight deep, one dependent float add per element).
+#define RS_THREADS 256
+#define RS_ROWS 16                         // 32-item rows per warp
+#define RS_TILE (RS_THREADS * RS_ROWS)     // items per block
+// digit counts per block: cnt[digit * nblk + block]
+__global__ void __launch_bounds__(RS_THREADS)
+rs_count_kernel(const uint32_t* __restrict__ keys, int n, int shift, int nblk, int* __restrict__ cnt)
+{
+    __shared__ int h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * RS_TILE;
+#pragma unroll
+    for (int k = 0; k < RS_ROWS; ++k) {
+        const int i = base + k * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1);
+    }
+    __syncthreads();
+    cnt[threadIdx.x * nblk + blockIdx.x] = h[threadIdx.x];
+}
+// exclusive scan of cnt (digit-major, so digit d of block b starts after every smaller digit and after digit d of the
+// blocks before b): one block
+__global__ void __launch_bounds__(1024)
+rs_scan_kernel(int* __restrict__ cnt, int m)
+{
+    __shared__ int part[1024];
+    const int per = (m + 1023) / 1024, i0 = threadIdx.x * per, i1 = min(i0 + per, m);
+    int s = 0;
+    for (int i = i0; i < i1; ++i) s += cnt[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {   // inclusive Hillis-Steele scan of the partial sums
+        int v = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    int run = part[threadIdx.x] - s;
+    for (int i = i0; i < i1; ++i) { int c = cnt[i]; cnt[i] = run; run += c; }
+}
+// stable scatter of (key, value) by the digit; vals_in == nullptr means the identity (the first pass sorts indices)
+__global__ void __launch_bounds__(RS_THREADS)
+rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, int n, int shift, int nblk,
+                  const int* __restrict__ offs, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out)
+{
+    __shared__ int wcnt[RS_THREADS / 32][256];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int k = threadIdx.x; k < (RS_THREADS / 32) * 256; k += RS_THREADS) (&wcnt[0][0])[k] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * RS_TILE + w * (RS_ROWS * 32);   // a warp owns RS_ROWS consecutive rows of 32 items
+    // per-warp digit counts
+    for (int r = 0; r < RS_ROWS; ++r) {
+        const int i = base + r * 32 + lane;
+        const uint32_t d = i < n ? (keys_in[i] >> shift) & 255u : 256u;
+        const unsigned m = __match_any_sync(0xffffffffu, d);
+        if (d < 256u && lane == __ffs(m) - 1) wcnt[w][d] += __popc(m);
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // digit threadIdx.x: running start of every warp
+        int run = offs[threadIdx.x * nblk + blockIdx.x];
+        for (int ww = 0; ww < RS_THREADS / 32; ++ww) { int c = wcnt[ww][threadIdx.x]; wcnt[ww][threadIdx.x] = run; run += c; }
+    }
+    __syncthreads();
+    for (int r = 0; r < RS_ROWS; ++r) {
+        const int i = base + r * 32 + lane;
+        const uint32_t key = i < n ? keys_in[i] : 0u;
+        const uint32_t d = i < n ? (key >> shift) & 255u : 256u;
+        const unsigned m = __match_any_sync(0xffffffffu, d);
+        int pos = 0;
+        if (d < 256u) pos = wcnt[w][d] + __popc(m & ((1u << lane) - 1u));
+        __syncwarp();   // every lane has read the running start before a leader advances it
+        if (d < 256u) {
+            if (lane == __ffs(m) - 1) wcnt[w][d] += __popc(m);
+            keys_out[pos] = key;
+            vals_out[pos] = vals_in ? vals_in[i] : (uint32_t)i;
+        }
+        __syncwarp();
+    }
+}
+
+// sorted point indices by key: perm (and the sorted keys) in `keys` / `perm` on return; tmp buffers of n each
+static int stable_sort_by_key(mvs_ctx* ctx, uint32_t* keys, uint32_t* perm, uint32_t* keys_tmp, uint32_t* perm_tmp, int n, int nkeys,
+                              int* cnt /* 256 * nblk */)
+{
+    cudaStream_t s = ctx->stream;
+    const int nblk = cdiv(n, RS_TILE);
+    int bits = 1;
+    while ((1 << bits) <= nkeys) ++bits;   // keys 0 .. nkeys
+    const int passes = (bits + 7) / 8 + (((bits + 7) / 8) & 1);   // an even number of passes: the result lands in keys / perm
+    const uint32_t *kin = keys, *vin = nullptr;
+    uint32_t *kout = keys_tmp, *vout = perm_tmp;
+    for (int p = 0; p < passes; ++p) {
+        rs_count_kernel<<<nblk, RS_THREADS, 0, s>>>(kin, n, 8 * p, nblk, cnt);
+        rs_scan_kernel<<<1, 1024, 0, s>>>(cnt, 256 * nblk);
+        rs_scatter_kernel<<<nblk, RS_THREADS, 0, s>>>(kin, vin, n, 8 * p, nblk, cnt, kout, vout);
+        MVS_LAUNCH_CHECK_N(ctx, "stable radix sort pass", 3);
+        kin = kout; vin = vout;
+        kout = kout == keys_tmp ? keys : keys_tmp;
+        vout = vout == perm_tmp ? perm : perm_tmp;
+    }
+    return MVS_OK;
+}
+
+// segment [seg[k], seg[k + 1]) of key k in the sorted order (keys that do not occur get an empty segment)
+__global__ void seg_bounds_kernel(const uint32_t* __restrict__ sorted_keys, int n, int nkeys, int* __restrict__ seg)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const uint32_t k = min(sorted_keys[j], (uint32_t)nkeys), kp = j ? min(sorted_keys[j - 1], (uint32_t)nkeys) : 0u;
+    if (j == 0) for (uint32_t q = 0; q <= k; ++q) seg[q] = 0;
+    else for (uint32_t q = kp + 1; q <= k; ++q) seg[q] = j;        // keys kp+1 .. k start here (those in between are empty)
+    if (j == n - 1) for (uint32_t q = k + 1; q <= (uint32_t)nkeys + 1; ++q) seg[q] = n;
+}
+// bin + weight per point; with cell4 != nullptr also the super-pixel key and the four floats the reference accumulates
+// per super-pixel: to_vec3f(Y) * float(weight) and the weight (floor-histogram.cpp:269-273)
 __global__ void __launch_bounds__(256)
 hist_points_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __restrict__ xy, const int32_t* n_dev, int n_host,
                    int cap, const int32_t* __restrict__ labels, const double* __restrict__ still, uint32_t* __restrict__ bins,
-                   float* __restrict__ weights)
+                   float* __restrict__ weights, uint32_t* __restrict__ lkeys, float4* __restrict__ cell4, double sp_min_z)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= cap) return;
     const int n = n_dev ? *n_dev : n_host;
     const Q q = {a.et[3], a.et[4], a.et[5], a.et[6]};
     const Q inv = hist_inverse_rotation(a);
-    int bin = a.hw * a.hh;
+    int bin = a.hw * a.hh, label = -1;
     float wgt = 0.0f;
-    if (i < n && !hist_point(a, q, inv, Xs, xy, labels, still, i, &bin, &wgt)) bin = a.hw * a.hh;
-    bins[i] = (uint32_t)bin;
-    weights[i] = wgt;
+    double Y[3] = {0.0, 0.0, 0.0};
+    bool ok = i < n && hist_point(a, q, inv, Xs, xy, labels, still, i, &bin, &wgt, &label, Y);
+    if (!ok) bin = a.hw * a.hh;
+    if (bins) { bins[i] = (uint32_t)bin; weights[i] = wgt; }
+    if (cell4) {
+        const bool in = ok && label >= 0 && label < a.n_labels && Y[2] >= sp_min_z;
+        lkeys[i] = in ? (uint32_t)label : (uint32_t)a.n_labels;
+        cell4[i] = make_float4((float)Y[0] * wgt, (float)Y[1] * wgt, (float)Y[2] * wgt, wgt);   // (this file is built --fmad=false)
+    }
 }
-__global__ void hist_segment_starts_kernel(const uint32_t* __restrict__ sorted_bins, int cap, int nbins, int* __restrict__ start)
+__global__ void gather_f1_kernel(const float* __restrict__ v, const uint32_t* __restrict__ perm, int n, float* __restrict__ out)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= cap) return;
-    const uint32_t b = sorted_bins[j];
-    if ((int)b < nbins && (j == 0 || sorted_bins[j - 1] != b)) start[b] = j;
+    if (j < n) out[j] = v[perm[j]];
 }
-__global__ void hist_ordered_sum_kernel(const uint32_t* __restrict__ sorted_bins, const float* __restrict__ sorted_weights, int cap,
-                                        int nbins, const int* __restrict__ start, float* __restrict__ hist)
+__global__ void gather_f4_kernel(const float4* __restrict__ v, const uint32_t* __restrict__ perm, int n, float4* __restrict__ out)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) out[j] = v[perm[j]];
+}
+// cam_hist(x, y) += weight in point order: one thread per bin, loads eight deep, one dependent add per element
+__global__ void hist_ordered_sum_kernel(const float* __restrict__ w, const int* __restrict__ seg, int nbins, float* __restrict__ hist)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= nbins) return;
     float s = 0.0f;   // cam_hist.fill(0.0f), floor-histogram.cpp:200
-    const int j0 = start[b];
-    if (j0 >= 0)
-        for (int j = j0; j < cap && sorted_bins[j] == (uint32_t)b; ++j) s += sorted_weights[j];
+    int j = seg[b];
+    const int j1 = seg[b + 1];
+    for (; j + 8 <= j1; j += 8) {
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = w[j + k];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s += v[k];
+    }
+    for (; j < j1; ++j) s += w[j];
     hist[b] = s;
 }
-
-static int floor_hist_ordered_dev(mvs_ctx* ctx, const HistArgs& a, const double* Xs, const int32_t* xy, const int32_t* n_dev, int n_host,
-                                  int cap, const int32_t* labels, const double* still, float* cam_hist)
+// slic_to_hist_xy: per super-pixel, in point order, sC += Vector4f(Yf * wf, sC.w + wf)  -- as written in the reference,
+// the fourth component doubles at every point (floor-histogram.cpp:270-272) -- then the cell of the centroid (:277-285)
+__global__ void slic_cells_kernel(const float4* __restrict__ c, const int* __restrict__ seg, int n_labels, double left, double top,
+                                  double hist_sz, mvs_sparse_hist_cell* __restrict__ out)
 {
-    cudaStream_t s = ctx->stream;
-    const int nbins = a.hw * a.hh;
-    if (cap <= 0) {
-        MVS_CUDA(ctx, cudaMemsetAsync(cam_hist, 0, sizeof(float) * (size_t)nbins, s));
-        return MVS_OK;
+    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n_labels) return;
+    float sx = 0.0f, sy = 0.0f, sz = 0.0f, sw = 0.0f;
+    int j = seg[l];
+    const int j1 = seg[l + 1];
+    for (; j + 4 <= j1; j += 4) {
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = c[j + k];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { sx += v[k].x; sy += v[k].y; sz += v[k].z; sw += sw + v[k].w; }
     }
-    MVS_ARENA(ctx, uint32_t, bins, "hist.ordered.bins", (size_t)cap * 2);
-    MVS_ARENA(ctx, float, wts, "hist.ordered.weights", (size_t)cap * 2);
-    MVS_ARENA(ctx, int, start, "hist.ordered.start", (size_t)nbins);
-    int end_bit = 1;
-    while ((1 << end_bit) <= nbins) ++end_bit;   // keys 0 .. nbins
-    size_t tmp_bytes = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, bins, bins + cap, wts, wts + cap, cap, 0, end_bit, s);
-    MVS_ARENA(ctx, unsigned char, tmp, "hist.ordered.tmp", tmp_bytes + 16);
-    hist_points_kernel<<<cdiv(cap, 256), 256, 0, s>>>(a, Xs, xy, n_dev, n_host, cap, labels, still, bins, wts);
-    MVS_LAUNCH_CHECK(ctx, "hist_points_kernel");
-    MVS_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, bins, bins + cap, wts, wts + cap, cap, 0, end_bit, s));
-    MVS_CUDA(ctx, cudaMemsetAsync(start, 0xff, sizeof(int) * (size_t)nbins, s));
-    hist_segment_starts_kernel<<<cdiv(cap, 256), 256, 0, s>>>(bins + cap, cap, nbins, start);
-    hist_ordered_sum_kernel<<<cdiv(nbins, 128), 128, 0, s>>>(bins + cap, wts + cap, cap, nbins, start, cam_hist);
-    MVS_LAUNCH_CHECK_N(ctx, "ordered histogram kernels", 2);
-    return MVS_OK;
+    for (; j < j1; ++j) { const float4 v = c[j]; sx += v.x; sy += v.y; sz += v.z; sw += sw + v.w; }
+    mvs_sparse_hist_cell cell = {-1, -1, 0.0f};   // SparseHistCell{{-1, -1}, 0}
+    if (sw != 0.0f) {
+        const double cx = (double)sx / (double)sw, cy = (double)sy / (double)sw;
+        const double zx = (cx - left) / hist_sz + 1e-9, zy = (cy - top) / hist_sz + 1e-9;
+        // to_pt2(Z.round()): int(std::round(.)); out-of-int-range / NaN is undefined in the reference, clamped here
+        const double rx = round(zx), ry = round(zy);
+        cell.x = rx >= -2147483648.0 && rx <= 2147483647.0 ? (int)rx : -1;
+        cell.y = ry >= -2147483648.0 && ry <= 2147483647.0 ? (int)ry : -1;
+        cell.count = roundf(sw);
+    }
+    out[l] = cell;
 }
 
 __global__ void hist_sum_kernel(const float* __restrict__ cam_hists, int n_cams, size_t n, float* __restrict__ hist)
@@ -181,10 +321,53 @@ extern "C" int mvs_hist_dims(const double aabb[4], float hist_sz, int* hw, int* 
     return (*hw > 0 && *hh > 0) ? MVS_OK : MVS_ERR_ARG;
 }
 
+// ordered histogram and / or super-pixel table of one camera (cap = capacity of Xs / xy when N lives on the device)
+static int floor_hist_ordered_dev(mvs_ctx* ctx, const HistArgs& a, const double* Xs, const int32_t* xy, const int32_t* n_dev, int n_host,
+                                  int cap, const int32_t* labels, const double* still, double sp_min_z, float* cam_hist /* or null */,
+                                  mvs_sparse_hist_cell* cells /* or null */)
+{
+    cudaStream_t s = ctx->stream;
+    const int nbins = a.hw * a.hh;
+    if (cap <= 0) cap = 1;   // one rejected pseudo-point (N = 0 keeps it out), so that every output is still written
+    const int nblk = cdiv(cap, RS_TILE);
+    MVS_ARENA(ctx, uint32_t, keys, "hist.ordered.keys", (size_t)cap * 4);       // bins | tmp | labels | tmp
+    MVS_ARENA(ctx, uint32_t, perm, "hist.ordered.perm", (size_t)cap * 2);       // perm | tmp
+    MVS_ARENA(ctx, float, wts, "hist.ordered.weights", (size_t)cap * 2);        // weights | sorted weights
+    MVS_ARENA(ctx, int, cnt, "hist.ordered.cnt", (size_t)256 * nblk);
+    const int nk = max(nbins, cells ? a.n_labels : 0);
+    MVS_ARENA(ctx, int, seg, "hist.ordered.seg", (size_t)nk + 2);
+    float4* c4 = nullptr;
+    if (cells) {
+        c4 = (float4*)arena_get(ctx, "hist.ordered.cell4", sizeof(float4) * (size_t)cap * 2);
+        if (!c4) return MVS_ERR_NOMEM;
+    }
+    uint32_t *bins = keys, *lkeys = keys + 2 * (size_t)cap;
+    hist_points_kernel<<<cdiv(cap, 256), 256, 0, s>>>(a, Xs, xy, n_dev, n_host, cap, labels, still, cam_hist ? bins : nullptr, wts,
+                                                       cells ? lkeys : nullptr, c4, sp_min_z);
+    MVS_LAUNCH_CHECK(ctx, "hist_points_kernel");
+    if (cam_hist) {
+        int rc = stable_sort_by_key(ctx, bins, perm, bins + cap, perm + cap, cap, nbins, cnt);
+        if (rc) return rc;
+        gather_f1_kernel<<<cdiv(cap, 256), 256, 0, s>>>(wts, perm, cap, wts + cap);
+        seg_bounds_kernel<<<cdiv(cap, 256), 256, 0, s>>>(bins, cap, nbins, seg);
+        hist_ordered_sum_kernel<<<cdiv(nbins, 128), 128, 0, s>>>(wts + cap, seg, nbins, cam_hist);
+        MVS_LAUNCH_CHECK_N(ctx, "ordered histogram kernels", 3);
+    }
+    if (cells && a.n_labels > 0) {
+        int rc = stable_sort_by_key(ctx, lkeys, perm, lkeys + cap, perm + cap, cap, a.n_labels, cnt);
+        if (rc) return rc;
+        gather_f4_kernel<<<cdiv(cap, 256), 256, 0, s>>>(c4, perm, cap, c4 + cap);
+        seg_bounds_kernel<<<cdiv(cap, 256), 256, 0, s>>>(lkeys, cap, a.n_labels, seg);
+        slic_cells_kernel<<<cdiv(a.n_labels, 128), 128, 0, s>>>(c4 + cap, seg, a.n_labels, a.aabb[0], a.aabb[1], a.hist_sz, cells);
+        MVS_LAUNCH_CHECK_N(ctx, "super-pixel table kernels", 3);
+    }
+    return MVS_OK;
+}
+
 int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
                           const double cam_center[3], const double* Xs, const int32_t* xy, const int32_t* n_dev,
                           int n_host, const int32_t* labels, int lw, int lh, const double* still, int n_labels,
-                          float* cam_hist, int hw, int hh)
+                          float* cam_hist, int hw, int hh, mvs_sparse_hist_cell* cells)
 {
     HistArgs a;
     memcpy(a.et, et, sizeof(a.et));
@@ -193,8 +376,12 @@ int floor_hist_camera_dev(mvs_ctx* ctx, const mvs_hist_params* p, const double e
     a.hist_sz = (double)p->hist_sz; a.min_z = (double)p->min_z; a.max_z = (double)p->max_z;
     a.weighting = p->weighting; a.use_still = p->use_still && labels && still;
     a.lw = lw; a.lh = lh; a.n_labels = n_labels; a.hw = hw; a.hh = hh;
-    if (p->ordered)   // n_host is the capacity of Xs / xy when the count lives on the device
-        return floor_hist_ordered_dev(ctx, a, Xs, xy, n_dev, n_host, n_host, labels, still, cam_hist);
+    if (!labels || n_labels <= 0) cells = nullptr;
+    if (p->ordered || cells) {   // n_host is the capacity of Xs / xy when the count lives on the device
+        int rc = floor_hist_ordered_dev(ctx, a, Xs, xy, n_dev, n_host, n_host, labels, still, (double)p->super_pixel_min_z,
+                                        p->ordered ? cam_hist : nullptr, cells);
+        if (rc || p->ordered) return rc;
+    }
     MVS_CUDA(ctx, cudaMemsetAsync(cam_hist, 0, sizeof(float) * (size_t)hw * hh, ctx->stream));
     const size_t smem = sizeof(float) * (size_t)hw * hh;
     if (smem <= 100 * 1024) {  // two blocks per SM keep a private histogram each
@@ -225,6 +412,14 @@ extern "C" int mvs_floor_hist_camera(mvs_ctx* ctx, const mvs_hist_params* p, con
                                      const int32_t* labels, int lw, int lh, const double* still_score, int n_labels,
                                      float* cam_hist, int hw, int hh)
 {
+    return mvs_floor_hist_camera_cells(ctx, p, et, aabb, cam_center, Xs, xy, n, labels, lw, lh, still_score, n_labels, cam_hist, hw, hh, nullptr);
+}
+
+extern "C" int mvs_floor_hist_camera_cells(mvs_ctx* ctx, const mvs_hist_params* p, const double et[8], const double aabb[4],
+                                           const double cam_center[3], const double* Xs, const int32_t* xy, int32_t n,
+                                           const int32_t* labels, int lw, int lh, const double* still_score, int n_labels,
+                                           float* cam_hist, int hw, int hh, mvs_sparse_hist_cell* slic_to_hist_xy)
+{
     if (!ctx) return MVS_ERR_ARG;
     int ew = 0, eh = 0;
     if (!p || !et || !aabb || !cam_center || !cam_hist || n < 0 || (n > 0 && (!Xs || !xy)) ||
@@ -249,8 +444,14 @@ extern "C" int mvs_floor_hist_camera(mvs_ctx* ctx, const mvs_hist_params* p, con
         MVS_CUDA(ctx, cudaMemcpyAsync(dl, labels, (size_t)lw * lh * 4, cudaMemcpyHostToDevice, s));
         MVS_CUDA(ctx, cudaMemcpyAsync(ds, still_score, (size_t)n_labels * 8, cudaMemcpyHostToDevice, s));
     }
-    int rc = floor_hist_camera_dev(ctx, p, et, aabb, cam_center, dXs, dxy, nullptr, n, dl, lw, lh, ds, n_labels, dh, hw, hh);
+    mvs_sparse_hist_cell* dc = nullptr;
+    if (slic_to_hist_xy && dl) {
+        dc = (mvs_sparse_hist_cell*)arena_get(ctx, "hist.api.cells", sizeof(mvs_sparse_hist_cell) * (size_t)n_labels);
+        if (!dc) return MVS_ERR_NOMEM;
+    }
+    int rc = floor_hist_camera_dev(ctx, p, et, aabb, cam_center, dXs, dxy, nullptr, n, dl, lw, lh, ds, n_labels, dh, hw, hh, dc);
     if (rc) return rc;
+    if (dc) MVS_CUDA(ctx, cudaMemcpyAsync(slic_to_hist_xy, dc, sizeof(mvs_sparse_hist_cell) * (size_t)n_labels, cudaMemcpyDeviceToHost, s));
     MVS_CUDA(ctx, cudaMemcpyAsync(cam_hist, dh, sizeof(float) * (size_t)hw * hh, cudaMemcpyDeviceToHost, s));
     MVS_CUDA(ctx, cudaStreamSynchronize(s));
     return MVS_OK;

@@ -231,6 +231,30 @@ def floor_hist_camera(hp: HistParams, et, aabb, cam_center, Xs, xy, labels=None,
     return hist
 
 
+class SparseHistCell(ctypes.Structure):
+    _fields_ = [("x", ctypes.c_int32), ("y", ctypes.c_int32), ("count", ctypes.c_float)]
+
+
+def floor_hist_camera_cells(hp: HistParams, et, aabb, cam_center, Xs, xy, labels, still_score, super_pixel_min_z=0.25):
+    """Histogram plus camera_info[cam].slic_to_hist_xy (floor-histogram.cpp:222-225,269-286) as an (n_labels, 3) float64
+    array of (x, y, count)."""
+    Xs = np.ascontiguousarray(Xs, np.float64)
+    xy = np.ascontiguousarray(xy, np.int32)
+    hw, hh = hist_dims(aabb, hp.hist_sz)
+    hist = np.empty((hh, hw), np.float32)
+    labels = np.ascontiguousarray(labels, np.int32)
+    lh, lw = labels.shape
+    still_score = np.ascontiguousarray(still_score, np.float64)
+    nl = still_score.shape[0]
+    cells = (SparseHistCell * nl)()
+    f = lib().orc_floor_hist_camera_cells
+    f.restype = None
+    f(ctypes.byref(hp), (ctypes.c_double * 8)(*et), (ctypes.c_double * 4)(*aabb), (ctypes.c_double * 3)(*cam_center), _p(Xs), _p(xy),
+      ctypes.c_int(Xs.shape[0]), _p(labels), ctypes.c_int(lw), ctypes.c_int(lh), _p(still_score), ctypes.c_int(nl), _p(hist),
+      ctypes.c_int(hw), ctypes.c_int(hh), ctypes.c_float(super_pixel_min_z), cells)
+    return hist, np.array([(c.x, c.y, c.count) for c in cells], np.float64).reshape(nl, 3)
+
+
 def hist_sum(cam_hists):
     ch = np.ascontiguousarray(cam_hists, np.float32)
     n, hh, hw = ch.shape

@@ -191,12 +191,17 @@ void orc_hist_dims(const double aabb[4], float hist_sz, int* w, int* h)
     *w = (int)(ceil((aabb[2] - aabb[0]) * inv) + 1e-9);
 }
 
-/* floor-histogram.cpp:197-275 (per-camera histogram; the super-pixel centroid table is out of scope).
+/* floor-histogram.cpp:197-286: per-camera histogram and (cells != NULL) the super-pixel table slic_to_hist_xy
+ * (:222-225, :269-286; cells[l] = {x, y, count} as SparseHistCell, geometry/sparse-hist-cell.hpp:8-17).
  * cam_center = translations[cam] (floor_hist.cpp:122). labels may be NULL (lw=lh=0). */
-void orc_floor_hist_camera(const orc_hist_params* p, const double et[8], const double aabb[4], const double cam_center[3],
-                           const double* Xs, const int32_t* xy, int n, const int32_t* labels, int lw, int lh,
-                           const double* still_score, int n_labels, float* cam_hist, int hw, int hh)
+typedef struct { int32_t x, y; float count; } orc_sparse_hist_cell;
+void orc_floor_hist_camera_cells(const orc_hist_params* p, const double et[8], const double aabb[4], const double cam_center[3],
+                                 const double* Xs, const int32_t* xy, int n, const int32_t* labels, int lw, int lh,
+                                 const double* still_score, int n_labels, float* cam_hist, int hw, int hh,
+                                 float super_pixel_min_z, orc_sparse_hist_cell* cells)
 {
+    /* vector<Vector4f> spixel_Cs(n_slic_labels, {0,0,0,0}), floor-histogram.cpp:222-225 */
+    float* sC = cells ? (float*)calloc((size_t)(n_labels > 0 ? n_labels : 1) * 4, sizeof(float)) : NULL;
     memset(cam_hist, 0, sizeof(float) * (size_t)hw * hh);
     double hist_sz = (double)p->hist_sz;
     v3 Cc = V(cam_center[0], cam_center[1], cam_center[2]);
@@ -212,8 +217,38 @@ void orc_floor_hist_camera(const orc_hist_params* p, const double et[8], const d
         int px = xy[2 * i], py = xy[2 * i + 1];
         int label = (labels && px >= 0 && px < lw && py >= 0 && py < lh) ? labels[(size_t)py * lw + px] : -1;
         if (p->use_still && label >= 0 && label < n_labels) wgt *= 1.0 + 10.0 * still_score[label];
-        cam_hist[(size_t)by * hw + bx] += (float)wgt;
+        const float weight = (float)wgt;
+        cam_hist[(size_t)by * hw + bx] += weight;
+        /* :269-273  spixel_Cs[label] += Vector4f(to_vec3f(Y) * float(weight), spixel_Cs[label].w + weight)
+         * (labels >= n_labels are skipped: the reference would index past its vector) */
+        if (sC && label >= 0 && label < n_labels && Y.z >= (double)super_pixel_min_z) {
+            float* c = sC + 4 * (size_t)label;
+            const float ax = (float)Y.x * weight, ay = (float)Y.y * weight, az = (float)Y.z * weight;
+            const float aw = c[3] + weight;
+            c[0] += ax; c[1] += ay; c[2] += az; c[3] += aw;
+        }
     }
+    if (cells) { /* :276-286 */
+        for (int l = 0; l < n_labels; ++l) {
+            const float* c = sC + 4 * (size_t)l;
+            cells[l].x = -1; cells[l].y = -1; cells[l].count = 0.0f;
+            if (c[3] == 0.0f) continue;
+            const double cx = (double)c[0] / (double)c[3], cy = (double)c[1] / (double)c[3];
+            const double zx = (cx - aabb[0]) / hist_sz + 1e-9, zy = (cy - aabb[1]) / hist_sz + 1e-9;
+            const double rx = round(zx), ry = round(zy);
+            cells[l].x = rx >= -2147483648.0 && rx <= 2147483647.0 ? (int32_t)rx : -1;   /* int(NaN / huge) is undefined there */
+            cells[l].y = ry >= -2147483648.0 && ry <= 2147483647.0 ? (int32_t)ry : -1;
+            cells[l].count = roundf(c[3]);
+        }
+        free(sC);
+    }
+}
+
+void orc_floor_hist_camera(const orc_hist_params* p, const double et[8], const double aabb[4], const double cam_center[3],
+                           const double* Xs, const int32_t* xy, int n, const int32_t* labels, int lw, int lh,
+                           const double* still_score, int n_labels, float* cam_hist, int hw, int hh)
+{
+    orc_floor_hist_camera_cells(p, et, aabb, cam_center, Xs, xy, n, labels, lw, lh, still_score, n_labels, cam_hist, hw, hh, 0.25f, NULL);
 }
 
 /* floor-histogram.cpp:296-300: hist = sum over cameras in camera order (float adds). */

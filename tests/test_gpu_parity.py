@@ -2,6 +2,7 @@
 
 Bit-exact for integer/byte/index results; point coordinates within 1e-4 relative (north_star)."""
 import ctypes
+import ctypes as C
 
 import numpy as np
 import pytest
@@ -392,3 +393,50 @@ def test_frame_batch_with_mixed_sensor_sizes_and_blur(ctx):
     d2 = api.make_frame_desc(cams[2], sp, hp, synth.HIST_AABB)
     api.frame_run(ctx, 30, d2)
     assert not np.array_equal(api.frame_fetch(ctx, 30, W, H, res[0].hw, res[0].hh)["disp"], single[2]["disp"])
+
+
+def test_super_pixel_table_and_ordered_histogram(ctx):
+    """camera_info[cam].slic_to_hist_xy (floor-histogram.cpp:222-225,269-286) and the order-preserving histogram, through
+    the host entry point and through the frame path, bit for bit against the sequential CPU restatement."""
+    W, H, D = 384, 240, 64
+    cam = synth.make_camera(W, H, D, config=2, cam=2, n_cams=4)
+    sp = _sp(D, 1)
+    rng = np.random.default_rng(11)
+    # super-pixels of very different sizes: 8x8 cells (few points: finite sums) next to 64x64 cells (the doubling fourth
+    # component overflows to inf, as it does in the reference), some unlabelled pixels, some labels beyond the table
+    lab = np.where(np.arange(W)[None, :] < W // 2, (np.arange(H)[:, None] // 8) * 100 + np.arange(W)[None, :] // 8,
+                   3000 + (np.arange(H)[:, None] // 64) * 10 + np.arange(W)[None, :] // 64).astype(np.int32)
+    lab[rng.random((H, W)) < 0.02] = -1
+    lab[5:9, 7:30] = 99999
+    lab = np.ascontiguousarray(lab)
+    n_labels = 3100
+    still = rng.uniform(0.0, 1.0, n_labels)
+    for weighting, use_still in [(api.WGT_NORM, True), (api.WGT_NONE, False), (api.WGT_QUADRANCE, True)]:
+        hp = api.FloorHistogramParams(weighting=weighting, apply_slic_still_weights=use_still, ordered=True)
+        desc = api.make_frame_desc(cam, sp, hp, synth.HIST_AABB, slic_lookup=lab, still_score=still)
+        res = api.frame_run(ctx, 0, desc)
+        out = api.frame_fetch_batch(ctx, 0, 1, W, H, res.hw, res.hh, n_labels=n_labels)[0]
+        ohp = oracle.HistParams(hp.hist_sz, hp.hist_min_z, hp.hist_max_z, weighting, int(use_still))
+        wh, wc = oracle.floor_hist_camera_cells(ohp, cam["et"], synth.HIST_AABB, cam["et"][:3], out["Xs"], out["xy"], lab, still)
+        assert np.array_equal(out["cam_hist"], wh) and wh.sum() > 100
+        got = out["slic_to_hist_xy"]
+        assert got.shape == wc.shape
+        assert np.array_equal(got[:, :2], wc[:, :2])
+        assert np.array_equal(got[:, 2], wc[:, 2])   # inf == inf
+        touched = wc[:, 0] >= 0
+        assert touched.sum() > 50 and np.isinf(wc[:, 2]).any() and np.isfinite(wc[touched, 2]).any()
+        assert (wc[~touched, 2] == 0).all()
+    # the host entry point gives the same table
+    pc = api.PointCloud()
+    pc.Xs, pc.xy = out["Xs"], out["xy"]
+    cells = (api._lib.SparseHistCell * n_labels)()
+    hist = np.empty((res.hh, res.hw), np.float32)
+    hpc = hp.to_c()
+    et = (C.c_double * 8)(*cam["et"])
+    ab = (C.c_double * 4)(*synth.HIST_AABB)
+    cc = (C.c_double * 3)(*cam["et"][:3])
+    ctx.check(ctx.lib.mvs_floor_hist_camera_cells(ctx.h, C.byref(hpc), et, ab, cc, out["Xs"].ctypes.data, out["xy"].ctypes.data, out["N"],
+                                                  lab.ctypes.data, W, H, still.ctypes.data, n_labels, hist.ctypes.data, res.hw, res.hh,
+                                                  cells), "mvs_floor_hist_camera_cells")
+    assert np.array_equal(hist, wh)
+    assert np.array_equal(np.array([(c.x, c.y, c.count) for c in cells], np.float64), wc)

@@ -65,6 +65,14 @@ int mvs_remap_bgr8(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, size_t sste
                    const float* mapy, size_t mstep, int w, int h, int interp, const uint8_t border_bgr[3],
                    uint8_t* dst, size_t dstep);
 
+/* The per-video half of get_xy_mapping (pipeline/nodes/get_xy_mapping.cpp:59, utils/create-cv-remap.cpp:10-68
+ * produce mapx / mapy once per video): register a sensor's maps once and the INTER_CUBIC remap of the frame path reads
+ * 6 bytes per pixel of precomputed fixed-point coordinates instead of converting 8 bytes of float maps in every frame.
+ * mapx / mapy: CV_32FC1 w x h, byte step mstep, host (on_device = 0) or device pointers; they are not needed after the
+ * call.  *handle (> 0) goes into mvs_frame_desc.maps_handle[i].  Results are identical (the same conversion, done once). */
+int mvs_maps_register(mvs_ctx* ctx, const float* mapx, const float* mapy, size_t mstep, int w, int h, int on_device, int* handle);
+int mvs_maps_release(mvs_ctx* ctx, int handle);
+
 /* -- a2: grey + pre-smoothing ----------------------------------------------------------------------
  * Replaces the prologue of Disparity::calculate, cost-functions/disparity/disparity.cpp:106-155:
  * cv::cvtColor(BGR2GRAY) when channels == 3, then cv::GaussianBlur(31x31, sigma) applied TWICE when
@@ -274,6 +282,8 @@ typedef struct {
     const double* still_score;
     int n_labels;
     int labels_on_device; /* labels and still_score: 0 = host pointers (copied in), 1 = device pointers */
+    int maps_handle[2];   /* > 0: the sensor's maps were registered with mvs_maps_register; mapx / mapy of that sensor are
+                             then ignored (may be NULL).  Used with interp = MVS_INTER_CUBIC, w x h must match. */
 } mvs_frame_desc;
 
 /* Device-side results of the last mvs_frame_run on this context slot (valid until the next run on it). */

@@ -44,7 +44,7 @@ class FrameDesc(C.Structure):
                 ("sgbm", SgbmParams), ("presmooth_sigma", c_double), ("bcam", Bcam), ("hist", HistParams),
                 ("et", c_double * 8), ("aabb", c_double * 4), ("cam_center", c_double * 3),
                 ("interp", c_int), ("left_is_ref", c_int), ("labels", c_void_p), ("lstep", c_size_t), ("still_score", c_void_p),
-                ("n_labels", c_int), ("labels_on_device", c_int)]
+                ("n_labels", c_int), ("labels_on_device", c_int), ("maps_handle", c_int * 2)]
 
 
 class FetchDesc(C.Structure):
@@ -70,6 +70,8 @@ SIGNATURES = {
     "mvs_launch_count": (C.c_longlong, [c_void_p]),
     "mvs_remap_bgr8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p, c_void_p, c_size_t, c_int, c_int,
                                c_int, c_void_p, c_void_p, c_size_t]),
+    "mvs_maps_register": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, C.POINTER(c_int)]),
+    "mvs_maps_release": (c_int, [c_void_p, c_int]),
     "mvs_presmooth": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_size_t, c_double, c_void_p, c_size_t]),
     "mvs_sgbm_check": (c_int, [C.POINTER(SgbmParams), c_int, c_int]),
     "mvs_sgbm_compute16": (c_int, [c_void_p, C.POINTER(SgbmParams), c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p,

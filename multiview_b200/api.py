@@ -437,6 +437,16 @@ def make_frame_desc(cam: dict, sgbm: StereoSGBMParams, hist: FloorHistogramParam
     return d
 
 
+def maps_register(ctx: Context, mapx, mapy) -> int:
+    """mvs_maps_register: the per-video conversion of a sensor's rectification maps (get_xy_mapping's result) into the
+    fixed-point form the cubic remap reads; returns the handle for FrameDesc.maps_handle[i]."""
+    mapx, mapy = np.ascontiguousarray(mapx, np.float32), np.ascontiguousarray(mapy, np.float32)
+    h, w = mapx.shape
+    handle = C.c_int(0)
+    ctx.check(ctx.lib.mvs_maps_register(ctx.h, _vp(mapx), _vp(mapy), w * 4, w, h, 0, C.byref(handle)), "mvs_maps_register")
+    return handle.value
+
+
 def frame_run(ctx: Context, slot: int, desc: FrameDesc) -> FrameResult:
     res = FrameResult()
     ctx.check(ctx.lib.mvs_frame_run(ctx.h, slot, C.byref(desc), C.byref(res)), "mvs_frame_run")

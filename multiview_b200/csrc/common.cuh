@@ -33,8 +33,15 @@ struct FrameSlot {
     bool valid = false;
 };
 
+// maps of a camera sensor in the packed fixed-point form of the cubic remap (mvs_maps_register)
+struct RegisteredMaps {
+    void* packed = nullptr;   // [h][w] uint32 {X | Y << 16}, then [h][w] uint16 weight-table index
+    int w = 0, h = 0;
+};
+
 struct mvs_ctx {
     int device = 0;
+    std::vector<RegisteredMaps> maps;
     cudaStream_t stream = nullptr;
     // Host<->device copies of the frame path run on their own stream so that the upload of the next batch and the
     // download of the previous one overlap the kernels of the current one (ordered by the events below).

@@ -116,6 +116,8 @@ extern "C" void mvs_ctx_destroy(mvs_ctx* ctx)
     if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
     for (auto& kv : ctx->arena.bufs)
         if (kv.second.p) cudaFree(kv.second.p);
+    for (auto& m : ctx->maps)
+        if (m.packed) cudaFree(m.packed);
     for (auto& kv : ctx->timers) {
         if (kv.second.beg) cudaEventDestroy(kv.second.beg);
         if (kv.second.end) cudaEventDestroy(kv.second.end);

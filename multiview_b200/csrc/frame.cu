@@ -37,9 +37,17 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     const mvs_frame_desc& d0 = descs[0];
     for (int f = 0; f < n_frames; ++f) {
         const mvs_frame_desc* d = descs + f;
-        if (d->w <= 0 || d->h <= 0 || d->sw <= 0 || d->sh <= 0 || !d->sensor[0] || !d->sensor[1] || !d->mapx[0] || !d->mapx[1] ||
-            !d->mapy[0] || !d->mapy[1])
+        if (d->w <= 0 || d->h <= 0 || d->sw <= 0 || d->sh <= 0 || !d->sensor[0] || !d->sensor[1])
             return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d: bad argument", f);
+        for (int i = 0; i < 2; ++i) {
+            const int mh = d->maps_handle[i];
+            if (mh > 0) {   // registered maps: cubic only, same output size
+                if (mh > (int)ctx->maps.size() || !ctx->maps[mh - 1].packed || ctx->maps[mh - 1].w != d->w || ctx->maps[mh - 1].h != d->h ||
+                    d->interp != MVS_INTER_CUBIC)
+                    return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d: maps_handle[%d] unknown, of another size, or interp is not cubic", f, i);
+            } else if (!d->mapx[i] || !d->mapy[i])
+                return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d: no maps for sensor %d", f, i);
+        }
         if (d->w != d0.w || d->h != d0.h || memcmp(&d->sgbm, &d0.sgbm, sizeof(mvs_sgbm_params)) || d->hist.hist_sz != d0.hist.hist_sz ||
             memcmp(d->aabb, d0.aabb, sizeof(d0.aabb)))
             return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d differs in size, SGBM parameters or histogram bounds", f);
@@ -71,7 +79,8 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
         // the label image feeds the still weights (when enabled) and, always, the super-pixel table
         const bool use_labels = d->labels && d->n_labels > 0 && (!d->hist.use_still || d->still_score);
         if (use_labels && d->lstep < (size_t)d->w * 4) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_frame_run_batch: frame %d: lstep too small", f);
-        if ((!d->inputs_on_device || !d->maps_on_device || (use_labels && !d->labels_on_device))) {
+        const bool maps_up = !d->maps_on_device && (d->maps_handle[0] <= 0 || d->maps_handle[1] <= 0);
+        if ((!d->inputs_on_device || maps_up || (use_labels && !d->labels_on_device))) {
             any_upload = true;
             // the slot's input buffers may still be read by the kernels of the previous frame that used this slot
             if (ctx->slot_done_recorded[slot]) MVS_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_slot_done[slot], 0));
@@ -85,7 +94,9 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
                 MVS_CUDA(ctx, cudaMemcpy2DAsync(ds, (size_t)d->sw * 3, d->sensor[i], d->sstep, (size_t)d->sw * 3, d->sh, cudaMemcpyHostToDevice, cs));
                 sensor[f][i] = ds;
             }
-            if (d->maps_on_device) {
+            if (d->maps_handle[i] > 0) {   // packed form: the remap kernel takes it through mapx with mapy == nullptr
+                mapx[f][i] = (const float*)ctx->maps[d->maps_handle[i] - 1].packed; mapy[f][i] = nullptr;
+            } else if (d->maps_on_device) {
                 mapx[f][i] = d->mapx[i]; mapy[f][i] = d->mapy[i];
             } else {
                 float* dx = (float*)arena_get(ctx, slot_name(slot, i ? "mapx1" : "mapx0").c_str(), n * 4);

@@ -162,11 +162,23 @@ remap_cubic_bgr8_body(const uint8_t* __restrict__ src, int sw, int sh, size_t ss
 {
     int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x >= w || y >= h) return;
-    float mx = *(const float*)((const char*)mapx + (size_t)y * mstep + (size_t)x * 4);
-    float my = *(const float*)((const char*)mapy + (size_t)y * mstep + (size_t)x * 4);
-    int sx = cv_round_f(mx * 32.0f), sy = cv_round_f(my * 32.0f);
-    int X = sat16_i(sx >> 5) - 1, Y = sat16_i(sy >> 5) - 1;
-    const int4* wp = (const int4*)(tab + (size_t)(((sy & 31) << 5) + (sx & 31)) * 16);
+    int X, Y, widx;
+    if (mapy) {
+        float mx = *(const float*)((const char*)mapx + (size_t)y * mstep + (size_t)x * 4);
+        float my = *(const float*)((const char*)mapy + (size_t)y * mstep + (size_t)x * 4);
+        int sx = cv_round_f(mx * 32.0f), sy = cv_round_f(my * 32.0f);
+        X = sat16_i(sx >> 5) - 1; Y = sat16_i(sy >> 5) - 1;
+        widx = ((sy & 31) << 5) + (sx & 31);
+    } else {
+        // registered maps (mvs_maps_register): mapx points at the packed form, [h][w] uint32 {X | Y << 16} followed by
+        // [h][w] uint16 weight-table indices: 6 bytes per pixel instead of 8, and no float -> fixed conversion per frame
+        const uint32_t* pxy = (const uint32_t*)mapx;
+        const uint16_t* pfr = (const uint16_t*)(pxy + (size_t)w * h);
+        const uint32_t v = __ldg(pxy + (size_t)y * w + x);
+        X = (int)(int16_t)(v & 0xffffu) - 1; Y = (int)(int16_t)(v >> 16) - 1;
+        widx = __ldg(pfr + (size_t)y * w + x);
+    }
+    const int4* wp = (const int4*)(tab + (size_t)widx * 16);
     int4 wa = __ldg(wp), wb = __ldg(wp + 1);
     int wraw[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
     int s0 = 0, s1 = 0, s2 = 0;
@@ -391,5 +403,64 @@ extern "C" int mvs_remap_bgr8(mvs_ctx* ctx, const uint8_t* src, int sw, int sh, 
     if (rc) return rc;
     MVS_CUDA(ctx, cudaMemcpy2DAsync(dst, dstep, ddst, (size_t)w * 3, (size_t)w * 3, h, cudaMemcpyDeviceToHost, s));
     MVS_CUDA(ctx, cudaStreamSynchronize(s));
+    return MVS_OK;
+}
+
+// ---- f1: the per-video half of get_xy_mapping / create_cv_remap that needs no distortion model --------
+// The maps a camera's get_xy_mapping task produces once per video (pipeline/nodes/get_xy_mapping.cpp:59,
+// utils/create-cv-remap.cpp:10-68) are converted once into what the cubic remap derives from them for every pixel of
+// every frame: the integer source corner saturate_cast<short>(cvRound(map * 32) >> 5) per axis and the index of the Q15
+// weight table (the two 5-bit fractions).  Bit-exact by construction (the same operations, done earlier).
+__global__ void maps_pack_kernel(const float* __restrict__ mapx, const float* __restrict__ mapy, size_t mstep, int w, int h,
+                                 uint32_t* __restrict__ pxy, uint16_t* __restrict__ pfr)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= w) return;
+    float mx = *(const float*)((const char*)mapx + (size_t)y * mstep + (size_t)x * 4);
+    float my = *(const float*)((const char*)mapy + (size_t)y * mstep + (size_t)x * 4);
+    int sx = cv_round_f(mx * 32.0f), sy = cv_round_f(my * 32.0f);
+    pxy[(size_t)y * w + x] = ((uint32_t)sat16_i(sx >> 5) & 0xffffu) | ((uint32_t)sat16_i(sy >> 5) << 16);
+    pfr[(size_t)y * w + x] = (uint16_t)(((sy & 31) << 5) + (sx & 31));
+}
+
+extern "C" int mvs_maps_register(mvs_ctx* ctx, const float* mapx, const float* mapy, size_t mstep, int w, int h, int on_device,
+                                 int* handle)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (!mapx || !mapy || !handle || w <= 0 || h <= 0 || mstep < (size_t)w * 4) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_maps_register: bad argument");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    const float *dx = mapx, *dy = mapy;
+    size_t dstep = mstep;
+    if (!on_device) {
+        float* tx = (float*)arena_get(ctx, "maps.reg.x", (size_t)w * h * 4);
+        float* ty = (float*)arena_get(ctx, "maps.reg.y", (size_t)w * h * 4);
+        if (!tx || !ty) return MVS_ERR_NOMEM;
+        MVS_CUDA(ctx, cudaMemcpy2DAsync(tx, (size_t)w * 4, mapx, mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+        MVS_CUDA(ctx, cudaMemcpy2DAsync(ty, (size_t)w * 4, mapy, mstep, (size_t)w * 4, h, cudaMemcpyHostToDevice, s));
+        dx = tx; dy = ty; dstep = (size_t)w * 4;
+    }
+    int id = 0;
+    for (; id < (int)ctx->maps.size(); ++id)
+        if (!ctx->maps[id].packed) break;
+    if (id == (int)ctx->maps.size()) ctx->maps.push_back(RegisteredMaps());
+    void* p = nullptr;
+    if (cudaMalloc(&p, (size_t)w * h * 6) != cudaSuccess) return mvs_fail(ctx, MVS_ERR_NOMEM, "mvs_maps_register: cudaMalloc(%zu) failed", (size_t)w * h * 6);
+    ctx->maps[id].packed = p; ctx->maps[id].w = w; ctx->maps[id].h = h;
+    maps_pack_kernel<<<dim3(cdiv(w, 256), h), 256, 0, s>>>(dx, dy, dstep, w, h, (uint32_t*)p, (uint16_t*)((uint32_t*)p + (size_t)w * h));
+    MVS_LAUNCH_CHECK(ctx, "maps_pack_kernel");
+    MVS_CUDA(ctx, cudaStreamSynchronize(s));   // the caller may free its maps on return
+    *handle = id + 1;
+    return MVS_OK;
+}
+
+extern "C" int mvs_maps_release(mvs_ctx* ctx, int handle)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    if (handle < 1 || handle > (int)ctx->maps.size() || !ctx->maps[handle - 1].packed) return mvs_fail(ctx, MVS_ERR_ARG, "mvs_maps_release: unknown handle");
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    mvs_sync(ctx);
+    cudaFree(ctx->maps[handle - 1].packed);
+    ctx->maps[handle - 1] = RegisteredMaps();
     return MVS_OK;
 }

@@ -440,3 +440,43 @@ def test_super_pixel_table_and_ordered_histogram(ctx):
                                                   cells), "mvs_floor_hist_camera_cells")
     assert np.array_equal(hist, wh)
     assert np.array_equal(np.array([(c.x, c.y, c.count) for c in cells], np.float64), wc)
+
+
+def test_registered_maps_give_the_same_frame(ctx):
+    """mvs_maps_register (the per-video half of get_xy_mapping): the frame path with registered maps is bit-identical."""
+    import torch
+
+    W, H, D = 384, 240, 64
+    cam = synth.make_camera(W, H, D, config=2, cam=3, n_cams=4)
+    sp = _sp(D, 1)
+    hp = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
+    plain = api.make_frame_desc(cam, sp, hp, synth.HIST_AABB)
+    res = api.frame_run(ctx, 0, plain)
+    a = api.frame_fetch(ctx, 0, W, H, res.hw, res.hh)
+    handles = [api.maps_register(ctx, cam["mapx"][i], cam["mapy"][i]) for i in range(2)]
+    assert handles[0] > 0 and handles[1] > 0 and handles[0] != handles[1]
+    reg = api.make_frame_desc(cam, sp, hp, synth.HIST_AABB)
+    for i in range(2):
+        reg.maps_handle[i] = handles[i]
+        reg.mapx[i] = reg.mapy[i] = None
+    res2 = api.frame_run(ctx, 1, reg)
+    b = api.frame_fetch(ctx, 1, W, H, res2.hw, res2.hh)
+    n = W * H * 3
+    dev = torch.device("cuda", ctx.device)
+    for i in range(2):   # the rectified images themselves
+        r0 = torch.as_tensor(bench_cai(res.rectified_dev[i], n), device=dev).cpu().numpy()
+        r1 = torch.as_tensor(bench_cai(res2.rectified_dev[i], n), device=dev).cpu().numpy()
+        assert np.array_equal(r0, r1)
+        assert np.array_equal(r0.reshape(H, W, 3), oracle.remap_cubic_bgr8(cam["sensor"][i], cam["mapx"][i], cam["mapy"][i]))
+    assert np.array_equal(a["disp"], b["disp"]) and a["N"] == b["N"] and np.array_equal(a["cam_hist"], b["cam_hist"])
+    # a handle of another size, or with another interpolation, is refused
+    reg.interp = api.INTER_LINEAR
+    assert ctx.lib.mvs_frame_run(ctx.h, 1, C.byref(reg), None) == -1
+    for hnd in handles:
+        assert ctx.lib.mvs_maps_release(ctx.h, hnd) == 0
+    assert ctx.lib.mvs_maps_release(ctx.h, handles[0]) == -1
+
+
+class bench_cai:
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"data": (int(ptr), False), "shape": (n,), "typestr": "|u1", "version": 2}

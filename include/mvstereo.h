@@ -95,6 +95,14 @@ typedef struct {
  * block^2 * (2*ftzero + 63) + P2 <= 32767 (16-bit costs cannot wrap), mode in {0, 1, 3}. */
 int mvs_sgbm_check(const mvs_sgbm_params* p, int w, int h);
 
+/* The reference pins OpenCV 4.4.0 (build/install-files/build-scripts/build-opencv.sh:29); the OpenCV importable where this
+ * library was validated is 4.13.0, whose path recurrence subtracts min(Lp) where older sources subtract min(Lp) + P2.
+ * subtract_p2 = 0 (default): the 4.13 form, bit-exact with cv2 4.13.  subtract_p2 = 1: the older form: every path cost is
+ * lower by P2, which changes only the uniqueness test; bit-exact with the CPU restatement built with
+ * -DORC_SGBM_SUBTRACT_P2 wherever no 16-bit cost sum saturates (a saturated sum makes the next synchronising call return
+ * MVS_ERR_UNSUPPORTED), and limited to directions * P2 <= 32767.  Applies to all later SGBM calls of the context. */
+int mvs_set_sgbm_recurrence(mvs_ctx* ctx, int subtract_p2);
+
 /* Replaces cv::StereoSGBM::compute(left, right, disp16S) as called from
  * StereoSGBMDisparity::calculate, strategies/stereosgbm_disp.cpp:121-125 (left is the reference image).
  * l, r: 8UC1 w x h; disp16: CV_16S w x h, Q4 fixed point, invalid = (min_disp - 1) * 16.  Bit-exact. */

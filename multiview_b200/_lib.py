@@ -74,6 +74,7 @@ SIGNATURES = {
     "mvs_maps_release": (c_int, [c_void_p, c_int]),
     "mvs_presmooth": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_size_t, c_double, c_void_p, c_size_t]),
     "mvs_sgbm_check": (c_int, [C.POINTER(SgbmParams), c_int, c_int]),
+    "mvs_set_sgbm_recurrence": (c_int, [c_void_p, c_int]),
     "mvs_sgbm_compute16": (c_int, [c_void_p, C.POINTER(SgbmParams), c_void_p, c_void_p, c_int, c_int, c_size_t, c_void_p,
                                    c_size_t]),
     "mvs_disparity_sgbm": (c_int, [c_void_p, C.POINTER(SgbmParams), c_double, c_void_p, c_void_p, c_int, c_int, c_int,

@@ -717,6 +717,18 @@ int sgbm_aggregate_wave_status(mvs_ctx* ctx, cudaStream_t stream)
     int h = 0;
     MVS_CUDA(ctx, cudaMemcpyAsync(&h, it->second.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(stream));
+    // the other flag of the chain: a saturated cost sum under the (min Lp + P2) form of the recurrence (wta_post.cu)
+    auto st = ctx->arena.bufs.find("sgbm.sat44");
+    if (st != ctx->arena.bufs.end() && st->second.p && ctx->sgbm_subtract_p2) {
+        int sat = 0;
+        MVS_CUDA(ctx, cudaMemcpyAsync(&sat, st->second.p, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        MVS_CUDA(ctx, cudaStreamSynchronize(stream));
+        if (sat) {
+            cudaMemsetAsync(st->second.p, 0, sizeof(int), stream);
+            return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "SGBM: a cost sum saturated; under the (min Lp + P2) form of the recurrence the result is "
+                                                      "not guaranteed to equal OpenCV's there (it is exact wherever nothing saturates)");
+        }
+    }
     if (h) {
         cudaMemsetAsync(it->second.p, 0, sizeof(int), stream);
         return mvs_fail(ctx, MVS_ERR_CUDA, "aggregation: a bounded wait expired (results invalid; kind %d, ring row %d, band %d, pixel %d)",
@@ -735,5 +747,20 @@ extern "C" int mvs_test_raise_wave_error(mvs_ctx* ctx, int code)
     ctx->wave_err_cleared = true;
     MVS_CUDA(ctx, cudaMemcpyAsync(err, &code, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
     MVS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MVS_OK;
+}
+
+// Which form of the path recurrence the SGBM chain reproduces: 0 = L = C + min(..) - min Lp, what the
+// OpenCV importable here (4.13) computes and the default; 1 = L = C + min(..) - (min Lp + P2), the form of older OpenCV
+// sources.  The second equals the first shifted by P2 per direction, so the sweeps are shared and only the uniqueness
+// test of the winner-take-all step differs; it is exact wherever no cost sum saturates, and a saturated sum is reported
+// (MVS_ERR_UNSUPPORTED from the next synchronising call) instead of being guessed around.
+extern "C" int mvs_set_sgbm_recurrence(mvs_ctx* ctx, int subtract_p2)
+{
+    if (!ctx) return MVS_ERR_ARG;
+    MVS_CUDA(ctx, cudaSetDevice(ctx->device));
+    MVS_ARENA(ctx, int, sat, "sgbm.sat44", 1);
+    MVS_CUDA(ctx, cudaMemsetAsync(sat, 0, sizeof(int), ctx->stream));
+    ctx->sgbm_subtract_p2 = subtract_p2 != 0;
     return MVS_OK;
 }

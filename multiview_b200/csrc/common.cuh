@@ -67,6 +67,8 @@ struct mvs_ctx {
     int16_t* interp_tab_dev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // by cv::INTER_* value: 32*32*K*K Q15 weights
     int sm_count = 148;
     bool wave_err_cleared = false;
+    bool sgbm_subtract_p2 = false;   // mvs_set_sgbm_recurrence
+    bool sat44_cleared = false;
     long long launches = 0;  // kernels launched through this context (bench.py reports it)
 };
 
@@ -128,6 +130,7 @@ struct SgbmGeom {
     int Dp;  // disparities per pixel in the device volumes (D rounded up to a multiple of 64)
     int SW2, SH2, ftzero, P1, P2, ur, d12, INV;
     int mode;
+    int K44;  // 0: OpenCV 4.13's recurrence (minus min Lp); directions * P2: the older form (minus (min Lp + P2)), see mvs_set_sgbm_recurrence
     size_t cells() const { return (size_t)H * W1 * Dp; }
 };
 int sgbm_geom(mvs_ctx* ctx, const mvs_sgbm_params* p, int w, int h, SgbmGeom* g);

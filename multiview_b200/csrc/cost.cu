@@ -46,6 +46,14 @@ int sgbm_geom(mvs_ctx* ctx, const mvs_sgbm_params* p, int w, int h, SgbmGeom* g)
     g->d12 = p->disp12_max_diff > 0 ? p->disp12_max_diff : 1;
     g->INV = (p->min_disp - 1) * 16;
     g->mode = p->mode;
+    g->K44 = 0;
+    if (ctx && ctx->sgbm_subtract_p2) {
+        const int dirs = p->mode == MVS_MODE_HH ? 8 : p->mode == MVS_MODE_SGBM ? 5 : 4;
+        g->K44 = dirs * g->P2;
+        // S' = S - K44 must stay above the lower end of a 16-bit cost
+        if (g->K44 > 32767)
+            return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "SGBM: the (min Lp + P2) form of the recurrence supports directions * P2 <= 32767 (here %d)", g->K44);
+    }
     return MVS_OK;
 }
 

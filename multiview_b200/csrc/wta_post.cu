@@ -11,7 +11,8 @@
 // ur_magic = ceil(2^32 / (100 - ur)) (0 when the divisor is 1): n / (100 - ur) == umulhi(n, ur_magic) for n < 2^25
 template <int NW>
 __global__ void __launch_bounds__(256)
-wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key)
+wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key,
+           int* __restrict__ sat_flag)
 {
     __shared__ __align__(16) uint32_t sh[8][NW * 32];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -59,7 +60,21 @@ wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_
         }
         key = __reduce_min_sync(0xffffffffu, key);
         const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
-        if (minS >= 32767) continue;  // every cost saturated: the reference leaves / writes INV here
+        // "minus (min Lp + P2)" form of the recurrence (g.K44 = directions * P2): S here is that form's S plus K44 wherever
+        // no sum saturated.  A saturated sum (32767 here, at least 32767 - K44 there) only matters where it takes part in a
+        // decision: as the minimum, as a neighbour of the minimum in the sub-pixel fit, or when the uniqueness threshold
+        // reaches it.  Those cases are reported (sat_flag), never guessed around; everywhere else the result is exact.
+        bool satp = false;
+        if (g.K44) {
+            uint32_t mx = 0;
+#pragma unroll
+            for (int j = 0; j < NW; ++j) mx = __vmaxu2(mx, w[j] & ~padbits[j]);
+            satp = __reduce_max_sync(0xffffffffu, max(mx & 0xffffu, mx >> 16)) >= 32767u;
+        }
+        if (minS >= 32767) {   // every cost saturated: the reference leaves / writes INV here
+            if (g.K44 && lane == 0) *sat_flag = 1;
+            continue;
+        }
         __syncwarp();
         // uniqueness: reject if some d outside best-1..best+1 has S*(100-ur) < minS*100, i.e. S <= thr.
         // Lane q reads the two neighbours it needs for the sub-pixel fit, blanks best-1..best+1 in the staged copy,
@@ -75,9 +90,13 @@ wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_
 #pragma unroll
         for (int j = 0; j < NW; ++j) m = __vminu2(m, mysh[lane * NW + j]);
         const uint32_t mn = __reduce_min_sync(0xffffffffu, min(m & 0xffffu, m >> 16));
-        const uint32_t num = (uint32_t)(minS * 100 - 1);
-        const uint32_t thr = minS > 0 ? (ur_magic ? __umulhi(num, ur_magic) : num) : 0xffffffffu;  // ur <= 99 (mvs_sgbm_check)
-        if (minS > 0 && mn != 0xffffu && mn <= thr) continue;
+        // S(d) * (100 - ur) < minS * 100 in the reference's own S; with S' = S - K44 (the other form of the recurrence,
+        // K44 = 0 for OpenCV 4.13's form) that is S(d) * (100 - ur) < minS * 100 - K44 * ur on the S held here
+        const int rhs = minS * 100 - g.K44 * g.ur;
+        const uint32_t num = (uint32_t)(rhs - 1);
+        const uint32_t thr = rhs > 0 ? (ur_magic ? __umulhi(num, ur_magic) : num) : 0xffffffffu;  // ur <= 99 (mvs_sgbm_check)
+        if (satp && lane == q && ((rhs > 0 && thr >= 32767u) || (best > 0 && sm >= 32767) || (best < g.D - 1 && sp >= 32767))) *sat_flag = 1;
+        if (rhs > 0 && mn != 0xffffu && mn <= thr) continue;
         if (lane == q) { my_best = best; my_minS = minS; my_sm = sm; my_sp = sp; }
     }
     if (lane < WTA_PPW && my_best >= 0) {
@@ -330,15 +349,16 @@ int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw
     cudaStream_t s = ctx->stream;
     size_t n = (size_t)g.W * g.H;
     MVS_ARENA(ctx, uint32_t, d2, "sgbm.disp2key", n);
+    MVS_ARENA(ctx, int, sat, "sgbm.sat44", 1);
     wta_init_kernel<<<cdiv(n, 256), 256, 0, s>>>(raw16, d2, n, g.INV);
     int blocks = cdiv((long long)g.W1 * g.H, 8 * WTA_PPW);
     const uint32_t udiv = (uint32_t)(100 - g.ur);
     const uint32_t ur_magic = udiv <= 1 ? 0u : (uint32_t)(((1ull << 32) + udiv - 1) / udiv);
     switch (g.Dp / 64) {
-    case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2); break;
-    case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2); break;
-    case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2); break;
-    case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2); break;
+    case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2, sat); break;
+    case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2, sat); break;
+    case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2, sat); break;
+    case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2, sat); break;
     default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
     }
     MVS_LAUNCH_CHECK_N(ctx, "wta_kernel", 2);
@@ -375,6 +395,7 @@ int sgbm_wta_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_para
     const size_t n = (size_t)g.W * g.H;
     MVS_ARENA(ctx, int16_t, raw, "sgbm.batch.raw", n * F);
     MVS_ARENA(ctx, uint32_t, d2, "sgbm.batch.disp2key", n * F);
+    MVS_ARENA(ctx, int, sat, "sgbm.sat44", 1);
     PostBatch b;
     memset(&b, 0, sizeof(b));
     for (int f = 0; f < F; ++f) b.disp16[f] = disp16[f];
@@ -387,10 +408,10 @@ int sgbm_wta_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_para
         int16_t* rf = raw + n * f;
         uint32_t* df = d2 + n * f;
         switch (g.Dp / 64) {
-        case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df); break;
-        case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df); break;
-        case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df); break;
-        case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df); break;
+        case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df, sat); break;
+        case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df, sat); break;
+        case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df, sat); break;
+        case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df, sat); break;
         default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
         }
         MVS_LAUNCH_CHECK(ctx, "wta_kernel");

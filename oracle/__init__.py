@@ -34,6 +34,22 @@ def build(force: bool = False) -> str:
     return _SO
 
 
+_lib44 = None
+
+
+def lib44():
+    """The oracle built with -DORC_SGBM_SUBTRACT_P2: the path recurrence of older OpenCV sources (the reference pins 4.4.0;
+    the form cv2 4.13 computes, and that lib() restates, subtracts min(Lp) only).  Not pinned by any runnable OpenCV here."""
+    global _lib44
+    if _lib44 is None:
+        so = os.path.join(_HERE, "libmvoracle44.so")
+        srcs = [os.path.join(_HERE, s) for s in _SRC]
+        if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+            subprocess.check_call(["make", "-s", "-B", "-C", _HERE, "libmvoracle44.so"])
+        _lib44 = ctypes.CDLL(so)
+    return _lib44
+
+
 _lib = None
 
 
@@ -79,8 +95,9 @@ def sgbm_dims(p: SgbmParams, W: int):
     return bool(ok), mn.value, w1.value
 
 
-def sgbm_compute(p: SgbmParams, L: np.ndarray, R: np.ndarray, taps: bool = False):
-    """StereoSGBM::compute restatement.  Returns disp16 (H,W) int16, or a dict with taps."""
+def sgbm_compute(p: SgbmParams, L: np.ndarray, R: np.ndarray, taps: bool = False, subtract_p2: bool = False):
+    """StereoSGBM::compute restatement.  Returns disp16 (H,W) int16, or a dict with taps.  subtract_p2 selects the build
+    with the older form of the path recurrence (lib44)."""
     L = np.ascontiguousarray(L, np.uint8)
     R = np.ascontiguousarray(R, np.uint8)
     H, W = L.shape
@@ -94,7 +111,7 @@ def sgbm_compute(p: SgbmParams, L: np.ndarray, R: np.ndarray, taps: bool = False
         S1 = np.empty_like(C)
         S = np.empty_like(C)
         raw = np.empty((H, W), np.int16)
-    rc = lib().orc_sgbm_compute(ctypes.byref(p), _p(L), _p(R), W, H, _sz(W), _p(disp), _p(C), _p(S1), _p(S), _p(raw))
+    rc = (lib44() if subtract_p2 else lib()).orc_sgbm_compute(ctypes.byref(p), _p(L), _p(R), W, H, _sz(W), _p(disp), _p(C), _p(S1), _p(S), _p(raw))
     if rc:
         raise RuntimeError(f"orc_sgbm_compute rc={rc}")
     if taps:

@@ -480,3 +480,47 @@ def test_registered_maps_give_the_same_frame(ctx):
 class bench_cai:
     def __init__(self, ptr, n):
         self.__cuda_array_interface__ = {"data": (int(ptr), False), "shape": (n,), "typestr": "|u1", "version": 2}
+
+
+@pytest.mark.parametrize("params", [
+    dict(block=3, p1=8, p2=32, ur=0, d12=1, sw=0, sr=0),
+    dict(block=5, p1=8, p2=32, ur=10, d12=2, sw=0, sr=0),
+    dict(block=9, p1=22, p2=1000, ur=3, d12=596, sw=0, sr=0),
+    dict(block=13, p1=22, p2=1000, ur=25, d12=1, sw=50, sr=2),
+    dict(block=11, p1=22, p2=4000, ur=3, d12=596, sw=0, sr=0),
+    dict(block=5, p1=10, p2=120, ur=5, d12=1, sw=20, sr=1, minD=3),
+    dict(block=7, p1=0, p2=0, ur=-1, d12=0, sw=100, sr=1, cap=10),
+])
+def test_sgbm_older_recurrence_form(ctx, params):
+    """mvs_set_sgbm_recurrence(1): L = C + min(..) - (min Lp + P2), the form of older OpenCV sources (the reference pins
+    4.4.0), against the restatement built with -DORC_SGBM_SUBTRACT_P2 (not pinned by a runnable OpenCV: cv2 here is 4.13)."""
+    differs = exact = 0
+    try:
+        assert ctx.lib.mvs_set_sgbm_recurrence(ctx.h, 1) == 0
+        for mode in (1, 0, 3):
+            L, R = _pair(160, 56, 32, 5 + mode, False)
+            sp = _sp(32, mode, **params)
+            want = oracle.sgbm_compute(_op(sp), L, R, subtract_p2=True)
+            got = np.empty((56, 160), np.int16)
+            rc = ctx.lib.mvs_sgbm_compute16(ctx.h, ctypes.byref(sp.to_c()), L.ctypes.data, R.ctypes.data, 160, 56, 160, got.ctypes.data, 320)
+            if rc == -3 and b"saturated" in ctx.lib.mvs_last_error(ctx.h):
+                continue   # a saturated sum took part in a decision (large blocks): reported, no result claimed
+            assert rc == 0
+            exact += 1
+            assert np.array_equal(got, want), f"mode {mode}: {(got != want).sum()} px differ"
+            differs += int((want != oracle.sgbm_compute(_op(sp), L, R)).sum())
+        if params["block"] <= 9:
+            assert exact == 3
+        # an uncorrelated pair saturates cost sums: that is reported, not silently approximated
+        L, R = _pair(160, 56, 32, 9, True)
+        sp = _sp(32, 1, **params)
+        d16 = np.empty((56, 160), np.int16)
+        rc = ctx.lib.mvs_sgbm_compute16(ctx.h, ctypes.byref(sp.to_c()), L.ctypes.data, R.ctypes.data, 160, 56, 160, d16.ctypes.data, 320)
+        if rc == 0:
+            assert np.array_equal(d16, oracle.sgbm_compute(_op(sp), L, R, subtract_p2=True))
+        else:
+            assert rc == -3 and b"saturated" in ctx.lib.mvs_last_error(ctx.h)
+    finally:
+        assert ctx.lib.mvs_set_sgbm_recurrence(ctx.h, 0) == 0
+    if params["ur"] > 0 and exact:
+        assert differs > 0   # the two forms do disagree (uniqueness test) on these inputs: the switch is not a no-op

@@ -22,7 +22,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "libmvoracle.so")
-_SRC = ["sgbm_oracle.c", "image_oracle.c", "geom_oracle.c"]
+_SRC = ["sgbm_oracle.c", "image_oracle.c", "geom_oracle.c", "census_oracle.c"]
 
 
 def build(force: bool = False) -> str:
@@ -117,6 +117,21 @@ def sgbm_compute(p: SgbmParams, L: np.ndarray, R: np.ndarray, taps: bool = False
     if taps:
         return {"disp": disp, "C": C, "S1": S1, "S": S, "raw": raw, "minX1": minx1, "W1": w1}
     return disp
+
+
+def census_sgm(left: np.ndarray, right: np.ndarray, disparity_size: int = 256, taps: bool = False):
+    """The reference's CUDA_SGM strategy (sgm_disp.cpp:102-211 over the vendored libSGM kernels), restated; PARITY UNPINNED
+    (see census_oracle.c).  left / right: uint8 or uint16 grey (H, W).  Returns the float disparity, or a dict with taps."""
+    assert left.dtype == right.dtype and left.dtype in (np.uint8, np.uint16) and left.shape == right.shape
+    left, right = np.ascontiguousarray(left), np.ascontiguousarray(right)
+    H, W = left.shape
+    out = np.empty((H, W), np.float32)
+    S = np.empty((H, W, disparity_size), np.uint16) if taps else None
+    d = np.empty((H, W), np.uint16) if taps else None
+    rc = lib().orc_census_sgm(_p(left), _p(right), 16 if left.dtype == np.uint16 else 8, W, H, disparity_size, _p(out), _p(S), _p(d))
+    if rc:
+        raise RuntimeError(f"orc_census_sgm rc={rc}")
+    return {"disp": out, "S": S, "disp16": d} if taps else out
 
 
 def disp_to_float(disp16: np.ndarray) -> np.ndarray:

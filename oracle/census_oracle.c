@@ -1,0 +1,180 @@
+/*
+ * CPU restatement of the reference's CUDA_SGM strategy (test infrastructure only; never part of the product).
+ *
+ * Call site: cost-functions/disparity/strategies/sgm_disp.cpp:102-211 (SGMDisparity::calculate: 8- or 16-bit grey pair
+ * in, sgm::StereoSGM(w, h, disparity_size, in_depth, out_depth).execute, then float out with values > 512 -> 0).
+ * Algorithm: the vendored libSGM sources, multiview/contrib/libSGM/src:
+ *   census.cu:27-152            9x7 census, 62-bit descriptor, border pixels (3 rows / 4 columns) not written
+ *   matching_cost.cu:32-169     cost(y,x,k) = popcll(L(y,x) ^ (x < k ? 0 : R(y,x-k))), 8 bit
+ *   scan_scost.cu:19-20,63-330  8 paths, P1 = 20, P2 = 100, L = C + min(Lp[d], Lp[d-1]+P1, Lp[d+1]+P1, minLp+P2) - minLp,
+ *                               paths start from L = 0 / min = 0, S = sum of the 8 path costs (no saturation needed)
+ *   winner_takes_all.cu:32-233  left and right winner, uniqueness 0.95 against the SECOND minimum, disparity + 1, 0 invalid
+ *   median_filter.cu:24-32      NPP 3x3 median with anchor (0, 0) on both disparity images
+ *   check_consistency.cu:20-35  left-right check (uses the +1 disparities as they are), source pixel 0 masks
+ *
+ * PARITY UNPINNED.  The vendored snapshot supports 64 / 128 disparities only while the reference calls it with 256
+ * through an un-vendored libSGM 2.x (run.sh:86,182-184), it cannot run without a GPU, and the reference holds no test
+ * vector for it.  Where the vendored kernels' behaviour is an artefact rather than an algorithm, this restatement takes
+ * the plain reading and says so:
+ *   - census descriptors of border pixels are never written there (uninitialised device memory): 0 here;
+ *   - at d = 0 and d = D-1 the vendored path step substitutes an in-range neighbour that comes from a lane shuffle not
+ *     wrapping (L[1] / L[D-2] in the 64 variant, L[3] / L[D-4] in the 128 variant, scan_scost.cu:81-82,158-159): no
+ *     neighbour (+infinity) here, the textbook recurrence;
+ *   - the launch grids there drop up to 15 rows / columns / diagonals when a size is not a multiple of 16
+ *     (scan_scost.cu:296-306): every path is run here;
+ *   - NPP's median reads past the right and bottom image edges (ROI = whole image, anchor (0,0)): replicated edge here.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define CEN_P1 20
+#define CEN_P2 100
+
+static uint32_t px(const void* img, int depth_bits, size_t i)
+{
+    return depth_bits == 16 ? ((const uint16_t*)img)[i] : ((const uint8_t*)img)[i];
+}
+
+/* census.cu:27-152: bit = (centre > neighbour), rows above, left of centre, right of centre, rows below */
+static void census(const void* img, int depth_bits, int w, int h, uint64_t* out)
+{
+    memset(out, 0, sizeof(uint64_t) * (size_t)w * h);
+    for (int y = 3; y < h - 3; ++y)
+        for (int x = 4; x < w - 4; ++x) {
+            const uint32_t c = px(img, depth_bits, (size_t)y * w + x);
+            uint64_t v = 0;
+            for (int dy = -3; dy <= 3; ++dy)
+                for (int dx = -4; dx <= 4; ++dx) {
+                    if (dy == 0 && dx == 0) continue;
+                    v = (v << 1) | (uint64_t)(c > px(img, depth_bits, (size_t)(y + dy) * w + x + dx));
+                }
+            out[(size_t)y * w + x] = v;
+        }
+}
+
+static int popc64(uint64_t v) { return __builtin_popcountll(v); }
+
+/* one path step; Lp has D entries; returns min over d of the new L */
+static int path_step(const uint8_t* C, const uint16_t* Lp, int minLp, int D, uint16_t* Lo)
+{
+    int mn = 1 << 30;
+    for (int d = 0; d < D; ++d) {
+        int v = Lp[d];
+        if (d > 0 && Lp[d - 1] + CEN_P1 < v) v = Lp[d - 1] + CEN_P1;
+        if (d < D - 1 && Lp[d + 1] + CEN_P1 < v) v = Lp[d + 1] + CEN_P1;
+        if (minLp + CEN_P2 < v) v = minLp + CEN_P2;
+        const int L = C[d] + v - minLp;
+        Lo[d] = (uint16_t)L;
+        if (L < mn) mn = L;
+    }
+    return mn;
+}
+
+/* left + right winner of one row (winner_takes_all.cu): S row is [w][D] */
+static void wta_row(const uint16_t* S, int w, int D, uint16_t* dl, uint16_t* dr)
+{
+    const float uniq = 0.95f;
+    for (int x = 0; x < w; ++x) {
+        /* left: first minimum over all d; second minimum over d != d1 with x + d < w */
+        int c1 = 1 << 30, d1 = -1;
+        for (int d = 0; d < D; ++d) { int c = S[(size_t)x * D + d]; if (c < c1) { c1 = c; d1 = d; } }
+        int c2 = 0x7fff, d2 = -1;
+        for (int d = 0; d < D; ++d) {
+            if (d == d1 || x + d >= w) continue;
+            int c = S[(size_t)x * D + d];
+            if (d2 < 0 || c < c2) { c2 = c; d2 = d; }
+        }
+        if (d2 < 0) c2 = 0x7fff;
+        dl[x] = ((float)c2 * uniq < (float)c1 && abs(d1 - d2) > 1) ? 0 : (uint16_t)(d1 + 1);
+        /* right: candidates S(x + d, d) */
+        int rc1 = 1 << 30, rd1 = -1;
+        for (int d = 0; d < D && x + d < w; ++d) { int c = S[(size_t)(x + d) * D + d]; if (c < rc1) { rc1 = c; rd1 = d; } }
+        int rc2 = 0x7fff, rd2 = -1;
+        for (int d = 0; d < D && x + d < w; ++d) {
+            if (d == rd1) continue;
+            int c = S[(size_t)(x + d) * D + d];
+            if (rd2 < 0 || c < rc2) { rc2 = c; rd2 = d; }
+        }
+        if (rd2 < 0) rc2 = 0x7fff;
+        dr[x] = ((float)rc2 * uniq < (float)rc1 && abs(rd1 - rd2) > 1) ? 0 : (uint16_t)(rd1 + 1);
+    }
+}
+
+static int cmp_u16(const void* a, const void* b) { return (int)*(const uint16_t*)a - (int)*(const uint16_t*)b; }
+/* 3x3 median, window (x..x+2, y..y+2) (anchor (0,0)), replicated at the right / bottom edge */
+static void median3_anchor0(const uint16_t* src, int w, int h, uint16_t* dst)
+{
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            uint16_t v[9];
+            for (int j = 0; j < 3; ++j)
+                for (int i = 0; i < 3; ++i) {
+                    int yy = y + j < h ? y + j : h - 1, xx = x + i < w ? x + i : w - 1;
+                    v[j * 3 + i] = src[(size_t)yy * w + xx];
+                }
+            qsort(v, 9, sizeof(uint16_t), cmp_u16);
+            dst[(size_t)y * w + x] = v[4];
+        }
+}
+
+/* Returns 0 on success.  left/right: grey images (8 or 16 bit, packed w x h); out: float w x h.
+ * S_tap (optional): the aggregated volume [h][w][D] uint16; disp_tap (optional): uint16 disparity + 1 after the checks. */
+int orc_census_sgm(const void* left, const void* right, int depth_bits, int w, int h, int D, float* out, uint16_t* S_tap,
+                   uint16_t* disp_tap)
+{
+    if ((depth_bits != 8 && depth_bits != 16) || (D != 64 && D != 128 && D != 256) || w <= 8 || h <= 6 || (w & 1) || (h & 1)) return -1;
+    const size_t n = (size_t)w * h;
+    uint64_t* cl = (uint64_t*)malloc(n * 8);
+    uint64_t* cr = (uint64_t*)malloc(n * 8);
+    uint8_t* C = (uint8_t*)malloc(n * D);
+    uint16_t* S = (uint16_t*)calloc(n * D, 2);
+    uint16_t* Lbuf = (uint16_t*)malloc(sizeof(uint16_t) * 2 * D);
+    uint16_t *dl = (uint16_t*)malloc(n * 2), *dr = (uint16_t*)malloc(n * 2), *ml = (uint16_t*)malloc(n * 2), *mr = (uint16_t*)malloc(n * 2);
+    if (!cl || !cr || !C || !S || !Lbuf || !dl || !dr || !ml || !mr) return -2;
+    census(left, depth_bits, w, h, cl);
+    census(right, depth_bits, w, h, cr);
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x)
+            for (int k = 0; k < D; ++k)
+                C[((size_t)y * w + x) * D + k] = (uint8_t)popc64(cl[(size_t)y * w + x] ^ (x < k ? 0 : cr[(size_t)y * w + x - k]));
+    /* 8 paths: every pixel on the border from which (dx, dy) points inwards starts a path */
+    static const int dirs[8][2] = {{1, 0}, {-1, 0}, {0, 1}, {0, -1}, {1, 1}, {-1, 1}, {-1, -1}, {1, -1}};
+    for (int k = 0; k < 8; ++k) {
+        const int dx = dirs[k][0], dy = dirs[k][1];
+        for (int sy = 0; sy < h; ++sy)
+            for (int sx = 0; sx < w; ++sx) {
+                const int px_ = sx - dx, py_ = sy - dy;
+                if (px_ >= 0 && px_ < w && py_ >= 0 && py_ < h) continue;   /* has a predecessor: not a start */
+                uint16_t *Lp = Lbuf, *Ln = Lbuf + D;
+                memset(Lp, 0, sizeof(uint16_t) * D);
+                int minLp = 0;
+                for (int x = sx, y = sy; x >= 0 && x < w && y >= 0 && y < h; x += dx, y += dy) {
+                    const size_t o = ((size_t)y * w + x) * D;
+                    minLp = path_step(C + o, Lp, minLp, D, Ln);
+                    for (int d = 0; d < D; ++d) S[o + d] = (uint16_t)(S[o + d] + Ln[d]);
+                    uint16_t* t = Lp; Lp = Ln; Ln = t;
+                }
+            }
+    }
+    if (S_tap) memcpy(S_tap, S, n * D * 2);
+    for (int y = 0; y < h; ++y) wta_row(S + (size_t)y * w * D, w, D, dl + (size_t)y * w, dr + (size_t)y * w);
+    median3_anchor0(dl, w, h, ml);
+    median3_anchor0(dr, w, h, mr);
+    /* check_consistency.cu:20-35 */
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const size_t i = (size_t)y * w + x;
+            const int d = ml[i], k = x - d;
+            if (px(left, depth_bits, i) == 0 || d <= 0 || (k >= 0 && k < w && abs((int)mr[(size_t)y * w + k] - d) > 1)) ml[i] = 0;
+        }
+    if (disp_tap) memcpy(disp_tap, ml, n * 2);
+    /* sgm_disp.cpp:195-207: 16-bit output (disparity_size 256): |v| > 512 -> 0; 8-bit output: plain conversion */
+    for (size_t i = 0; i < n; ++i) {
+        float v = (float)(D == 256 ? ml[i] : (uint8_t)ml[i]);
+        out[i] = (D == 256 && v > 512.0f) ? 0.0f : v;
+    }
+    free(cl); free(cr); free(C); free(S); free(Lbuf); free(dl); free(dr); free(ml); free(mr);
+    return 0;
+}

@@ -116,6 +116,18 @@ int mvs_sgbm_compute16(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l,
 int mvs_disparity_sgbm(mvs_ctx* ctx, const mvs_sgbm_params* p, double presmooth_sigma, const uint8_t* l,
                        const uint8_t* r, int channels, int w, int h, size_t step, float* out, size_t ostep);
 
+/* -- a5: the CUDA_SGM strategy ---------------------------------------------------------------------------
+ * Replaces SGMDisparity::calculate(p, l_is_ref = true, image0, image1, out), strategies/sgm_disp.cpp:102-211, i.e. libSGM's
+ * sgm::StereoSGM(w, h, disparity_size, depth_bits, 8 | 16).execute plus the float conversion (:195-207): census 9x7,
+ * Hamming cost, 8 paths with P1 = 20 / P2 = 100, left / right winner with uniqueness 0.95, 3x3 median, left-right check;
+ * disparities are stored + 1, 0 = invalid, values > 512 -> 0.  l, r: grey images of depth_bits 8 or 16 (use_16bit_greyscale,
+ * sgm_disp.hpp:19-20), byte step `step`; disparity_size 64, 128 or 256; w and h even; out: CV_32FC1.  disp_tap (may be
+ * NULL): the 16-bit disparity image before the float conversion.  Parity UNPINNED: bit-exact with the CPU restatement of
+ * the vendored libSGM kernels (oracle/census_oracle.c, which lists where those kernels' artefacts are not reproduced); no
+ * runnable libSGM or test vector exists to pin it against. */
+int mvs_disparity_census(mvs_ctx* ctx, const void* l, const void* r, int depth_bits, int w, int h, size_t step,
+                         int disparity_size, float* out, size_t ostep, uint16_t* disp_tap);
+
 /* -- a8: merge with the scene's reference disparity ------------------------------------------------------
  * Replaces the loop of disp_map_update::Task::execute, pipeline/nodes/disp_map_update.cpp:98-113: in place,
  * disp[x] = ref[x] where ref[x] is finite, labels[x] >= 0 and (the super-pixel is not flagged still_cuttoff, or

@@ -79,6 +79,7 @@ SIGNATURES = {
                                    c_size_t]),
     "mvs_disparity_sgbm": (c_int, [c_void_p, C.POINTER(SgbmParams), c_double, c_void_p, c_void_p, c_int, c_int, c_int,
                                    c_size_t, c_void_p, c_size_t]),
+    "mvs_disparity_census": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_size_t, c_int, c_void_p, c_size_t, c_void_p]),
     "mvs_disp_merge_ref": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_size_t, c_void_p, c_int, c_int, c_int]),
     "mvs_point_cloud": (c_int, [c_void_p, C.POINTER(Bcam), c_void_p, c_size_t, c_int, c_int, c_int, c_void_p, c_void_p,
                                 c_void_p, C.POINTER(C.c_int32), c_void_p]),

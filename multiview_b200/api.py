@@ -208,6 +208,26 @@ class Disparity:
         return Disparity._run(p.stereosgbm_params, p.presmooth_sigma, image0, image1, ctx)
 
 
+class SGMDisparity:
+    """strategies/sgm_disp.hpp:13-35: the CUDA_SGM strategy (libSGM: census + Hamming semi-global matching)."""
+
+    @staticmethod
+    def calculate(disparity_size: int, l_is_ref_image: bool, image0, image1, ctx: Context | None = None, tap: bool = False):
+        if not l_is_ref_image:
+            raise MvsError("SGMDisparity: the pipeline only calls this with the left image as reference")
+        ctx = ctx or default_context()
+        image0, image1 = np.ascontiguousarray(image0), np.ascontiguousarray(image1)
+        if image0.dtype != image1.dtype or image0.dtype not in (np.uint8, np.uint16) or image0.ndim != 2 or image0.shape != image1.shape:
+            raise MvsError("expected a pair of 8-bit or 16-bit greyscale images of equal size")   # sgm_disp.cpp:122-132
+        h, w = image0.shape
+        bpp = image0.dtype.itemsize
+        out = np.empty((h, w), np.float32)
+        d16 = np.empty((h, w), np.uint16) if tap else None
+        ctx.check(ctx.lib.mvs_disparity_census(ctx.h, _vp(image0), _vp(image1), 8 * bpp, w, h, w * bpp, int(disparity_size), _vp(out), w * 4,
+                                               _vp(d16)), "mvs_disparity_census")
+        return (out, d16) if tap else out
+
+
 def presmooth(image, sigma=2.15, ctx: Context | None = None):
     """The prologue of Disparity::calculate alone (grey + double blur), for stage-level tests."""
     ctx = ctx or default_context()

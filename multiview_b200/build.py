@@ -26,6 +26,7 @@ UNITS = {
     # tuning experiments: MVS_WAVE_FLAGS="-DWAVE_R=15 -DWAVE_D12=7" python -m multiview_b200.build --force
     "aggregate_wave.cu": os.environ.get("MVS_WAVE_FLAGS", "").split(),
     "wta_post.cu": [],
+    "census.cu": [],
     "sgbm.cu": [],
     "frame.cu": [],
     "cloud.cu": ["--fmad=false"],

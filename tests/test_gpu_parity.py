@@ -524,3 +524,19 @@ def test_sgbm_older_recurrence_form(ctx, params):
         assert ctx.lib.mvs_set_sgbm_recurrence(ctx.h, 0) == 0
     if params["ur"] > 0 and exact:
         assert differs > 0   # the two forms do disagree (uniqueness test) on these inputs: the switch is not a no-op
+
+
+@pytest.mark.parametrize("W,H,D,dtype", [(192, 96, 64, np.uint8), (320, 120, 128, np.uint16), (384, 130, 256, np.uint8),
+                                         (330, 98, 256, np.uint16)])
+def test_census_sgm_strategy(ctx, W, H, D, dtype):
+    """The CUDA_SGM strategy (sgm_disp.cpp:102-211 over libSGM's kernels) against its CPU restatement (parity unpinned)."""
+    l, r = synth.rectified_pair(W, H, min(D, 96), 31 + D)
+    gl, gr = oracle.bgr2gray(l), oracle.bgr2gray(r)
+    if dtype == np.uint16:
+        gl, gr = gl.astype(np.uint16) * 257, gr.astype(np.uint16) * 257
+    gl[5:9, 40:60] = 0   # source pixels that are 0 mask the output (check_consistency.cu:29-31)
+    want = oracle.census_sgm(gl, gr, D, taps=True)
+    got, d16 = api.SGMDisparity.calculate(D, True, gl, gr, ctx=ctx, tap=True)
+    assert np.array_equal(d16, want["disp16"]), f"{(d16 != want['disp16']).sum()} px differ"
+    assert np.array_equal(got, want["disp"])
+    assert (got[5:9, 40:60] == 0).all() and (got > 0).mean() > 0.5

@@ -100,6 +100,9 @@ struct WaveParams {
     int* error;            // set when a bounded wait expires
     int W1, H, D, P1, P2, nbands, F;
     uint32_t one;          // 1, opaque to the compiler (see WAVE_FMA_ADDS)
+#ifdef WAVE_DBG_PROF       // developer build: per-row clock counts {row total, waiting for the row above, waiting for the row below, slow paths}
+    unsigned long long* prof;
+#endif
 };
 
 __device__ __forceinline__ uint32_t wdup16(uint32_t v) { return v | (v << 16); }
@@ -458,6 +461,9 @@ wave_kernel(WaveParams p)
             // Barrier tests for the coming pixel are issued one pixel early (their ~90 cycles of latency overlap the
             // arithmetic); a direction that has nothing to wait for counts as passed.  Pixel 0 starts untested.
             early_set(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
+#ifdef WAVE_DBG_PROF
+            long long prof_t0 = clock64(), prof_full = 0, prof_cons = 0, prof_n = 0;
+#endif
 
             // The pixel loop is unrolled by UN = 4 (the prefetch depth; half the ring depth: the instruction footprint of
             // an unroll by eight does not fit the instruction cache).  Trip t covers pixels 4t .. 4t+3, which live in
@@ -492,7 +498,16 @@ wave_kernel(WaveParams p)
                         const uint32_t bf = k == 3 ? fullo : fullc + (k + 1) * 8u, pf = k == 3 ? par ^ h : par;
                         const uint32_t bc = WAR == 6 ? (k == 3 ? conso : consc + (k + 1) * 8u) : (k == 0 ? consc + 24u : conso + (k - 1) * 8u);
                         const uint32_t pc = WAR == 6 ? pf ^ 1u : (k == 0 ? par ^ 1u : par ^ h ^ 1u);
+#ifdef WAVE_DBG_PROF
+                        const long long w0 = clock64();
+                        const bool was_full = ok_full == 0u;
+#endif
                         wait_both(bf, pf, ok_full, bc, pc, ok_cons, x);
+#ifdef WAVE_DBG_PROF
+                        const long long w1 = clock64() - w0;
+                        if (was_full) prof_full += w1; else prof_cons += w1;
+                        ++prof_n;
+#endif
                     }
 #endif
                     // All directions advance together, phase by phase, so that the warp always has four independent
@@ -614,6 +629,15 @@ wave_kernel(WaveParams p)
                 optr += UN * GS;
                 gout += UN * 3 * WPP;
             }
+#ifdef WAVE_DBG_PROF
+            if (lane == 0) {
+                const int slot = (to_global ? 16 : r) * 4;
+                atomicAdd(p.prof + slot, (unsigned long long)(clock64() - prof_t0));
+                atomicAdd(p.prof + slot + 1, (unsigned long long)prof_full);
+                atomicAdd(p.prof + slot + 2, (unsigned long long)prof_cons);
+                atomicAdd(p.prof + slot + 3, (unsigned long long)prof_n);
+            }
+#endif
             if (to_ring) {
                 // zero vector "x = W1" for direction 3 of the row below (its predecessor is outside the image);
                 // the pseudo-pixel W1 is what the row below waits for at its last pixel
@@ -686,6 +710,11 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
     p.W1 = g.W1; p.H = g.H; p.D = g.D; p.P1 = g.P1; p.P2 = g.P2; p.nbands = nbands;
     MVS_CUDA(ctx, cudaMemsetAsync(ctl, 0, sizeof(int) * 2 * ctl_pass, ctx->stream));
     int rc;
+#ifdef WAVE_DBG_PROF
+    MVS_ARENA(ctx, unsigned long long, prof, "sgbm.wave.prof", 2 * 32 * 4);
+    MVS_CUDA(ctx, cudaMemsetAsync(prof, 0, sizeof(unsigned long long) * 2 * 32 * 4, ctx->stream));
+    p.prof = prof;
+#endif
     // forward sweep
     for (int f = 0; f < F; ++f) {
         p.f[f].C = (const uint32_t*)C[f]; p.f[f].Sin = nullptr; p.f[f].Sout = (uint32_t*)S[f];
@@ -697,9 +726,25 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
     // backward sweep: the same recurrence on the image flipped in x and y
     for (int f = 0; f < F; ++f) p.f[f].Sin = (const uint32_t*)S[f];
     p.ticket = ctl + ctl_pass; p.progress = ctl + ctl_pass + WAVE_CTL_PAD;
+#ifdef WAVE_DBG_PROF
+    p.prof = prof + 32 * 4;
+#endif
     if (g.mode == MVS_MODE_HH) rc = launch_wave_nw<0xF, true>(ctx, g, p);
     else if (g.mode == MVS_MODE_HH4) rc = launch_wave_nw<0x5, true>(ctx, g, p);
     else rc = launch_wave_nw<0x1, true>(ctx, g, p);  // MODE_SGBM: only the (x+1, y) direction
+#ifdef WAVE_DBG_PROF
+    {
+        unsigned long long h[2 * 32 * 4];
+        cudaMemcpyAsync(h, prof, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+        for (int s = 0; s < 2; ++s)
+            for (int r = 0; r <= 16; ++r) {
+                const unsigned long long* q = h + (s * 32 + r) * 4;
+                if (q[0]) fprintf(stderr, "prof sweep %d row %2d: total %8.2f Mclk  wait-above %5.1f%%  wait-below %5.1f%%  slow paths %llu\n", s, r,
+                                  q[0] * 1e-6, 100.0 * q[1] / q[0], 100.0 * q[2] / q[0], q[3]);
+            }
+    }
+#endif
     return rc;
 }
 

@@ -77,6 +77,9 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #define WAVE_HELPER_LAG 3    // boundary copies in flight in the helper warp (4 measured the same, 5 stalls)
 #endif
 #define WAVE_UNROLL 4        // pixels per trip of the sweep loop = WAVE_PF = half the ring depth
+#ifndef WAVE_L2PF
+#define WAVE_L2PF 8          // every second trip a warp asks L2 for the eight pixels of C (and S) that start this many pixels ahead
+#endif                       // (0 = off): the register prefetch above then finds its lines in L2 instead of waiting for HBM
 #ifndef WAVE_FMA_ADDS
 #define WAVE_FMA_ADDS 1      // plain adds on the FMA pipe (IMAD) instead of the ALU pipe
 #endif
@@ -458,6 +461,12 @@ wave_kernel(WaveParams p)
                 if (BWD) ldg_stream<NW>(sptr + q * GS, Sq[q]);
             }
             const uint32_t lane0 = lane == 0 ? 1u : 0u, lane0_ring = lane == 0 && to_ring ? 1u : 0u;
+#if WAVE_L2PF
+            // byte offset from this lane's pointer to the 128-byte line it prefetches: line `lane` of the eight pixels
+            // (4 KB at Dp = 256) that start WAVE_L2PF pixels ahead in sweep order
+            const ptrdiff_t l2pf_off = (ptrdiff_t)(BWD ? -(WAVE_L2PF + 7) : WAVE_L2PF) * (WPP * 4) + lane * 128 - lane * NW * 4;
+            constexpr int L2PF_LINES = 8 * WPP * 4 / 128;   // lines in eight pixels (32 at Dp = 256)
+#endif
             // Barrier tests for the coming pixel are issued one pixel early (their ~90 cycles of latency overlap the
             // arithmetic); a direction that has nothing to wait for counts as passed.  Pixel 0 starts untested.
             early_set(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
@@ -481,6 +490,12 @@ wave_kernel(WaveParams p)
                 const uint32_t fullc = my_full + hb, fullo = my_full + (32u - hb);
                 const uint32_t consc = dn_cons + hb, conso = dn_cons + (32u - hb);
                 const uint32_t arr_full = dn_full + hb, arr_cons = my_cons + hb;
+#if WAVE_L2PF
+                if (h == 0 && rem >= WAVE_L2PF + 8 && lane < L2PF_LINES) {
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"((const char*)cptr + l2pf_off));
+                    if (BWD) asm volatile("prefetch.global.L2 [%0];" ::"l"((const char*)sptr + l2pf_off));
+                }
+#endif
                 auto body = [&](auto kk) {
                     constexpr int k = decltype(kk)::value;
                     if (k >= rem) return;
@@ -493,7 +508,19 @@ wave_kernel(WaveParams p)
                     // phase and the wait on the opposite parity passes at once (the row below cannot finish pixel
                     // x - WAR + 7 before this row has written x - WAR + 8 > x).
                     uint32_t ok_full, ok_cons;
+#ifdef WAVE_DBG_PROF   // how long the outcome of each early test takes to arrive (a test suspends the warp while its phase is incomplete)
+                    {
+                        const long long q0 = clock64();
+                        asm volatile("selp.u32 %0, 1, 0, wave_pf;" : "=r"(ok_full)::"memory");
+                        const long long q1 = clock64();
+                        asm volatile("selp.u32 %0, 1, 0, wave_pc;" : "=r"(ok_cons)::"memory");
+                        const long long q2 = clock64();
+                        prof_full += q1 - q0;
+                        prof_cons += q2 - q1;
+                    }
+#else
                     early_read(ok_full, ok_cons);
+#endif
                     if (__builtin_expect((ok_full & ok_cons) == 0u, 0)) {
                         const uint32_t bf = k == 3 ? fullo : fullc + (k + 1) * 8u, pf = k == 3 ? par ^ h : par;
                         const uint32_t bc = WAR == 6 ? (k == 3 ? conso : consc + (k + 1) * 8u) : (k == 0 ? consc + 24u : conso + (k - 1) * 8u);
@@ -565,6 +592,9 @@ wave_kernel(WaveParams p)
                                 l[d][j] = v;
                             }
                         }
+#ifdef WAVE_REFILL_EARLY   // experiment: refill C right after its last use
+                    ldg_stream<NW>(cptr + (k + PF) * GS, Cq[k % PF]);
+#endif
 #pragma unroll
                     for (int d = 0; d < 4; ++d)
                         if (on[d]) {
@@ -588,12 +618,17 @@ wave_kernel(WaveParams p)
                         acc[j] = s;
                     }
                     stg_stream<NW>(optr + k * GS, acc);
+#ifdef WAVE_REFILL_EARLY
+                    if (BWD) ldg_stream<NW>(sptr + (k + PF) * GS, Sq[k % PF]);
+#endif
                     // Refill the prefetch slot with pixel x + PF, AFTER its last use, so that the load can target the same
                     // registers (issued earlier it gets temporaries, and the move into place waits for the load one pixel
                     // later).  Unconditional: beyond the row's end it reads up to PF pixels of the neighbouring row or of
                     // the guard band the volumes are allocated with (MVS_VOLUME_GUARD); those values are never used.
+#ifndef WAVE_REFILL_EARLY
                     ldg_stream<NW>(cptr + (k + PF) * GS, Cq[k % PF]);
                     if (BWD) ldg_stream<NW>(sptr + (k + PF) * GS, Sq[k % PF]);
+#endif
 #pragma unroll
                     for (int d = 0; d < 4; ++d)
                         if (on[d]) {

@@ -65,7 +65,10 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #define WAVE_D3 8            // ring depth for L3 (4 or 8; lock-step needs 2); L1 and L2 are 8 deep
 #endif
 #ifndef WAVE_PF
-#define WAVE_PF 4            // pixels of C / S prefetched into registers (= WAVE_UNROLL)
+#define WAVE_PF 4            // pixels of C prefetched into registers (1, 2 or 4 = WAVE_UNROLL)
+#endif
+#ifndef WAVE_PFS
+#define WAVE_PFS 4           // the same for S in the backward sweep
 #endif
 #ifndef WAVE_CONS_SLEEP
 #define WAVE_CONS_SLEEP 100
@@ -75,6 +78,9 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #endif                       // measured: 8 and 32 are slower)
 #ifndef WAVE_HELPER_LAG
 #define WAVE_HELPER_LAG 3    // boundary copies in flight in the helper warp (4 measured the same, 5 stalls)
+#endif
+#ifndef WAVE_DEFER_LAST
+#define WAVE_DEFER_LAST 1    // the prefetch slot of a trip's last pixel is loaded inside the same trip (see the refill in the sweep loop)
 #endif
 #define WAVE_UNROLL 4        // pixels per trip of the sweep loop = WAVE_PF = half the ring depth
 #ifndef WAVE_L2PF
@@ -154,13 +160,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t saddr, uint32_t parity)  
 // so the ~90 cycles a try_wait takes (even on a completed phase) overlap the arithmetic.  The outcome stays in a PTX
 // predicate in between (reading it into a register right away would wait for it): wave_kernel declares the predicates
 // wave_pf / wave_pc once at function scope and these helpers name them.
+// A row that has nothing to wait for in a direction (the first row of the first band has no row above, the last row of a
+// band no row below) keeps that in the predicates wave_na / wave_nr (set once per row): the tests need no branch.
+// test_wait only probes: it never suspends the warp.
 __device__ __forceinline__ void early_test_full(uint32_t saddr, uint32_t parity)
 {
-    asm volatile("mbarrier.try_wait.parity.shared::cta.b64 wave_pf, [%0], %1;" ::"r"(saddr), "r"(parity) : "memory");
+    asm volatile("mbarrier.test_wait.parity.shared::cta.b64 wave_pf, [%0], %1; or.pred wave_pf, wave_pf, wave_na;" ::"r"(saddr), "r"(parity) : "memory");
 }
 __device__ __forceinline__ void early_test_cons(uint32_t saddr, uint32_t parity)
 {
-    asm volatile("mbarrier.try_wait.parity.shared::cta.b64 wave_pc, [%0], %1;" ::"r"(saddr), "r"(parity) : "memory");
+    asm volatile("mbarrier.test_wait.parity.shared::cta.b64 wave_pc, [%0], %1; or.pred wave_pc, wave_pc, wave_nr;" ::"r"(saddr), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void early_row(uint32_t no_above, uint32_t no_below)
+{
+    asm volatile("setp.ne.u32 wave_na, %0, 0; setp.ne.u32 wave_nr, %1, 0;" ::"r"(no_above), "r"(no_below) : "memory");
 }
 __device__ __forceinline__ void early_set(uint32_t full_passed, uint32_t cons_passed)
 {
@@ -256,9 +269,9 @@ __global__ void __launch_bounds__(Ring<NW>::THREADS, 1)
 wave_kernel(WaveParams p)
 {
     using RG = Ring<NW>;
-    asm volatile(".reg .pred wave_pf, wave_pc;");   // outcomes of the early barrier tests (see early_test_full)
+    asm volatile(".reg .pred wave_pf, wave_pc, wave_na, wave_nr;");   // outcomes of the early barrier tests (see early_test_full)
     constexpr bool VERT = (DIRMASK & 0xE) != 0;
-    constexpr int WAVE_R = RG::R, WPP = RG::WPP, PF = WAVE_PF;
+    constexpr int WAVE_R = RG::R, WPP = RG::WPP, PF = WAVE_PF, PFS = WAVE_PFS;
     constexpr int GS = BWD ? -WPP : WPP;   // word step from pixel to pixel along the sweep
     extern __shared__ __align__(16) uint32_t ring[];
     __shared__ int s_item;
@@ -291,7 +304,9 @@ wave_kernel(WaveParams p)
     const uint32_t* rd = ring + (helper ? 0 : r) * RG::ROW_WORDS + lane * NW;
     uint32_t* wr = ring + (helper || r + 1 >= WAVE_R ? 0 : r + 1) * RG::ROW_WORDS + lane * NW;
     const uint32_t my_full = full_s + (uint32_t)(helper ? 0 : r) * (WAVE_NB * 8u), my_cons = cons_s + (uint32_t)(helper ? 0 : r) * (WAVE_NB * 8u);
-    const uint32_t dn_full = my_full + WAVE_NB * 8u, dn_cons = my_cons + WAVE_NB * 8u;   // ring row r + 1 (unused when r + 1 == R)
+    // ring row r + 1; the band's last warp has none: its (unused) tests then look at its own barriers, which are valid objects
+    const uint32_t dn_step = helper || r + 1 >= WAVE_R ? 0u : WAVE_NB * 8u;
+    const uint32_t dn_full = my_full + dn_step, dn_cons = my_cons + dn_step;
 
     for (;;) {
         __syncthreads();  // every warp has left the previous band
@@ -452,13 +467,35 @@ wave_kernel(WaveParams p)
             uint32_t* optr = fr.Sout + gbase;
             uint32_t* gout = bout + lane * NW;         // this lane's words of boundary pixel x4, direction 1
             // register prefetch ring: pixel q lives in slot q % PF
-            uint32_t Cq[PF][NW], Sq[PF][NW];
+            uint32_t Cq[PF][NW], Sq[PFS][NW];
+            // All global loads of a warp complete through ONE hardware scoreboard, so the first use of a prefetched register
+            // waits for every load issued before it, the youngest included: what counts is the age of the YOUNGEST load at
+            // each first use, not the depth of the ring.  A slot is refilled right after its pixel (the load targets the same
+            // registers); with a ring as deep as the trip (four pixels: one wait per trip) the slot of the trip's LAST pixel
+            // is instead loaded in the middle of the same trip's first pixel, so that no load is younger than 0.7 pixels
+            // at a first use.  The lines come from L2 (see WAVE_L2PF), which that age covers.
+            auto refill = [&](auto kk, auto& Q, const uint32_t* ptr, auto depth) {
+                constexpr int k = decltype(kk)::value, DEPTH = decltype(depth)::value;
+                if (DEPTH == WAVE_UNROLL && WAVE_DEFER_LAST) {
+                    if (k == 0) ldg_stream<NW>(ptr + (DEPTH - 1) * GS, Q[DEPTH - 1]);
+                    if (k != DEPTH - 1) ldg_stream<NW>(ptr + (k + DEPTH) * GS, Q[k % DEPTH]);
+                } else {
+                    // beyond the row's end this reads up to DEPTH pixels of the neighbouring row or of the guard band the
+                    // volumes are allocated with (MVS_VOLUME_GUARD); those values are never used
+                    ldg_stream<NW>(ptr + (k + DEPTH) * GS, Q[k % DEPTH]);
+                }
+            };
 #pragma unroll
             for (int q = 0; q < PF; ++q) {
 #pragma unroll
+                for (int j = 0; j < NW; ++j) Cq[q][j] = 0;
+                if (!(PF == WAVE_UNROLL && WAVE_DEFER_LAST && q == PF - 1)) ldg_stream<NW>(cptr + q * GS, Cq[q]);
+            }
+#pragma unroll
+            for (int q = 0; q < PFS; ++q) {
+#pragma unroll
                 for (int j = 0; j < NW; ++j) Sq[q][j] = 0;
-                ldg_stream<NW>(cptr + q * GS, Cq[q]);
-                if (BWD) ldg_stream<NW>(sptr + q * GS, Sq[q]);
+                if (BWD && !(PFS == WAVE_UNROLL && WAVE_DEFER_LAST && q == PFS - 1)) ldg_stream<NW>(sptr + q * GS, Sq[q]);
             }
             const uint32_t lane0 = lane == 0 ? 1u : 0u, lane0_ring = lane == 0 && to_ring ? 1u : 0u;
 #if WAVE_L2PF
@@ -470,6 +507,7 @@ wave_kernel(WaveParams p)
             // Barrier tests for the coming pixel are issued one pixel early (their ~90 cycles of latency overlap the
             // arithmetic); a direction that has nothing to wait for counts as passed.  Pixel 0 starts untested.
             early_set(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
+            early_row(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
 #ifdef WAVE_DBG_PROF
             long long prof_t0 = clock64(), prof_full = 0, prof_cons = 0, prof_n = 0;
 #endif
@@ -501,7 +539,7 @@ wave_kernel(WaveParams p)
                     if (k >= rem) return;
                     const int x = x4 + k;
                     uint32_t (&Cw)[NW] = Cq[k % PF];   // operands of this pixel: loaded PF pixels ago
-                    uint32_t (&Sw)[NW] = Sq[k % PF];
+                    uint32_t (&Sw)[NW] = Sq[k % PFS];
 #ifndef WAVE_DBG_NOWAIT   // (timing experiment: wrong results)
                     // (1) the row above is written through pixel x + 1; (2) the slots about to be overwritten were read:
                     // pixel x - WAR - 1 of the row below is finished.  For x <= WAR that barrier is still in its first
@@ -549,15 +587,14 @@ wave_kernel(WaveParams p)
                     if (on[3]) ldw<NW>(RG::D3 == 8 ? (k == 3 ? rdo + RG::O3 : rdc + RG::O3 + (k + 1) * WPP)   // L3 of pixel x + 1
                                                    : rd + RG::O3 + ((k + 1) & 3) * WPP, a[3]);
 #ifndef WAVE_DBG_NOWAIT
-                    // test the NEXT pixel's two barriers now (looked at when the next pixel starts)
-                    if (VERT && k + 1 < rem) {
+                    // test the NEXT pixel's two barriers now (looked at when the next pixel starts; behind the row's last
+                    // pixel the outcome is not used: the next row starts untested)
+                    if (VERT) {
                         const uint32_t bf = k >= 2 ? fullo + (k - 2) * 8u : fullc + (k + 2) * 8u, pf = k >= 2 ? par ^ h : par;
                         const uint32_t bc = WAR == 6 ? (k >= 2 ? conso + (k - 2) * 8u : consc + (k + 2) * 8u) : conso + k * 8u;
                         const uint32_t pc = WAR == 6 ? pf ^ 1u : par ^ h ^ 1u;
-                        if (wait_above) early_test_full(bf, pf);
-                        if (to_ring) early_test_cons(bc, pc);
-                    } else if (VERT) {
-                        early_set(wait_above ? 0u : 1u, to_ring ? 0u : 1u);   // the next row starts untested
+                        early_test_full(bf, pf);
+                        early_test_cons(bc, pc);
                     }
 #endif
 #pragma unroll
@@ -592,9 +629,6 @@ wave_kernel(WaveParams p)
                                 l[d][j] = v;
                             }
                         }
-#ifdef WAVE_REFILL_EARLY   // experiment: refill C right after its last use
-                    ldg_stream<NW>(cptr + (k + PF) * GS, Cq[k % PF]);
-#endif
 #pragma unroll
                     for (int d = 0; d < 4; ++d)
                         if (on[d]) {
@@ -618,17 +652,10 @@ wave_kernel(WaveParams p)
                         acc[j] = s;
                     }
                     stg_stream<NW>(optr + k * GS, acc);
-#ifdef WAVE_REFILL_EARLY
-                    if (BWD) ldg_stream<NW>(sptr + (k + PF) * GS, Sq[k % PF]);
-#endif
-                    // Refill the prefetch slot with pixel x + PF, AFTER its last use, so that the load can target the same
-                    // registers (issued earlier it gets temporaries, and the move into place waits for the load one pixel
-                    // later).  Unconditional: beyond the row's end it reads up to PF pixels of the neighbouring row or of
-                    // the guard band the volumes are allocated with (MVS_VOLUME_GUARD); those values are never used.
-#ifndef WAVE_REFILL_EARLY
-                    ldg_stream<NW>(cptr + (k + PF) * GS, Cq[k % PF]);
-                    if (BWD) ldg_stream<NW>(sptr + (k + PF) * GS, Sq[k % PF]);
-#endif
+                    // refill the prefetch slots AFTER their last use, so that the loads can target the same registers (issued
+                    // earlier they get temporaries, and the move into place waits for the load one pixel later)
+                    refill(kk, Cq, cptr, IC<PF>());
+                    if (BWD) refill(kk, Sq, sptr, IC<PFS>());
 #pragma unroll
                     for (int d = 0; d < 4; ++d)
                         if (on[d]) {

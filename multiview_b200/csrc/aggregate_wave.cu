@@ -67,8 +67,11 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #ifndef WAVE_PF
 #define WAVE_PF 4            // pixels of C prefetched into registers (1, 2 or 4 = WAVE_UNROLL)
 #endif
+#ifndef WAVE_PF_BWD
+#define WAVE_PF_BWD 2        // the same in the backward sweep, whose winner-take-all step needs the registers (measured: 2 + 1
+#endif                       // costs 0.8 % against 4 + 4)
 #ifndef WAVE_PFS
-#define WAVE_PFS 4           // the same for S in the backward sweep
+#define WAVE_PFS 1           // pixels of S prefetched in the backward sweep
 #endif
 #ifndef WAVE_CONS_SLEEP
 #define WAVE_CONS_SLEEP 100
@@ -99,8 +102,16 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 struct WaveFrame {
     const uint32_t* C;
     const uint32_t* Sin;   // backward sweep: S after the forward sweep (nullptr in the forward sweep)
-    uint32_t* Sout;
+    uint32_t* Sout;        // the sweep's sums (nullptr in a backward sweep whose winner-take-all step is the only consumer of S)
     uint32_t* bnd;         // [nbands][W1][3][wpp] boundary vectors (normalised path costs of a band's last row)
+    int16_t* raw;          // backward sweep with the winner-take-all step: raw disparity image [H][W] (initialised to INV) ..
+    uint32_t* disp2key;    // .. and the right-view keys [H][W] (initialised to 0x7fffffff); nullptr: no winner-take-all step
+};
+// winner-take-all step of cv::StereoSGBM inside the backward sweep (see wta_pixel)
+struct WaveWta {
+    int W, minX1, minD, ur, K44;
+    uint32_t ur_magic;     // ceil(2^32 / (100 - ur)) (0 when the divisor is 1): n / (100 - ur) == umulhi(n, ur_magic) for n < 2^25
+    int* sat_flag;
 };
 struct WaveParams {
     WaveFrame f[MVS_MAX_BATCH];
@@ -109,6 +120,7 @@ struct WaveParams {
     int* error;            // set when a bounded wait expires
     int W1, H, D, P1, P2, nbands, F;
     uint32_t one;          // 1, opaque to the compiler (see WAVE_FMA_ADDS)
+    WaveWta wta;
 #ifdef WAVE_DBG_PROF       // developer build: per-row clock counts {row total, waiting for the row above, waiting for the row below, slow paths}
     unsigned long long* prof;
 #endif
@@ -264,6 +276,101 @@ __device__ __forceinline__ uint32_t addf(uint32_t a, uint32_t b, uint32_t one)
 
 template <int K> struct IC { static constexpr int value = K; };
 
+// ---- winner-take-all step of cv::StereoSGBM inside the backward sweep --------------------------------------------------
+// (reference call site strategies/stereosgbm_disp.cpp:121-125.)  The backward sweep is the last writer of
+// S, and the winner-take-all step its only reader: done here, on the sums a warp holds in registers, S never goes back to
+// memory (2 B per cell written and 2 B read saved).  One pixel: first minimum, uniqueness test over the disparities
+// outside best-1..best+1, the two neighbours of the minimum for the sub-pixel fit; the divisions, the right-view key
+// (atomicMin on minS << 16 | (0xFFFF - x): the reference's "first writer in descending x wins") and the store are done
+// for 32 pixels at a time, one pixel per lane (wta_flush).
+// In: S, this lane's words of the pixel (split layout: word j holds disparity lane * NW + j in its low half and that
+// + Dp/2 in its high half; padding disparities hold 32767).  Out, the same in all lanes: key = minS << 16 | best
+// (0xFFFFFFFF: the pixel keeps the invalid value), nb = S(best-1) | S(best+1) << 16.
+template <int NW, bool PAD>
+__device__ __forceinline__ void wta_pixel(const uint32_t (&S)[NW], const uint32_t (&padsent)[NW], int lane, int D, const WaveWta& w,
+                                          uint32_t& key_out, uint32_t& nb_out)
+{
+    constexpr uint32_t HALF = NW * 32;
+    const uint32_t d0 = (uint32_t)lane * NW;
+    // (1) first minimum: min over (S << 16 | d); padding never beats a real minimum below 32767
+    uint32_t kl = 0xffffffffu, kh = 0xffffffffu;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+        kl = min(kl, S[j] * 65536u + (d0 + j));
+        kh = min(kh, (S[j] & 0xffff0000u) | (d0 + j));
+    }
+    const uint32_t key = __reduce_min_sync(0xffffffffu, min(kl, kh + HALF));
+    const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
+    // (2) the neighbours of the minimum: S(d) for a warp-uniform d
+    auto getS = [&](int d) -> uint32_t {
+        const int half = d >= (int)HALF ? 1 : 0, idx = d - half * (int)HALF, src = idx / NW, word = idx - src * NW;
+        uint32_t v = S[0];
+#pragma unroll
+        for (int j = 1; j < NW; ++j) v = word == j ? S[j] : v;
+        v = __shfl_sync(0xffffffffu, v, src);
+        return half ? v >> 16 : v & 0xffffu;
+    };
+    const bool has_m = best > 0, has_p = best < D - 1;
+    const uint32_t smv = getS(max(best - 1, 0)), spv = getS(min(best + 1, D - 1));
+    const uint32_t sm = has_m ? smv : 0u, sp = has_p ? spv : 0u;
+    // (3) uniqueness: reject if some d outside best-1..best+1 has S(d) * (100 - ur) < minS * 100, i.e. S(d) <= thr; with the
+    // "minus (min Lp + P2)" form of the recurrence (K44 = directions * P2, see mvs_set_sgbm_recurrence) the S held here is
+    // that form's S plus K44 and the test reads S(d) * (100 - ur) < minS * 100 - K44 * ur.  Counted: the real disparities
+    // with S <= thr (per half, bit 15 of (thr | 0x8000) - S), against those of the window itself.
+    const int rhs = minS * 100 - w.K44 * w.ur;
+    const uint32_t num = (uint32_t)(rhs - 1);
+    const uint32_t thr = w.ur_magic ? __umulhi(num, w.ur_magic) : num;   // meaningful when rhs > 0
+    const uint32_t tc = min(thr, 32767u);
+    const uint32_t T2 = (tc | 0x8000u) * 0x10001u;
+    uint32_t u[2] = {0u, 0u};
+#pragma unroll
+    for (int j = 0; j < NW; j += 2) {
+        uint32_t t0 = T2 - S[j], t1 = j + 1 < NW ? T2 - S[j + 1 < NW ? j + 1 : j] : 0u;
+        if (PAD) {
+            t0 &= ~((padsent[j] + 0x00010001u) & 0x80008000u);
+            if (j + 1 < NW) t1 &= ~((padsent[j + 1 < NW ? j + 1 : j] + 0x00010001u) & 0x80008000u);
+        }
+        // bytes of u: 0xFF where the flag (bit 15 / 31 of t0, t1) is set -- prmt's sign-replicating selectors (the
+        // __byte_perm intrinsic only passes the three index bits of a selector)
+        asm("prmt.b32 %0, %1, %2, 0xFDB9;" : "=r"(u[j / 2]) : "r"(t0), "r"(t1));
+    }
+    const int cnt4 = __reduce_add_sync(0xffffffffu, __popc((u[0] & 0x0f0f0f0fu) | (u[1] & 0xf0f0f0f0u)));   // 4 per flagged disparity
+    const int nwin = ((uint32_t)minS <= tc ? 1 : 0) + (has_m && sm <= tc ? 1 : 0) + (has_p && sp <= tc ? 1 : 0);
+    const bool not_unique = rhs > 0 && cnt4 != 4 * nwin;
+    if (w.K44) {
+        // A saturated sum (32767 here) only matters where it takes part in a decision: as the minimum, as a neighbour of the
+        // minimum, or when the uniqueness threshold reaches it.  Those cases are reported, never guessed around.
+        uint32_t sf = 0;
+#pragma unroll
+        for (int j = 0; j < NW; ++j) sf |= (S[j] + 0x00010001u) & ~((padsent[j] + 0x00010001u) & 0x80008000u);
+        const bool satp = __any_sync(0xffffffffu, (sf & 0x80008000u) != 0u);
+        if (lane == 0 && (minS >= 32767 || (satp && ((rhs > 0 && thr >= 32767u) || (has_m && sm >= 32767u) || (has_p && sp >= 32767u)))))
+            *w.sat_flag = 1;
+    }
+    key_out = (minS >= 32767 || not_unique) ? 0xffffffffu : key;
+    nb_out = sm | (sp << 16);
+}
+
+// Lane q holds the outcome of sweep pixel xs_first + q of sweep row `y` (image row): sub-pixel fit, right-view key, store.
+template <bool BWD>
+__device__ __forceinline__ void wta_flush(const WaveFrame& fr, const WaveWta& w, int W1, int D, int y, int xs_first, int n, int lane,
+                                          uint32_t st_key, uint32_t st_nb)
+{
+    if (lane >= n || st_key == 0xffffffffu) return;
+    const int xs = xs_first + lane, x = BWD ? W1 - 1 - xs : xs;
+    const int best = (int)(st_key & 0xffffu), minS = (int)(st_key >> 16), sm = (int)(st_nb & 0xffffu), sp = (int)(st_nb >> 16);
+    const int x2 = x + w.minX1 - best - w.minD;
+    atomicMin(fr.disp2key + (size_t)y * w.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
+    int d = best;
+    if (0 < d && d < D - 1) {
+        const int den = max(sm + sp - 2 * minS, 1);
+        d = d * 16 + ((sm - sp) * 16 + den) / (den * 2);
+    } else
+        d *= 16;
+    fr.raw[(size_t)y * w.W + x + w.minX1] = (int16_t)(d + w.minD * 16);
+}
+
+
 template <int NW, int DIRMASK, bool PAD, bool BWD>
 __global__ void __launch_bounds__(Ring<NW>::THREADS, 1)
 wave_kernel(WaveParams p)
@@ -271,7 +378,7 @@ wave_kernel(WaveParams p)
     using RG = Ring<NW>;
     asm volatile(".reg .pred wave_pf, wave_pc, wave_na, wave_nr;");   // outcomes of the early barrier tests (see early_test_full)
     constexpr bool VERT = (DIRMASK & 0xE) != 0;
-    constexpr int WAVE_R = RG::R, WPP = RG::WPP, PF = WAVE_PF, PFS = WAVE_PFS;
+    constexpr int WAVE_R = RG::R, WPP = RG::WPP, PF = BWD ? WAVE_PF_BWD : WAVE_PF, PFS = WAVE_PFS;
     constexpr int GS = BWD ? -WPP : WPP;   // word step from pixel to pixel along the sweep
     extern __shared__ __align__(16) uint32_t ring[];
     __shared__ int s_item;
@@ -498,6 +605,12 @@ wave_kernel(WaveParams p)
                 if (BWD && !(PFS == WAVE_UNROLL && WAVE_DEFER_LAST && q == PFS - 1)) ldg_stream<NW>(sptr + q * GS, Sq[q]);
             }
             const uint32_t lane0 = lane == 0 ? 1u : 0u, lane0_ring = lane == 0 && to_ring ? 1u : 0u;
+            // backward sweep: the winner-take-all step runs one pixel behind the sums (its reductions and shuffles then
+            // overlap the next pixel's arithmetic); lane q keeps the outcome of pixel q mod 32 until 32 are complete
+            const bool wta_on = BWD && fr.raw != nullptr, store_s = !BWD || fr.Sout != nullptr;
+            uint32_t accp[NW], st_key = 0xffffffffu, st_nb = 0u;
+#pragma unroll
+            for (int j = 0; j < NW; ++j) accp[j] = SENT2;
 #if WAVE_L2PF
             // byte offset from this lane's pointer to the 128-byte line it prefetches: line `lane` of the eight pixels
             // (4 KB at Dp = 256) that start WAVE_L2PF pixels ahead in sweep order
@@ -597,6 +710,12 @@ wave_kernel(WaveParams p)
                         early_test_cons(bc, pc);
                     }
 #endif
+                    if (BWD && wta_on && (k > 0 || x4 > 0)) {   // the previous pixel of the row
+                        uint32_t wkey, wnb;
+                        wta_pixel<NW, PAD>(accp, padsent, lane, p.D, p.wta, wkey, wnb);
+                        if (lane == ((x - 1) & 31)) { st_key = wkey; st_nb = wnb; }
+                        if (k == 0 && (x4 & 31) == 0) wta_flush<BWD>(fr, p.wta, W1, p.D, y, x4 - 32, 32, lane, st_key, st_nb);
+                    }
 #pragma unroll
                     for (int d = 0; d < 4; ++d)
                         if (on[d]) {
@@ -651,7 +770,11 @@ wave_kernel(WaveParams p)
                         if (BWD) s = __viaddmin_u16x2(Sw[j], s, SENT2);   // S = min(S_in + sum L, 32767)
                         acc[j] = s;
                     }
-                    stg_stream<NW>(optr + k * GS, acc);
+                    if (store_s) stg_stream<NW>(optr + k * GS, acc);
+                    if (BWD) {
+#pragma unroll
+                        for (int j = 0; j < NW; ++j) accp[j] = acc[j];
+                    }
                     // refill the prefetch slots AFTER their last use, so that the loads can target the same registers (issued
                     // earlier they get temporaries, and the move into place waits for the load one pixel later)
                     refill(kk, Cq, cptr, IC<PF>());
@@ -690,6 +813,12 @@ wave_kernel(WaveParams p)
                 if (BWD) sptr += UN * GS;
                 optr += UN * GS;
                 gout += UN * 3 * WPP;
+            }
+            if (BWD && wta_on) {   // the row's last pixel, and the outcomes not stored yet
+                uint32_t wkey, wnb;
+                wta_pixel<NW, PAD>(accp, padsent, lane, p.D, p.wta, wkey, wnb);
+                if (lane == ((W1 - 1) & 31)) { st_key = wkey; st_nb = wnb; }
+                wta_flush<BWD>(fr, p.wta, W1, p.D, y, (W1 - 1) & ~31, ((W1 - 1) & 31) + 1, lane, st_key, st_nb);
             }
 #ifdef WAVE_DBG_PROF
             if (lane == 0) {
@@ -752,7 +881,7 @@ static int launch_wave_nw(mvs_ctx* ctx, const SgbmGeom& g, const WaveParams& p)
 #endif
 }
 
-int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S)
+int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S, const SgbmWtaOut* wta)
 {
     if (F < 1 || F > MVS_MAX_BATCH) return mvs_fail(ctx, MVS_ERR_ARG, "aggregate: batch of %d frames (1..%d)", F, MVS_MAX_BATCH);
     const int nbands = cdiv(g.H, wave_rows(g.Dp / 64));
@@ -785,8 +914,22 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
     p.ticket = ctl; p.progress = ctl + WAVE_CTL_PAD;
     rc = g.mode == MVS_MODE_HH4 ? launch_wave_nw<0x5, false>(ctx, g, p) : launch_wave_nw<0xF, false>(ctx, g, p);
     if (rc) return rc;
-    // backward sweep: the same recurrence on the image flipped in x and y
-    for (int f = 0; f < F; ++f) p.f[f].Sin = (const uint32_t*)S[f];
+    // backward sweep: the same recurrence on the image flipped in x and y; with the winner-take-all step inside, S is
+    // not written again unless the caller wants to look at it
+    for (int f = 0; f < F; ++f) {
+        p.f[f].Sin = (const uint32_t*)S[f];
+        if (wta) {
+            p.f[f].raw = wta->raw[f]; p.f[f].disp2key = wta->disp2key[f];
+            if (!wta->store_S) p.f[f].Sout = nullptr;
+        }
+    }
+    if (wta) {
+        MVS_ARENA(ctx, int, sat, "sgbm.sat44", 1);
+        const uint32_t udiv = (uint32_t)(100 - g.ur);
+        p.wta.W = g.W; p.wta.minX1 = g.minX1; p.wta.minD = g.minD; p.wta.ur = g.ur; p.wta.K44 = g.K44;
+        p.wta.ur_magic = udiv <= 1 ? 0u : (uint32_t)(((1ull << 32) + udiv - 1) / udiv);
+        p.wta.sat_flag = sat;
+    }
     p.ticket = ctl + ctl_pass; p.progress = ctl + ctl_pass + WAVE_CTL_PAD;
 #ifdef WAVE_DBG_PROF
     p.prof = prof + 32 * 4;
@@ -812,7 +955,7 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
 
 int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S)
 {
-    return sgbm_aggregate_batch_dev(ctx, g, 1, &C, &S);
+    return sgbm_aggregate_batch_dev(ctx, g, 1, &C, &S, nullptr);
 }
 
 // Host check of the bounded-wait flag (synchronises the stream); called by the entry points that sync anyway.

@@ -175,7 +175,7 @@ static int census_chain(mvs_ctx* ctx, const T* dl_img, const T* dr_img, int w, i
     }
     MVS_LAUNCH_CHECK_N(ctx, "census kernels", 3);
     const int16_t* Cc = C;
-    int rc = sgbm_aggregate_batch_dev(ctx, g, 1, &Cc, &S);
+    int rc = sgbm_aggregate_batch_dev(ctx, g, 1, &Cc, &S, nullptr);
     if (rc) return rc;
     switch (D / 64) {
     case 1: census_wta_kernel<1><<<pb, 256, 0, s>>>((const uint16_t*)S, w, h, disp, disp + n); break;

@@ -171,14 +171,22 @@ int sgbm_cost_volume_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const uin
                                int16_t* const* C);
 int sgbm_aggregate_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* C, int16_t* S);       // fused wavefront sweeps
 int sgbm_aggregate_wave_status(mvs_ctx* ctx, cudaStream_t stream = nullptr);  // nullptr: the compute stream
-int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S);
+// wta != nullptr: the backward sweep also does the winner-take-all step of cv::StereoSGBM (raw disparities into raw[f],
+// [H][W], initialised to INV; right-view keys into disp2key[f], [H][W], initialised to 0x7fffffff; the left-right check
+// follows in sgbm_lr_post_batch_dev) and leaves S as the forward sweep wrote it unless store_S is set
+struct SgbmWtaOut {
+    int16_t* raw[MVS_MAX_BATCH];
+    uint32_t* disp2key[MVS_MAX_BATCH];
+    bool store_S;
+};
+int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S, const SgbmWtaOut* wta);
 int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
                              int16_t* const* disp16, int16_t* raw16_tap /* F == 1 only */);
-int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16);
 int sgbm_front_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
-                         int sset, int16_t** S);
-int sgbm_tail_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, int w, int h, int16_t* const* S, int16_t* const* disp16,
+                         int sset, bool keep_S, SgbmWtaOut* wta);
+int sgbm_tail_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, int w, int h, const SgbmWtaOut& wta, int16_t* const* disp16,
                         int16_t* raw16_tap);
-int sgbm_wta_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, int F, int16_t* const* S, int16_t* const* disp16);
+int sgbm_wta_buffers_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, int sset, SgbmWtaOut* out);
+int sgbm_lr_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, int F, const SgbmWtaOut& wta, int16_t* const* disp16,
+                           int16_t* raw16_tap);
 int disp_to_float_batch_dev(mvs_ctx* ctx, int F, int16_t* const* d16, int w, int h, float* const* out);
-int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, const int16_t* raw16, int16_t* disp16);

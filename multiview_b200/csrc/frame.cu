@@ -188,17 +188,18 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
                 rc = presmooth_batch_dev(ctx, 2, ps + 2 * f, 3, w, h, (size_t)w * 3, descs[f].presmooth_sigma, pd + 2 * f, (size_t)w);
     }
     stage_end(ctx, "presmooth");
-    int16_t* Sv[MVS_MAX_BATCH];
+    SgbmWtaOut wta;
     int sset = 0;
     if (rc) return rc;
     {
         const uint8_t *l[MVS_MAX_BATCH], *r[MVS_MAX_BATCH];
         for (int f = 0; f < n_frames; ++f) { l[f] = sb[f].grey[0]; r[f] = sb[f].grey[1]; }
-        // first half on the main stream: cost volumes + aggregation into S set `sset`, whose previous reader must be done
+        // first half on the main stream: cost volumes + aggregation (with the winner-take-all step) into buffer set `sset`, whose
+        // previous reader must be done
         sset = ctx->s_set;
         ctx->s_set ^= 1;
         if (ctx->tail_done_recorded[sset]) MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_tail_done[sset], 0));
-        rc = sgbm_front_batch_dev(ctx, &d0.sgbm, n_frames, l, r, w, h, sset, Sv);
+        rc = sgbm_front_batch_dev(ctx, &d0.sgbm, n_frames, l, r, w, h, sset, false, &wta);
         if (rc) return rc;
         MVS_CUDA(ctx, cudaEventRecord(ctx->ev_front_done, s));
     }
@@ -212,7 +213,7 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     if (!rc) {
         int16_t* d16[MVS_MAX_BATCH];
         for (int f = 0; f < n_frames; ++f) d16[f] = sb[f].disp16;
-        rc = sgbm_tail_batch_dev(ctx, &d0.sgbm, n_frames, w, h, Sv, d16, nullptr);
+        rc = sgbm_tail_batch_dev(ctx, &d0.sgbm, n_frames, w, h, wta, d16, nullptr);
     }
     stage_begin(ctx, "cloud");
     if (!rc) {

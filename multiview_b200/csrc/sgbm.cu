@@ -29,64 +29,57 @@ static std::string fname(const char* base, int f)
 // A batch of F pairs of equal size through the SGBM chain, in two halves so that the frame path can run the second
 // half of one batch on another stream while the first half of the next batch occupies the main stream:
 //   front: cost volumes of all frames, then ONE aggregation launch per sweep for the whole batch (its wavefronts fill
-//          the GPU); writes the S volumes of set `sset` (0 or 1);
-//   tail:  WTA + LR check + median + speckle filter from those S volumes.
+//          the GPU); the backward sweep does the winner-take-all step and writes raw disparities + right-view keys into
+//          the buffers of set `sset` (0 or 1).  S is final only when keep_S is set (the test tap);
+//   tail:  left-right check + median + speckle filter from those buffers.
 int sgbm_front_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
-                         int sset, int16_t** S)
+                         int sset, bool keep_S, SgbmWtaOut* wta)
 {
     if (F < 1 || F > MVS_MAX_BATCH) return mvs_fail(ctx, MVS_ERR_ARG, "sgbm: batch of %d frames (1..%d)", F, MVS_MAX_BATCH);
     SgbmGeom g;
     int rc = sgbm_geom(ctx, p, w, h, &g);
     if (rc) return rc;
-    int16_t* C[MVS_MAX_BATCH];
+    int16_t *C[MVS_MAX_BATCH], *S[MVS_MAX_BATCH];
     for (int f = 0; f < F; ++f) {
         C[f] = sgbm_volume(ctx, fname("sgbm.C", f).c_str(), g);
-        S[f] = sgbm_volume(ctx, fname(sset ? "sgbm.S1" : "sgbm.S", f).c_str(), g);
+        S[f] = sgbm_volume(ctx, fname("sgbm.S", f).c_str(), g);
         if (!C[f] || !S[f]) return MVS_ERR_NOMEM;
     }
     stage_begin(ctx, "cost");
     rc = sgbm_cost_volume_batch_dev(ctx, g, F, l, r, C);
     stage_end(ctx, "cost");
     if (rc) return rc;
+    rc = sgbm_wta_buffers_dev(ctx, g, F, sset, wta);
+    if (rc) return rc;
+    wta->store_S = keep_S;
     stage_begin(ctx, "aggregate");
-    rc = sgbm_aggregate_batch_dev(ctx, g, F, C, S);
+    rc = sgbm_aggregate_batch_dev(ctx, g, F, C, S, wta);
     stage_end(ctx, "aggregate");
     return rc;
 }
 
-int sgbm_tail_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, int w, int h, int16_t* const* S, int16_t* const* disp16,
+int sgbm_tail_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, int w, int h, const SgbmWtaOut& wta, int16_t* const* disp16,
                         int16_t* raw16_tap)
 {
     SgbmGeom g;
     int rc = sgbm_geom(ctx, p, w, h, &g);
     if (rc) return rc;
-    // F == 1: "wta" and "post" are timed separately; a batch times both under "wta"
-    if (F > 1) {
-        stage_begin(ctx, "wta");
-        rc = sgbm_wta_post_batch_dev(ctx, g, p, F, S, disp16);
-        stage_end(ctx, "wta");
-        return rc;
-    }
-    int16_t* raw = raw16_tap ? raw16_tap : (int16_t*)arena_get(ctx, "sgbm.raw", sizeof(int16_t) * (size_t)w * h);
-    if (!raw) return MVS_ERR_NOMEM;
-    stage_begin(ctx, "wta");
-    rc = sgbm_wta_dev(ctx, g, S[0], raw);
-    stage_end(ctx, "wta");
-    stage_begin(ctx, "post");
-    if (!rc) rc = sgbm_post_dev(ctx, g, p, raw, disp16[0]);
-    stage_end(ctx, "post");
+    // F == 1: "wta" (left-right check) and "post" are timed separately; a batch times both under "wta"
+    if (F > 1) stage_begin(ctx, "wta");
+    rc = sgbm_lr_post_batch_dev(ctx, g, p, F, wta, disp16, F == 1 ? raw16_tap : nullptr);
+    if (F > 1) stage_end(ctx, "wta");
     return rc;
 }
 
 int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r,
                              int w, int h, int16_t* const* disp16, int16_t* raw16_tap)
 {
-    int16_t* S[MVS_MAX_BATCH];
+    SgbmWtaOut wta;
     int rc = main_stream_waits_for_tail(ctx);
     if (rc) return rc;
-    rc = sgbm_front_batch_dev(ctx, p, F, l, r, w, h, 0, S);
+    rc = sgbm_front_batch_dev(ctx, p, F, l, r, w, h, 0, /* keep_S: the tap reads it */ raw16_tap != nullptr, &wta);
     if (rc) return rc;
-    return sgbm_tail_batch_dev(ctx, p, F, w, h, S, disp16, F == 1 ? raw16_tap : nullptr);
+    return sgbm_tail_batch_dev(ctx, p, F, w, h, wta, disp16, F == 1 ? raw16_tap : nullptr);
 }
 
 int sgbm_compute16_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, const uint8_t* l, const uint8_t* r, int w, int h,

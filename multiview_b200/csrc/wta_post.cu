@@ -1,119 +1,12 @@
-// a3 (v)-(vii) and a4: winner-take-all with uniqueness, parabola sub-pixel, right-view consistency,
-// 3x3 median, speckle filter and float conversion (reference call sites
+// a3 (vi)-(vii) and a4: right-view consistency check, 3x3 median, speckle filter and float conversion (reference call sites
 // cost-functions/disparity/strategies/stereosgbm_disp.cpp:121-125 and :141-150).
 #include "common.cuh"
 
-// ---- WTA: one warp per pixel ---------------------------------------------------------------------------------
-// disp2 (the right-view disparity) is a per-row argmin with "first writer in descending x wins ties":
-// realised as atomicMin on key = minS << 16 | (0xFFFF - x), from which the winning d follows as
-// x + minX1 - x2 - minD... (x2 = x + minX1 - d - minD), so no second array is needed.
-#define WTA_PPW 8  // pixels per warp: their loads are issued together (memory-level parallelism), then processed in turn
-// ur_magic = ceil(2^32 / (100 - ur)) (0 when the divisor is 1): n / (100 - ur) == umulhi(n, ur_magic) for n < 2^25
-template <int NW>
-__global__ void __launch_bounds__(256)
-wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key,
-           int* __restrict__ sat_flag)
-{
-    __shared__ __align__(16) uint32_t sh[8][NW * 32];
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const long long npix = (long long)g.W1 * g.H;
-    const long long pix0 = ((long long)blockIdx.x * 8 + wib) * WTA_PPW;
-    if (pix0 >= npix) return;
-    uint32_t wall[WTA_PPW][NW];
-#pragma unroll
-    for (int q = 0; q < WTA_PPW; ++q) {
-        const long long pix = min(pix0 + q, npix - 1);
-        const uint32_t* Sp = S + (size_t)pix * (NW * 32) + lane * NW;
-        if (NW == 4) { uint4 v = __ldcs((const uint4*)Sp); wall[q][0] = v.x; wall[q][1 % NW] = v.y; wall[q][2 % NW] = v.z; wall[q][3 % NW] = v.w; }
-        else if (NW == 2) { uint2 v = __ldcs((const uint2*)Sp); wall[q][0] = v.x; wall[q][1 % NW] = v.y; }
-        else {
-#pragma unroll
-            for (int j = 0; j < NW; ++j) wall[q][j] = __ldcs(Sp + j);
-        }
-    }
-    // split layout (common.cuh): word w of a pixel holds disparity w (low half) and w + Dp/2 (high half)
-    constexpr uint32_t HALF = NW * 32;
-    uint32_t padbits[NW];
-#pragma unroll
-    for (int j = 0; j < NW; ++j) {
-        const uint32_t d0 = (uint32_t)(lane * NW + j);
-        padbits[j] = (d0 >= (uint32_t)g.D ? 0xffffu : 0u) | (d0 + HALF >= (uint32_t)g.D ? 0xffff0000u : 0u);
-    }
-    auto hw_index = [](int d) -> int { return d >= (int)HALF ? 2 * (d - (int)HALF) + 1 : 2 * d; };  // halfword of disparity d in the staged copy
-    uint32_t* mysh = sh[wib];
-    uint16_t* hw = (uint16_t*)mysh;
-    // lane q keeps the outcome of pixel q; the divisions, the atomic and the store happen once per warp at the end
-    int my_best = -1, my_minS = 0, my_sm = 0, my_sp = 0;
-#pragma unroll
-    for (int q = 0; q < WTA_PPW; ++q) {
-        if (pix0 + q >= npix) break;
-        const uint32_t (&w)[NW] = wall[q];
-        // first argmin: min over (S << 16 | d); padding (d >= D) holds 32767 and never beats a real minimum below it
-        uint32_t key = 0xffffffffu;
-        __syncwarp();  // the previous pixel's staged copy has been read by every lane
-#pragma unroll
-        for (int j = 0; j < NW; ++j) {
-            const uint32_t d0 = (uint32_t)(lane * NW + j);
-            key = min(key, min(w[j] * 65536u + d0, (w[j] & 0xffff0000u) | (d0 + HALF)));
-            // staged copy for the uniqueness test: padding is taken out of it (0xFFFF never counts)
-            mysh[lane * NW + j] = w[j] | padbits[j];
-        }
-        key = __reduce_min_sync(0xffffffffu, key);
-        const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
-        // "minus (min Lp + P2)" form of the recurrence (g.K44 = directions * P2): S here is that form's S plus K44 wherever
-        // no sum saturated.  A saturated sum (32767 here, at least 32767 - K44 there) only matters where it takes part in a
-        // decision: as the minimum, as a neighbour of the minimum in the sub-pixel fit, or when the uniqueness threshold
-        // reaches it.  Those cases are reported (sat_flag), never guessed around; everywhere else the result is exact.
-        bool satp = false;
-        if (g.K44) {
-            uint32_t mx = 0;
-#pragma unroll
-            for (int j = 0; j < NW; ++j) mx = __vmaxu2(mx, w[j] & ~padbits[j]);
-            satp = __reduce_max_sync(0xffffffffu, max(mx & 0xffffu, mx >> 16)) >= 32767u;
-        }
-        if (minS >= 32767) {   // every cost saturated: the reference leaves / writes INV here
-            if (g.K44 && lane == 0) *sat_flag = 1;
-            continue;
-        }
-        __syncwarp();
-        // uniqueness: reject if some d outside best-1..best+1 has S*(100-ur) < minS*100, i.e. S <= thr.
-        // Lane q reads the two neighbours it needs for the sub-pixel fit, blanks best-1..best+1 in the staged copy,
-        // and the warp takes one packed minimum over what is left.
-        int sm = 0, sp = 0;
-        if (lane == q) {
-            if (best > 0) { sm = hw[hw_index(best - 1)]; hw[hw_index(best - 1)] = 0xffffu; }
-            if (best < g.D - 1) { sp = hw[hw_index(best + 1)]; hw[hw_index(best + 1)] = 0xffffu; }
-            hw[hw_index(best)] = 0xffffu;
-        }
-        __syncwarp();
-        uint32_t m = 0xffffffffu;
-#pragma unroll
-        for (int j = 0; j < NW; ++j) m = __vminu2(m, mysh[lane * NW + j]);
-        const uint32_t mn = __reduce_min_sync(0xffffffffu, min(m & 0xffffu, m >> 16));
-        // S(d) * (100 - ur) < minS * 100 in the reference's own S; with S' = S - K44 (the other form of the recurrence,
-        // K44 = 0 for OpenCV 4.13's form) that is S(d) * (100 - ur) < minS * 100 - K44 * ur on the S held here
-        const int rhs = minS * 100 - g.K44 * g.ur;
-        const uint32_t num = (uint32_t)(rhs - 1);
-        const uint32_t thr = rhs > 0 ? (ur_magic ? __umulhi(num, ur_magic) : num) : 0xffffffffu;  // ur <= 99 (mvs_sgbm_check)
-        if (satp && lane == q && ((rhs > 0 && thr >= 32767u) || (best > 0 && sm >= 32767) || (best < g.D - 1 && sp >= 32767))) *sat_flag = 1;
-        if (rhs > 0 && mn != 0xffffu && mn <= thr) continue;
-        if (lane == q) { my_best = best; my_minS = minS; my_sm = sm; my_sp = sp; }
-    }
-    if (lane < WTA_PPW && my_best >= 0) {
-        int y = (int)(pix0 / g.W1), x = (int)(pix0 - (long long)y * g.W1) + lane;
-        while (x >= g.W1) { x -= g.W1; ++y; }
-        const int x2 = x + g.minX1 - my_best - g.minD;
-        atomicMin(disp2key + (size_t)y * g.W + x2, ((uint32_t)my_minS << 16) | (uint32_t)(0xffff - x));
-        int d = my_best;
-        if (0 < d && d < g.D - 1) {
-            int den = max(my_sm + my_sp - 2 * my_minS, 1);
-            d = d * 16 + ((my_sm - my_sp) * 16 + den) / (den * 2);
-        } else
-            d *= 16;
-        raw[(size_t)y * g.W + x + g.minX1] = (int16_t)(d + g.minD * 16);
-    }
-}
-
+// The winner-take-all step itself (first minimum, uniqueness, sub-pixel fit, right-view key) runs inside the backward
+// aggregation sweep (aggregate_wave.cu: wta_pixel / wta_flush) on the sums the sweep holds in registers.  disp2 (the
+// right-view disparity) is a per-row argmin with "first writer in descending x wins ties": realised there as atomicMin on
+// key = minS << 16 | (0xFFFF - x), from which the winning d follows as x + minX1 - x2 - minD (x2 = x + minX1 - d - minD),
+// so no second array is needed.  Here: the initial values, and the left-right check that reads the keys.
 __device__ __forceinline__ void wta_init_body(int16_t* raw, uint32_t* disp2key, size_t n, int inv)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -281,26 +174,6 @@ __device__ __forceinline__ void disp_to_float_body(const int16_t* __restrict__ d
 }
 
 // ---- launchable forms: one image, or the images of a whole batch (blockIdx.z = frame) ----------------------------------
-__global__ void wta_init_kernel(int16_t* raw, uint32_t* disp2key, size_t n, int inv) { wta_init_body(raw, disp2key, n, inv); }
-__global__ void lr_check_kernel(int16_t* __restrict__ raw, const uint32_t* __restrict__ disp2key, SgbmGeom g) { lr_check_body(raw, disp2key, g); }
-__global__ void median3_kernel(const int16_t* __restrict__ src, int W, int H, int16_t* __restrict__ dst) { median3_body(src, W, H, dst); }
-__global__ void __launch_bounds__(256)
-speckle_runs_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* __restrict__ L, int* __restrict__ cnt)
-{
-    speckle_runs_body(img, W, H, newVal, maxDiff, L, cnt);
-}
-__global__ void speckle_merge_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L)
-{
-    speckle_merge_body(img, W, H, newVal, maxDiff, L);
-}
-__global__ void speckle_resolve_kernel(const int16_t* __restrict__ img, int W, int H, int newVal, int maxDiff, int* L, int* cnt)
-{
-    speckle_resolve_body(img, W, H, newVal, maxDiff, L, cnt);
-}
-__global__ void speckle_apply_kernel(int16_t* img, size_t n, int newVal, int maxSize, const int* __restrict__ L, const int* __restrict__ cnt)
-{
-    speckle_apply_body(img, n, newVal, maxSize, L, cnt);
-}
 __global__ void disp_to_float_kernel(const int16_t* __restrict__ d, size_t n, float* __restrict__ out) { disp_to_float_body(d, n, out); }
 
 // Batched: raw / disp2key / L / cnt of frame z are slices of one buffer (stride n = W*H); the disparity images are the
@@ -344,81 +217,41 @@ __global__ void speckle_apply_batch_kernel(PostBatch b, size_t n, int newVal, in
 }
 __global__ void disp_to_float_batch_kernel(PostBatch b, size_t n) { disp_to_float_body(b.disp16[blockIdx.z], n, b.dispf[blockIdx.z]); }
 
-int sgbm_wta_dev(mvs_ctx* ctx, const SgbmGeom& g, const int16_t* S, int16_t* raw16)
+// Buffers of the winner-take-all step for a batch of F frames, set `sset` (the frame path alternates two sets: the second
+// half of batch k on the tail stream reads one while the sweeps of batch k + 1 fill the other), initialised.
+int sgbm_wta_buffers_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, int sset, SgbmWtaOut* out)
 {
-    cudaStream_t s = ctx->stream;
-    size_t n = (size_t)g.W * g.H;
-    MVS_ARENA(ctx, uint32_t, d2, "sgbm.disp2key", n);
-    MVS_ARENA(ctx, int, sat, "sgbm.sat44", 1);
-    wta_init_kernel<<<cdiv(n, 256), 256, 0, s>>>(raw16, d2, n, g.INV);
-    int blocks = cdiv((long long)g.W1 * g.H, 8 * WTA_PPW);
-    const uint32_t udiv = (uint32_t)(100 - g.ur);
-    const uint32_t ur_magic = udiv <= 1 ? 0u : (uint32_t)(((1ull << 32) + udiv - 1) / udiv);
-    switch (g.Dp / 64) {
-    case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2, sat); break;
-    case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2, sat); break;
-    case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2, sat); break;
-    case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S, g, ur_magic, raw16, d2, sat); break;
-    default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
-    }
-    MVS_LAUNCH_CHECK_N(ctx, "wta_kernel", 2);
-    lr_check_kernel<<<dim3(cdiv(g.W1, 128), g.H), 128, 0, s>>>(raw16, d2, g);
-    MVS_LAUNCH_CHECK(ctx, "lr_check_kernel");
+    const size_t n = (size_t)g.W * g.H;
+    int16_t* raw = (int16_t*)arena_get(ctx, sset ? "sgbm.batch.raw.1" : "sgbm.batch.raw", sizeof(int16_t) * n * MVS_MAX_BATCH);
+    uint32_t* d2 = (uint32_t*)arena_get(ctx, sset ? "sgbm.batch.disp2key.1" : "sgbm.batch.disp2key", sizeof(uint32_t) * n * MVS_MAX_BATCH);
+    if (!raw || !d2) return MVS_ERR_NOMEM;
+    memset(out, 0, sizeof(*out));
+    for (int f = 0; f < F; ++f) { out->raw[f] = raw + n * f; out->disp2key[f] = d2 + n * f; }
+    wta_init_batch_kernel<<<dim3(cdiv(n, 256), 1, F), 256, 0, ctx->stream>>>(raw, d2, n, g.INV);
+    MVS_LAUNCH_CHECK(ctx, "wta_init_batch_kernel");
     return MVS_OK;
 }
 
-int sgbm_post_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, const int16_t* raw16, int16_t* disp16)
-{
-    cudaStream_t s = ctx->stream;
-    size_t n = (size_t)g.W * g.H;
-    median3_kernel<<<dim3(cdiv(g.W, 128), g.H), 128, 0, s>>>(raw16, g.W, g.H, disp16);
-    MVS_LAUNCH_CHECK(ctx, "median3_kernel");
-    if (p->speckle_win > 0) {
-        MVS_ARENA(ctx, int, L, "sgbm.speckle.label", n);
-        MVS_ARENA(ctx, int, cnt, "sgbm.speckle.count", n);
-        int maxDiff = 16 * p->speckle_range;
-        MVS_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int) * n, s));
-        speckle_runs_kernel<<<cdiv(g.H, 8), 256, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L, cnt);
-        if (g.H > 1) speckle_merge_kernel<<<dim3(cdiv(g.W, 128), g.H - 1), 128, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L);
-        speckle_resolve_kernel<<<dim3(cdiv(g.W, 128), g.H), 128, 0, s>>>(disp16, g.W, g.H, g.INV, maxDiff, L, cnt);
-        speckle_apply_kernel<<<cdiv(n, 256), 256, 0, s>>>(disp16, n, g.INV, p->speckle_win, L, cnt);
-        MVS_LAUNCH_CHECK_N(ctx, "speckle kernels", 4);
-    }
-    return MVS_OK;
-}
-
-// WTA + LR check + median + speckle filter for the F frames of a batch: the small per-image kernels run once per batch
-// (blockIdx.z = frame), only the WTA scan of the S volumes stays one launch per frame.
-int sgbm_wta_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, int F, int16_t* const* S, int16_t* const* disp16)
+// Left-right check + median + speckle filter for the F frames of a batch whose raw disparities and right-view keys the
+// backward sweep has written (buffers of sgbm_wta_buffers_dev): the small per-image kernels run once per batch
+// (blockIdx.z = frame).  raw16_tap (F == 1): copy of the raw disparities after the left-right check.
+int sgbm_lr_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, int F, const SgbmWtaOut& wta, int16_t* const* disp16,
+                           int16_t* raw16_tap)
 {
     cudaStream_t s = ctx->stream;
     const size_t n = (size_t)g.W * g.H;
-    MVS_ARENA(ctx, int16_t, raw, "sgbm.batch.raw", n * F);
-    MVS_ARENA(ctx, uint32_t, d2, "sgbm.batch.disp2key", n * F);
-    MVS_ARENA(ctx, int, sat, "sgbm.sat44", 1);
+    int16_t* raw = wta.raw[0];          // frames are consecutive slices
+    uint32_t* d2 = wta.disp2key[0];
     PostBatch b;
     memset(&b, 0, sizeof(b));
     for (int f = 0; f < F; ++f) b.disp16[f] = disp16[f];
-    wta_init_batch_kernel<<<dim3(cdiv(n, 256), 1, F), 256, 0, s>>>(raw, d2, n, g.INV);
-    MVS_LAUNCH_CHECK(ctx, "wta_init_batch_kernel");
-    const int blocks = cdiv((long long)g.W1 * g.H, 8 * WTA_PPW);
-    const uint32_t udiv = (uint32_t)(100 - g.ur);
-    const uint32_t ur_magic = udiv <= 1 ? 0u : (uint32_t)(((1ull << 32) + udiv - 1) / udiv);
-    for (int f = 0; f < F; ++f) {
-        int16_t* rf = raw + n * f;
-        uint32_t* df = d2 + n * f;
-        switch (g.Dp / 64) {
-        case 1: wta_kernel<1><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df, sat); break;
-        case 2: wta_kernel<2><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df, sat); break;
-        case 3: wta_kernel<3><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df, sat); break;
-        case 4: wta_kernel<4><<<blocks, 256, 0, s>>>((const uint32_t*)S[f], g, ur_magic, rf, df, sat); break;
-        default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
-        }
-        MVS_LAUNCH_CHECK(ctx, "wta_kernel");
-    }
+    if (F == 1) stage_begin(ctx, "wta");
     lr_check_batch_kernel<<<dim3(cdiv(g.W1, 128), g.H, F), 128, 0, s>>>(raw, d2, g);
+    MVS_LAUNCH_CHECK(ctx, "lr_check_batch_kernel");
+    if (raw16_tap) MVS_CUDA(ctx, cudaMemcpyAsync(raw16_tap, raw, n * sizeof(int16_t), cudaMemcpyDeviceToDevice, s));
+    if (F == 1) { stage_end(ctx, "wta"); stage_begin(ctx, "post"); }
     median3_batch_kernel<<<dim3(cdiv(g.W, 128), g.H, F), 128, 0, s>>>(raw, g.W, g.H, b);
-    MVS_LAUNCH_CHECK_N(ctx, "lr_check / median3 batch kernels", 2);
+    MVS_LAUNCH_CHECK(ctx, "median3_batch_kernel");
     if (p->speckle_win > 0) {
         MVS_ARENA(ctx, int, L, "sgbm.batch.speckle.label", n * F);
         MVS_ARENA(ctx, int, cnt, "sgbm.batch.speckle.count", n * F);
@@ -428,8 +261,9 @@ int sgbm_wta_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_para
         if (g.H > 1) speckle_merge_batch_kernel<<<dim3(cdiv(g.W, 128), g.H - 1, F), 128, 0, s>>>(b, g.W, g.H, g.INV, maxDiff, L);
         speckle_resolve_batch_kernel<<<dim3(cdiv(g.W, 128), g.H, F), 128, 0, s>>>(b, g.W, g.H, g.INV, maxDiff, L, cnt);
         speckle_apply_batch_kernel<<<dim3(cdiv(n, 256), 1, F), 256, 0, s>>>(b, n, g.INV, p->speckle_win, L, cnt);
-        MVS_LAUNCH_CHECK_N(ctx, "speckle batch kernels", 4);
+        MVS_LAUNCH_CHECK_N(ctx, "speckle batch kernels", g.H > 1 ? 4 : 3);
     }
+    if (F == 1) stage_end(ctx, "post");
     return MVS_OK;
 }
 

@@ -283,44 +283,53 @@ template <int K> struct IC { static constexpr int value = K; };
 // outside best-1..best+1, the two neighbours of the minimum for the sub-pixel fit; the divisions, the right-view key
 // (atomicMin on minS << 16 | (0xFFFF - x): the reference's "first writer in descending x wins") and the store are done
 // for 32 pixels at a time, one pixel per lane (wta_flush).
-// In: S, this lane's words of the pixel (split layout: word j holds disparity lane * NW + j in its low half and that
-// + Dp/2 in its high half; padding disparities hold 32767).  Out, the same in all lanes: key = minS << 16 | best
-// (0xFFFFFFFF: the pixel keeps the invalid value), nb = S(best-1) | S(best+1) << 16.
-template <int NW, bool PAD>
-__device__ __forceinline__ void wta_pixel(const uint32_t (&S)[NW], const uint32_t (&padsent)[NW], int lane, int D, const WaveWta& w,
-                                          uint32_t& key_out, uint32_t& nb_out)
+// S: this lane's words of the pixel (split layout: word j holds disparity lane * NW + j in its low half and that
+// + Dp/2 in its high half; padding disparities hold 32767).
+// Per pixel only what needs the whole vector is done, in two stages placed between the phases of the sweep's own
+// arithmetic (the compiler keeps warp-wide operations in program order, and each stage's reduction then has the next phase
+// of the sweep to complete in; no branch around a stage: it must share a basic block with that arithmetic):
+//   A: the first minimum, one min-reduction over (S << 16 | d);
+//   B: the two neighbours of the minimum, read from a copy of the vector the warp staged in shared memory, and one
+//      sum-reduction that counts the disparities below the uniqueness threshold.
+// Lane q keeps these raw outcomes of pixel q mod 32; everything scalar (threshold test, sub-pixel division, right-view key,
+// store) is done for 32 pixels at a time, one pixel per lane (wta_flush).
+template <int NW>
+__device__ __forceinline__ uint32_t wta_stage_a(const uint32_t (&S)[NW], int lane)
 {
     constexpr uint32_t HALF = NW * 32;
     const uint32_t d0 = (uint32_t)lane * NW;
-    // (1) first minimum: min over (S << 16 | d); padding never beats a real minimum below 32767
-    uint32_t kl = 0xffffffffu, kh = 0xffffffffu;
+    uint32_t kl = 0xffffffffu, kh = 0xffffffffu;   // padding never beats a real minimum below 32767
 #pragma unroll
     for (int j = 0; j < NW; ++j) {
         kl = min(kl, S[j] * 65536u + (d0 + j));
         kh = min(kh, (S[j] & 0xffff0000u) | (d0 + j));
     }
-    const uint32_t key = __reduce_min_sync(0xffffffffu, min(kl, kh + HALF));
-    const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
-    // (2) the neighbours of the minimum: S(d) for a warp-uniform d
-    auto getS = [&](int d) -> uint32_t {
-        const int half = d >= (int)HALF ? 1 : 0, idx = d - half * (int)HALF, src = idx / NW, word = idx - src * NW;
-        uint32_t v = S[0];
-#pragma unroll
-        for (int j = 1; j < NW; ++j) v = word == j ? S[j] : v;
-        v = __shfl_sync(0xffffffffu, v, src);
-        return half ? v >> 16 : v & 0xffffu;
-    };
-    const bool has_m = best > 0, has_p = best < D - 1;
-    const uint32_t smv = getS(max(best - 1, 0)), spv = getS(min(best + 1, D - 1));
-    const uint32_t sm = has_m ? smv : 0u, sp = has_p ? spv : 0u;
-    // (3) uniqueness: reject if some d outside best-1..best+1 has S(d) * (100 - ur) < minS * 100, i.e. S(d) <= thr; with the
-    // "minus (min Lp + P2)" form of the recurrence (K44 = directions * P2, see mvs_set_sgbm_recurrence) the S held here is
-    // that form's S plus K44 and the test reads S(d) * (100 - ur) < minS * 100 - K44 * ur.  Counted: the real disparities
-    // with S <= thr (per half, bit 15 of (thr | 0x8000) - S), against those of the window itself.
-    const int rhs = minS * 100 - w.K44 * w.ur;
+    return __reduce_min_sync(0xffffffffu, min(kl, kh + HALF));   // minS << 16 | best
+}
+// Uniqueness: a pixel is rejected if some d outside best-1..best+1 has S(d) * (100 - ur) < minS * 100, i.e. S(d) <= thr;
+// with the "minus (min Lp + P2)" form of the recurrence (K44 = directions * P2, see mvs_set_sgbm_recurrence) the S held
+// here is that form's S plus K44 and the test reads S(d) * (100 - ur) < minS * 100 - K44 * ur = rhs.
+__device__ __forceinline__ uint32_t wta_threshold(int minS, const WaveWta& w, int& rhs)
+{
+    rhs = minS * 100 - w.K44 * w.ur;
     const uint32_t num = (uint32_t)(rhs - 1);
-    const uint32_t thr = w.ur_magic ? __umulhi(num, w.ur_magic) : num;   // meaningful when rhs > 0
-    const uint32_t tc = min(thr, 32767u);
+    return w.ur_magic ? __umulhi(num, w.ur_magic) : num;   // meaningful when rhs > 0
+}
+// staged: the warp's copy of S as 16-bit values in the order of the split layout.  nb = S(best-1) | S(best+1) << 16 (the
+// clamped neighbours: the flush ignores the one that does not exist); cnt = 4 * (real disparities with S <= min(thr, 32767):
+// per half, bit 15 of (thr | 0x8000) - S) + 4096 * (lanes that hold a saturated sum; only the other form of the recurrence
+// looks at it, but a branch would cut the basic block).
+template <int NW, bool PAD>
+__device__ __forceinline__ void wta_stage_b(const uint32_t (&S)[NW], const uint32_t (&padsent)[NW], int D, const WaveWta& w, uint32_t key,
+                                            const uint16_t* staged, uint32_t& nb, int& cnt)
+{
+    constexpr int HALF = NW * 32;
+    const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
+    const int dm = max(best - 1, 0), dp = min(best + 1, D - 1);
+    const uint32_t sm = staged[dm >= HALF ? 2 * (dm - HALF) + 1 : 2 * dm], sp = staged[dp >= HALF ? 2 * (dp - HALF) + 1 : 2 * dp];
+    nb = sm | (sp << 16);
+    int rhs;
+    const uint32_t tc = min(wta_threshold(minS, w, rhs), 32767u);
     const uint32_t T2 = (tc | 0x8000u) * 0x10001u;
     uint32_t u[2] = {0u, 0u};
 #pragma unroll
@@ -334,31 +343,35 @@ __device__ __forceinline__ void wta_pixel(const uint32_t (&S)[NW], const uint32_
         // __byte_perm intrinsic only passes the three index bits of a selector)
         asm("prmt.b32 %0, %1, %2, 0xFDB9;" : "=r"(u[j / 2]) : "r"(t0), "r"(t1));
     }
-    const int cnt4 = __reduce_add_sync(0xffffffffu, __popc((u[0] & 0x0f0f0f0fu) | (u[1] & 0xf0f0f0f0u)));   // 4 per flagged disparity
-    const int nwin = ((uint32_t)minS <= tc ? 1 : 0) + (has_m && sm <= tc ? 1 : 0) + (has_p && sp <= tc ? 1 : 0);
-    const bool not_unique = rhs > 0 && cnt4 != 4 * nwin;
-    if (w.K44) {
-        // A saturated sum (32767 here) only matters where it takes part in a decision: as the minimum, as a neighbour of the
-        // minimum, or when the uniqueness threshold reaches it.  Those cases are reported, never guessed around.
-        uint32_t sf = 0;
+    uint32_t mx = 0;
 #pragma unroll
-        for (int j = 0; j < NW; ++j) sf |= (S[j] + 0x00010001u) & ~((padsent[j] + 0x00010001u) & 0x80008000u);
-        const bool satp = __any_sync(0xffffffffu, (sf & 0x80008000u) != 0u);
-        if (lane == 0 && (minS >= 32767 || (satp && ((rhs > 0 && thr >= 32767u) || (has_m && sm >= 32767u) || (has_p && sp >= 32767u)))))
-            *w.sat_flag = 1;
-    }
-    key_out = (minS >= 32767 || not_unique) ? 0xffffffffu : key;
-    nb_out = sm | (sp << 16);
+    for (int j = 0; j < NW; ++j) mx = __vmaxu2(mx, PAD ? S[j] & ~(padsent[j] | (padsent[j] << 1)) : S[j]);   // padding halves -> 0
+    const uint32_t sat = ((mx + 0x00010001u) & 0x80008000u) != 0u ? 4096u : 0u;
+    cnt = __reduce_add_sync(0xffffffffu, __popc((u[0] & 0x0f0f0f0fu) | (u[1] & 0xf0f0f0f0u)) + sat);
 }
 
-// Lane q holds the outcome of sweep pixel xs_first + q of sweep row `y` (image row): sub-pixel fit, right-view key, store.
+// Lane q holds the raw outcome of sweep pixel xs_first + q of image row y: uniqueness decision, sub-pixel fit, right-view
+// key, store.
 template <bool BWD>
 __device__ __forceinline__ void wta_flush(const WaveFrame& fr, const WaveWta& w, int W1, int D, int y, int xs_first, int n, int lane,
-                                          uint32_t st_key, uint32_t st_nb)
+                                          uint32_t st_key, uint32_t st_nb, int st_cnt)
 {
-    if (lane >= n || st_key == 0xffffffffu) return;
+    if (lane >= n) return;
     const int xs = xs_first + lane, x = BWD ? W1 - 1 - xs : xs;
-    const int best = (int)(st_key & 0xffffu), minS = (int)(st_key >> 16), sm = (int)(st_nb & 0xffffu), sp = (int)(st_nb >> 16);
+    const int best = (int)(st_key & 0xffffu), minS = (int)(st_key >> 16);
+    const bool has_m = best > 0, has_p = best < D - 1;
+    const int sm = has_m ? (int)(st_nb & 0xffffu) : 0, sp = has_p ? (int)(st_nb >> 16) : 0;
+    int rhs;
+    const uint32_t thr = wta_threshold(minS, w, rhs), tc = min(thr, 32767u);
+    const int cnt4 = st_cnt & 4095;
+    const bool satp = st_cnt >= 4096;
+    // the window's own members among the counted disparities
+    const int nwin = ((uint32_t)minS <= tc ? 1 : 0) + (has_m && (uint32_t)sm <= tc ? 1 : 0) + (has_p && (uint32_t)sp <= tc ? 1 : 0);
+    const bool not_unique = rhs > 0 && cnt4 != 4 * nwin;
+    // A saturated sum (32767 here) only matters where it takes part in a decision: as the minimum, as a neighbour of the
+    // minimum, or when the uniqueness threshold reaches it.  Those cases are reported, never guessed around.
+    if (w.K44 && (minS >= 32767 || (satp && ((rhs > 0 && thr >= 32767u) || (has_m && sm >= 32767) || (has_p && sp >= 32767))))) *w.sat_flag = 1;
+    if (minS >= 32767 || not_unique) return;   // the pixel keeps the invalid value
     const int x2 = x + w.minX1 - best - w.minD;
     atomicMin(fr.disp2key + (size_t)y * w.W + x2, ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
     int d = best;
@@ -370,8 +383,7 @@ __device__ __forceinline__ void wta_flush(const WaveFrame& fr, const WaveWta& w,
     fr.raw[(size_t)y * w.W + x + w.minX1] = (int16_t)(d + w.minD * 16);
 }
 
-
-template <int NW, int DIRMASK, bool PAD, bool BWD>
+template <int NW, int DIRMASK, bool PAD, bool BWD, bool WTA>
 __global__ void __launch_bounds__(Ring<NW>::THREADS, 1)
 wave_kernel(WaveParams p)
 {
@@ -386,6 +398,7 @@ wave_kernel(WaveParams p)
     // "pixel p of ring row k consumed" (by warp k); the pseudo-pixel W1 is the zero slot behind the row
     __shared__ __align__(8) uint64_t s_full[WAVE_R][WAVE_NB];
     __shared__ __align__(8) uint64_t s_cons[WAVE_R][WAVE_NB];
+    __shared__ __align__(16) uint32_t s_wta[WTA ? WAVE_R : 1][WTA ? WPP : 4];   // winner-take-all step: a warp's copy of its last sums
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const bool helper = wid == WAVE_R;
     // The warp scheduler favours higher warp ids among eligible warps: upstream rows (whose progress everything below
@@ -607,8 +620,10 @@ wave_kernel(WaveParams p)
             const uint32_t lane0 = lane == 0 ? 1u : 0u, lane0_ring = lane == 0 && to_ring ? 1u : 0u;
             // backward sweep: the winner-take-all step runs one pixel behind the sums (its reductions and shuffles then
             // overlap the next pixel's arithmetic); lane q keeps the outcome of pixel q mod 32 until 32 are complete
-            const bool wta_on = BWD && fr.raw != nullptr, store_s = !BWD || fr.Sout != nullptr;
+            const bool store_s = !BWD || fr.Sout != nullptr;
             uint32_t accp[NW], st_key = 0xffffffffu, st_nb = 0u;
+            int st_cnt = 0;
+            uint32_t* wta_mine = &s_wta[WTA ? r : 0][0];
 #pragma unroll
             for (int j = 0; j < NW; ++j) accp[j] = SENT2;
 #if WAVE_L2PF
@@ -710,12 +725,14 @@ wave_kernel(WaveParams p)
                         early_test_cons(bc, pc);
                     }
 #endif
-                    if (BWD && wta_on && (k > 0 || x4 > 0)) {   // the previous pixel of the row
-                        uint32_t wkey, wnb;
-                        wta_pixel<NW, PAD>(accp, padsent, lane, p.D, p.wta, wkey, wnb);
-                        if (lane == ((x - 1) & 31)) { st_key = wkey; st_nb = wnb; }
-                        if (k == 0 && (x4 & 31) == 0) wta_flush<BWD>(fr, p.wta, W1, p.D, y, x4 - 32, 32, lane, st_key, st_nb);
-                    }
+                    // winner-take-all step of the row's previous pixel, stage A (B follows the sweep's own reductions, C the
+                    // barrier arrivals)
+                    // (no branch around the stages: they must share a basic block with the sweep's arithmetic to be
+                    // interleaved with it.  The row's first pixel runs them on a vector of saturated sums, which gives
+                    // "no disparity" for a lane slot that has just been stored.)
+                    uint32_t wkey = 0, wnb = 0;
+                    int wcnt = 0;
+                    if (WTA) wkey = wta_stage_a<NW>(accp, lane);
 #pragma unroll
                     for (int d = 0; d < 4; ++d)
                         if (on[d]) {
@@ -761,6 +778,10 @@ wave_kernel(WaveParams p)
 #pragma unroll
                     for (int d = 0; d < 4; ++d)
                         if (on[d]) m[d] = __reduce_min_sync(0xffffffffu, m[d]);   // (v << 16 | v) is monotone in v: still duplicated
+                    if (WTA) {
+                        if (!VERT) __syncwarp();   // (with vertical directions the warp barrier before the arrivals has ordered the staged copy)
+                        wta_stage_b<NW, PAD>(accp, padsent, p.D, p.wta, wkey, (const uint16_t*)wta_mine, wnb, wcnt);
+                    }
                     // S accumulation (the reference saturates once per pass; all terms are non-negative, so clamping as we go is the same)
 #pragma unroll
                     for (int j = 0; j < NW; ++j) {
@@ -771,7 +792,10 @@ wave_kernel(WaveParams p)
                         acc[j] = s;
                     }
                     if (store_s) stg_stream<NW>(optr + k * GS, acc);
-                    if (BWD) {
+                    if (WTA) {
+                        // (the stage-B reads of the previous vector precede this store in program order)
+                        if (lane == ((x - 1) & 31)) { st_key = wkey; st_nb = wnb; st_cnt = wcnt; }
+                        stw<NW>(wta_mine + lane * NW, acc);
 #pragma unroll
                         for (int j = 0; j < NW; ++j) accp[j] = acc[j];
                     }
@@ -807,6 +831,7 @@ wave_kernel(WaveParams p)
                         mbar_arrive_if(arr_full + (uint32_t)k * 8u, lane0_ring);
                         mbar_arrive_if(arr_cons + (uint32_t)k * 8u, lane0);
                     }
+                    if (WTA && k == 0 && (x4 & 31) == 0 && x4 > 0) wta_flush<BWD>(fr, p.wta, W1, p.D, y, x4 - 32, 32, lane, st_key, st_nb, st_cnt);
                 };
                 body(IC<0>()); body(IC<1>()); body(IC<2>()); body(IC<3>());
                 cptr += UN * GS;
@@ -814,11 +839,15 @@ wave_kernel(WaveParams p)
                 optr += UN * GS;
                 gout += UN * 3 * WPP;
             }
-            if (BWD && wta_on) {   // the row's last pixel, and the outcomes not stored yet
-                uint32_t wkey, wnb;
-                wta_pixel<NW, PAD>(accp, padsent, lane, p.D, p.wta, wkey, wnb);
-                if (lane == ((W1 - 1) & 31)) { st_key = wkey; st_nb = wnb; }
-                wta_flush<BWD>(fr, p.wta, W1, p.D, y, (W1 - 1) & ~31, ((W1 - 1) & 31) + 1, lane, st_key, st_nb);
+            if (WTA) {   // the row's last pixel, and the outcomes not stored yet
+                uint32_t wnb;
+                int wcnt;
+                const uint32_t wkey = wta_stage_a<NW>(accp, lane);
+                __syncwarp();
+                wta_stage_b<NW, PAD>(accp, padsent, p.D, p.wta, wkey, (const uint16_t*)wta_mine, wnb, wcnt);
+                if (lane == ((W1 - 1) & 31)) { st_key = wkey; st_nb = wnb; st_cnt = wcnt; }
+                wta_flush<BWD>(fr, p.wta, W1, p.D, y, (W1 - 1) & ~31, ((W1 - 1) & 31) + 1, lane, st_key, st_nb, st_cnt);
+                __syncwarp();   // the staged copy is overwritten by the next band's first pixel
             }
 #ifdef WAVE_DBG_PROF
             if (lane == 0) {
@@ -846,7 +875,7 @@ wave_kernel(WaveParams p)
     }
 }
 
-template <int NW, int DIRMASK, bool PAD, bool BWD>
+template <int NW, int DIRMASK, bool PAD, bool BWD, bool WTA>
 static int launch_wave(mvs_ctx* ctx, const WaveParams& p)
 {
     const int smem = Ring<NW>::WORDS * 4;
@@ -854,28 +883,28 @@ static int launch_wave(mvs_ctx* ctx, const WaveParams& p)
     static bool attr_set[MVS_MAX_DEVICES] = {};
     const int dv = ctx->device >= 0 && ctx->device < MVS_MAX_DEVICES ? ctx->device : -1;
     if (dv < 0 || !attr_set[dv]) {
-        MVS_CUDA(ctx, cudaFuncSetAttribute(wave_kernel<NW, DIRMASK, PAD, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        MVS_CUDA(ctx, cudaFuncSetAttribute(wave_kernel<NW, DIRMASK, PAD, BWD, WTA>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         if (dv >= 0) attr_set[dv] = true;
     }
     const int grid = min(p.nbands * p.F, ctx->sm_count);   // one CTA per SM (__launch_bounds__(.., 1), > half of the shared memory)
-    wave_kernel<NW, DIRMASK, PAD, BWD><<<grid, Ring<NW>::THREADS, smem, ctx->stream>>>(p);
+    wave_kernel<NW, DIRMASK, PAD, BWD, WTA><<<grid, Ring<NW>::THREADS, smem, ctx->stream>>>(p);
     MVS_LAUNCH_CHECK(ctx, "wave_kernel");
     return MVS_OK;
 }
 
-template <int DIRMASK, bool BWD>
+template <int DIRMASK, bool BWD, bool WTA>
 static int launch_wave_nw(mvs_ctx* ctx, const SgbmGeom& g, const WaveParams& p)
 {
     bool pad = g.Dp != g.D;
 #ifdef WAVE_ONLY_NW4   // quick experimental builds
-    if (g.Dp == 256 && !pad) return launch_wave<4, DIRMASK, false, BWD>(ctx, p);
+    if (g.Dp == 256 && !pad) return launch_wave<4, DIRMASK, false, BWD, WTA>(ctx, p);
     return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "aggregate: experimental build (Dp = 256 only)");
 #else
     switch (g.Dp / 64) {
-    case 1: return pad ? launch_wave<1, DIRMASK, true, BWD>(ctx, p) : launch_wave<1, DIRMASK, false, BWD>(ctx, p);
-    case 2: return pad ? launch_wave<2, DIRMASK, true, BWD>(ctx, p) : launch_wave<2, DIRMASK, false, BWD>(ctx, p);
-    case 3: return pad ? launch_wave<3, DIRMASK, true, BWD>(ctx, p) : launch_wave<3, DIRMASK, false, BWD>(ctx, p);
-    case 4: return pad ? launch_wave<4, DIRMASK, true, BWD>(ctx, p) : launch_wave<4, DIRMASK, false, BWD>(ctx, p);
+    case 1: return pad ? launch_wave<1, DIRMASK, true, BWD, WTA>(ctx, p) : launch_wave<1, DIRMASK, false, BWD, WTA>(ctx, p);
+    case 2: return pad ? launch_wave<2, DIRMASK, true, BWD, WTA>(ctx, p) : launch_wave<2, DIRMASK, false, BWD, WTA>(ctx, p);
+    case 3: return pad ? launch_wave<3, DIRMASK, true, BWD, WTA>(ctx, p) : launch_wave<3, DIRMASK, false, BWD, WTA>(ctx, p);
+    case 4: return pad ? launch_wave<4, DIRMASK, true, BWD, WTA>(ctx, p) : launch_wave<4, DIRMASK, false, BWD, WTA>(ctx, p);
     }
     return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "aggregate: Dp=%d", g.Dp);
 #endif
@@ -912,7 +941,7 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
         p.f[f].bnd = bnd + bnd_sz * f;
     }
     p.ticket = ctl; p.progress = ctl + WAVE_CTL_PAD;
-    rc = g.mode == MVS_MODE_HH4 ? launch_wave_nw<0x5, false>(ctx, g, p) : launch_wave_nw<0xF, false>(ctx, g, p);
+    rc = g.mode == MVS_MODE_HH4 ? launch_wave_nw<0x5, false, false>(ctx, g, p) : launch_wave_nw<0xF, false, false>(ctx, g, p);
     if (rc) return rc;
     // backward sweep: the same recurrence on the image flipped in x and y; with the winner-take-all step inside, S is
     // not written again unless the caller wants to look at it
@@ -934,9 +963,10 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
 #ifdef WAVE_DBG_PROF
     p.prof = prof + 32 * 4;
 #endif
-    if (g.mode == MVS_MODE_HH) rc = launch_wave_nw<0xF, true>(ctx, g, p);
-    else if (g.mode == MVS_MODE_HH4) rc = launch_wave_nw<0x5, true>(ctx, g, p);
-    else rc = launch_wave_nw<0x1, true>(ctx, g, p);  // MODE_SGBM: only the (x+1, y) direction
+    if (!wta) rc = launch_wave_nw<0xF, true, false>(ctx, g, p);   // the CUDA_SGM strategy: all directions, its own winner rule afterwards
+    else if (g.mode == MVS_MODE_HH) rc = launch_wave_nw<0xF, true, true>(ctx, g, p);
+    else if (g.mode == MVS_MODE_HH4) rc = launch_wave_nw<0x5, true, true>(ctx, g, p);
+    else rc = launch_wave_nw<0x1, true, true>(ctx, g, p);  // MODE_SGBM: only the (x+1, y) direction
 #ifdef WAVE_DBG_PROF
     {
         unsigned long long h[2 * 32 * 4];

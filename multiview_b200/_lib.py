@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmvstereo.so")
+LIB_PATH = os.environ.get("MVS_LIB") or os.path.join(_HERE, "libmvstereo.so")   # MVS_LIB: a developer build of the same library
 
 c_int, c_size_t, c_void_p, c_double, c_float = C.c_int, C.c_size_t, C.c_void_p, C.c_double, C.c_float
 

@@ -383,6 +383,34 @@ __device__ __forceinline__ void wta_flush(const WaveFrame& fr, const WaveWta& w,
     fr.raw[(size_t)y * w.W + x + w.minX1] = (int16_t)(d + w.minD * 16);
 }
 
+// The long form of a pixel's two waits ("pixel written" by the row above, then "pixel consumed" by the row below), out of
+// line: the sweep loop first retries each test once with try_wait, which lets the hardware suspend the warp, and comes
+// here only when that was not enough.  Bounded in TIME: a wait that expires, here or anywhere else in the grid, raises the
+// error flag and ends all waiting (results are then invalid and the host reports an error), so a logic fault cannot
+// hang the GPU.  Returns true when waiting was abandoned.  `where`: ring row, band and pixel for the report.
+__device__ __noinline__ bool wave_wait_long(uint32_t bf, uint32_t pf, uint32_t okf, uint32_t bc, uint32_t pc, uint32_t okc, int* error, int where)
+{
+    unsigned long long t0 = 0;
+    int spins = 0;
+    for (;;) {
+        if (!okf) okf = mbar_try_wait(bf, pf);
+        if (okf && !okc) okc = mbar_try_wait(bc, pc);
+        if (okf && okc) return false;
+        if ((++spins & 127) == 0) {
+            if (*(volatile int*)error) return true;
+            const unsigned long long t = global_ns();
+            if (!t0) t0 = t;
+            else if (t - t0 > WAVE_TIMEOUT_NS) {
+                atomicCAS(error, 0, ((okf ? 2 : 1) << 28) | where);   // kind 1: "written", 2: "consumed"
+                return true;
+            }
+        }
+#if WAVE_CONS_SLEEP
+        if (okf) __nanosleep(WAVE_CONS_SLEEP);   // only the back-pressure wait is left: this warp is AHEAD of its consumer, so it
+#endif                                           // sleeps between polls and leaves the issue slots to the slower warps
+    }
+}
+
 template <int NW, int DIRMASK, bool PAD, bool BWD, bool WTA>
 __global__ void __launch_bounds__(Ring<NW>::THREADS, 1)
 wave_kernel(WaveParams p)
@@ -490,31 +518,13 @@ wave_kernel(WaveParams p)
 #endif
             }
         };
-        // the two waits of a pixel in one loop (one slow path per pixel in the unrolled body): okf / okc hold what the early
-        // tests saw and are left non-zero
-        auto wait_both = [&](uint32_t bf, uint32_t pf, uint32_t& okf, uint32_t bc, uint32_t pc, uint32_t& okc, int pixel) {
-            if (failed) { okf = okc = 1u; return; }
-            unsigned long long t0 = 0;
-            int spins = 0;
-            for (;;) {
-                if (!okf) okf = mbar_try_wait(bf, pf);
-                if (okf && !okc) okc = mbar_try_wait(bc, pc);
-                if (okf && okc) break;
-                if ((++spins & 127) == 0) {
-                    if (*(volatile int*)p.error) { failed = true; break; }
-                    const unsigned long long t = global_ns();
-                    if (!t0) t0 = t;
-                    else if (t - t0 > WAVE_TIMEOUT_NS) {
-                        atomicCAS(p.error, 0, ((okf ? 2 : 1) << 28) | ((r & 31) << 23) | ((band & 127) << 16) | (pixel & 0xffff));
-                        failed = true;
-                        break;
-                    }
-                }
-#if WAVE_CONS_SLEEP
-                if (okf) __nanosleep(WAVE_CONS_SLEEP);   // only the back-pressure wait is left: this warp is ahead
-#endif
-            }
-            okf = okc = 1u;
+        // the two waits of a pixel when the early tests have not both passed: one retry each with try_wait (the hardware may
+        // suspend the warp until the phase completes), then the long form.  okf / okc hold what the tests saw.
+        auto wait_both = [&](uint32_t bf, uint32_t pf, uint32_t okf, uint32_t bc, uint32_t pc, uint32_t okc, int pixel) {
+            if (!okf) okf = mbar_try_wait(bf, pf);
+            if (okf && !okc) okc = mbar_try_wait(bc, pc);
+            if (__builtin_expect((okf & okc) == 0u, 0) && !failed)
+                failed = wave_wait_long(bf, pf, okf, bc, pc, okc, p.error, ((r & 31) << 23) | ((band & 127) << 16) | (pixel & 0xffff));
         };
 
         // zero slots prepared before anybody runs: the row above the image, and "x = -1" of the row each warp reads

@@ -318,7 +318,7 @@ def run_ours(args, rank, world, local_rank):
     # ---- per-stage device times (CUDA events inside the library, on the launching stream) -----------------
     # (a) the batched step, as timed above: stage time / B = per camera-frame; the aggregation stage is 2 launches
     #     (forward + backward sweep) covering all B frames, so this is its per-launch duration inside the step
-    stages = ["rectify", "presmooth", "cost", "aggregate", "wta", "cloud", "hist"]
+    stages = ["rectify", "presmooth", "cost", "aggregate", "aggregate_fwd", "aggregate_bwd", "wta", "cloud", "hist"]
     acc = {s_: [] for s_ in stages}
     for _ in range(max(3, min(args.steps, 10))):
         api.frame_run_batch(ctx, 0, batch_dev)
@@ -326,7 +326,8 @@ def run_ours(args, rank, world, local_rank):
         for s_ in stages:
             acc[s_].append(ctx.stage_ms(s_))
     stage_ms = {s_: float(np.mean(v)) / B for s_, v in acc.items()}
-    stage_ms["wta+post"] = stage_ms.pop("wta")
+    stage_ms["lr_check+post"] = stage_ms.pop("wta")   # the winner-take-all step itself runs inside the backward sweep
+    sweep_ms = {"forward": stage_ms.pop("aggregate_fwd"), "backward_with_wta": stage_ms.pop("aggregate_bwd")}
     if not args.float_maps:   # the rectify stage when it converts the float maps in every frame
         batch_f = (api.FrameDesc * B)(*[descs_dev[b % len(descs_dev)] for b in range(B)])
         for b in range(B):
@@ -339,7 +340,7 @@ def run_ours(args, rank, world, local_rank):
                 racc.append(ctx.stage_ms("rectify"))
         stage_ms["rectify_float_maps"] = float(np.mean(racc)) / B
     # (b) one camera-frame alone (latency mode); the first two calls load the single-frame kernels and are not counted
-    acc1 = {s_: [] for s_ in stages + ["post"]}
+    acc1 = {s_: [] for s_ in stages + ["post"] if not s_.startswith("aggregate_")}
     for it in range(5):
         api.frame_run(ctx, 0, descs_dev[0])
         ctx.sync()
@@ -371,10 +372,12 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_src = peaks()
     agg_bytes = 8.0 * cells  # read C + write S forward, read C + read S backward
     achieved = agg_bytes / (stage_ms["aggregate"] / 1000.0) / 1e9
-    roofline = {"bound": "hbm", "kernel": f"wave_kernel: SGM aggregation, forward + backward sweep over the batch of {B} frames",
+    roofline = {"bound": "hbm", "kernel": f"wave_kernel: SGM aggregation, forward + backward sweep over the batch of {B} frames; the backward "
+                                          "sweep includes the winner-take-all step (SURVEY.md 8d counts no bytes for it: S stays in registers)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "algorithmic_bytes_per_frame": agg_bytes, "ms_per_frame": stage_ms["aggregate"], "peak_source": peak_src,
                 "frac_of_8TBs_nominal": achieved / 8000.0,
+                "sweeps": {k_: {"ms_per_frame": v_, "frac": 4.0 * cells / (v_ / 1000.0) / 1e9 / peak} for k_, v_ in sweep_ms.items()},
                 "single_frame": {"ms": stage_ms_single["aggregate"],
                                  "frac": agg_bytes / (stage_ms_single["aggregate"] / 1000.0) / 1e9 / peak}}
 

@@ -52,8 +52,7 @@ int mvs_sync(mvs_ctx* ctx);                     /* wait for the context's stream
 void* mvs_stream(mvs_ctx* ctx);                 /* the main cudaStream_t (stage entry points, first half of the frame path) */
 void* mvs_tail_stream(mvs_ctx* ctx);            /* the cudaStream_t the frame path finishes a batch on (left-right check ..
                                                    histogram, the histogram sums): work that consumes frame results is
-                                                   enqueued here.  In the default build it is the main stream itself; a
-                                                   build with -DMVS_TWO_STREAMS gives it a stream of its own */
+                                                   enqueued here */
 const char* mvs_version(void);
 long long mvs_launch_count(const mvs_ctx* ctx); /* kernels launched through this context so far */
 
@@ -162,9 +161,9 @@ int mvs_point_cloud(mvs_ctx* ctx, const mvs_bcam* bcam, const float* disp, size_
  *   - All pointers are DEVICE pointers supplied by the caller: disp_dev (w*h floats, tightly packed), Xs_dev
  *     (capacity w*h*3 doubles), xy_dev (capacity w*h*2 int32), lookup_dev (w*h int32), n_dev (one int32),
  *     centroid_dev (3 doubles).  The call is asynchronous on the context's MAIN stream, mvs_stream() (mvs_sync to
- *     wait).  Where mvs_tail_stream() differs from it (see there) that stream is not ordered behind the frame path's
- *     second half: a disparity taken from mvs_frame_result.disp_dev is produced on mvs_tail_stream(), so make the
- *     main stream wait for it first (an event recorded on the tail stream, or mvs_sync).
+ *     wait).  That stream is not ordered behind the frame path's second half: a disparity taken from
+ *     mvs_frame_result.disp_dev is produced on mvs_tail_stream(), so make the main stream wait for it first
+ *     (an event recorded on the tail stream, or mvs_sync).
  *   - It performs no cudaMalloc/cudaFree and calls nothing that allocates.  Its compaction scratch is a fixed
  *     288 KiB device array inside the library, resident on every GPU that loads the library until exit.
  *   - Limit: w*h <= MVS_STATIC_CLOUD_MAX_PIXELS (4096 x 2304); larger images return MVS_ERR_UNSUPPORTED and

@@ -910,11 +910,15 @@ static int launch_wave_nw(mvs_ctx* ctx, const SgbmGeom& g, const WaveParams& p)
     if (g.Dp == 256 && !pad) return launch_wave<4, DIRMASK, false, BWD, WTA>(ctx, p);
     return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "aggregate: experimental build (Dp = 256 only)");
 #else
-    switch (g.Dp / 64) {
-    case 1: return pad ? launch_wave<1, DIRMASK, true, BWD, WTA>(ctx, p) : launch_wave<1, DIRMASK, false, BWD, WTA>(ctx, p);
-    case 2: return pad ? launch_wave<2, DIRMASK, true, BWD, WTA>(ctx, p) : launch_wave<2, DIRMASK, false, BWD, WTA>(ctx, p);
-    case 3: return pad ? launch_wave<3, DIRMASK, true, BWD, WTA>(ctx, p) : launch_wave<3, DIRMASK, false, BWD, WTA>(ctx, p);
-    case 4: return pad ? launch_wave<4, DIRMASK, true, BWD, WTA>(ctx, p) : launch_wave<4, DIRMASK, false, BWD, WTA>(ctx, p);
+    if constexpr (WTA) {   // the winner-take-all step is in the sweep at 256 disparities only (sgbm_wta_in_sweep)
+        if (g.Dp == 256) return pad ? launch_wave<4, DIRMASK, true, BWD, true>(ctx, p) : launch_wave<4, DIRMASK, false, BWD, true>(ctx, p);
+    } else {
+        switch (g.Dp / 64) {
+        case 1: return pad ? launch_wave<1, DIRMASK, true, BWD, false>(ctx, p) : launch_wave<1, DIRMASK, false, BWD, false>(ctx, p);
+        case 2: return pad ? launch_wave<2, DIRMASK, true, BWD, false>(ctx, p) : launch_wave<2, DIRMASK, false, BWD, false>(ctx, p);
+        case 3: return pad ? launch_wave<3, DIRMASK, true, BWD, false>(ctx, p) : launch_wave<3, DIRMASK, false, BWD, false>(ctx, p);
+        case 4: return pad ? launch_wave<4, DIRMASK, true, BWD, false>(ctx, p) : launch_wave<4, DIRMASK, false, BWD, false>(ctx, p);
+        }
     }
     return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "aggregate: Dp=%d", g.Dp);
 #endif
@@ -951,7 +955,9 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
         p.f[f].bnd = bnd + bnd_sz * f;
     }
     p.ticket = ctl; p.progress = ctl + WAVE_CTL_PAD;
+    stage_begin(ctx, "aggregate_fwd");
     rc = g.mode == MVS_MODE_HH4 ? launch_wave_nw<0x5, false, false>(ctx, g, p) : launch_wave_nw<0xF, false, false>(ctx, g, p);
+    stage_end(ctx, "aggregate_fwd");
     if (rc) return rc;
     // backward sweep: the same recurrence on the image flipped in x and y; with the winner-take-all step inside, S is
     // not written again unless the caller wants to look at it
@@ -973,10 +979,11 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
 #ifdef WAVE_DBG_PROF
     p.prof = prof + 32 * 4;
 #endif
-    if (!wta) rc = launch_wave_nw<0xF, true, false>(ctx, g, p);   // the CUDA_SGM strategy: all directions, its own winner rule afterwards
-    else if (g.mode == MVS_MODE_HH) rc = launch_wave_nw<0xF, true, true>(ctx, g, p);
-    else if (g.mode == MVS_MODE_HH4) rc = launch_wave_nw<0x5, true, true>(ctx, g, p);
-    else rc = launch_wave_nw<0x1, true, true>(ctx, g, p);  // MODE_SGBM: only the (x+1, y) direction
+    stage_begin(ctx, "aggregate_bwd");
+    if (g.mode == MVS_MODE_HH) rc = wta ? launch_wave_nw<0xF, true, true>(ctx, g, p) : launch_wave_nw<0xF, true, false>(ctx, g, p);
+    else if (g.mode == MVS_MODE_HH4) rc = wta ? launch_wave_nw<0x5, true, true>(ctx, g, p) : launch_wave_nw<0x5, true, false>(ctx, g, p);
+    else rc = wta ? launch_wave_nw<0x1, true, true>(ctx, g, p) : launch_wave_nw<0x1, true, false>(ctx, g, p);  // MODE_SGBM: only the (x+1, y) direction
+    stage_end(ctx, "aggregate_bwd");
 #ifdef WAVE_DBG_PROF
     {
         unsigned long long h[2 * 32 * 4];

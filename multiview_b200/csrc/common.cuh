@@ -177,8 +177,14 @@ int sgbm_aggregate_wave_status(mvs_ctx* ctx, cudaStream_t stream = nullptr);  //
 struct SgbmWtaOut {
     int16_t* raw[MVS_MAX_BATCH];
     uint32_t* disp2key[MVS_MAX_BATCH];
+    int16_t* S[MVS_MAX_BATCH];   // the aggregated volumes (final only when !in_sweep or store_S)
+    bool in_sweep;               // the backward sweep did the winner-take-all step (sgbm_wta_in_sweep)
+    int sset;                    // buffer set (0 or 1) of raw / disp2key and, when !in_sweep, of S
     bool store_S;
 };
+// where the winner-take-all step runs: inside the backward sweep at 256 disparities, as its own kernel below (wta_post.cu)
+static inline bool sgbm_wta_in_sweep(const SgbmGeom& g) { return g.Dp == 256; }
+int sgbm_wta_from_s_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const SgbmWtaOut& wta);
 int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S, const SgbmWtaOut* wta);
 int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,
                              int16_t* const* disp16, int16_t* raw16_tap /* F == 1 only */);

@@ -95,14 +95,6 @@ extern "C" int mvs_ctx_create(int device, mvs_ctx** out)
               cudaEventCreateWithFlags(&ctx->ev_front_done, cudaEventDisableTiming) == cudaSuccess &&
               cudaEventCreateWithFlags(&ctx->ev_tail_done[0], cudaEventDisableTiming) == cudaSuccess &&
               cudaEventCreateWithFlags(&ctx->ev_tail_done[1], cudaEventDisableTiming) == cudaSuccess;
-#ifndef MVS_TWO_STREAMS
-    // The second half of a batch (left-right check .. histogram) follows the first on the SAME stream: since the
-    // winner-take-all step moved into the backward sweep that half is 8 % of a batch, and running it beside the next
-    // batch's cost kernels measured slower than running it alone (c2, batch 16: 31.5 ms per step on two streams, 30.5 ms
-    // on one).  Building with -DMVS_TWO_STREAMS gives the frame path its own tail stream again; the event plumbing in
-    // frame.cu serves both.
-    if (ok) { cudaStreamDestroy(ctx->tail_stream); ctx->tail_stream = ctx->stream; }
-#endif
     for (int i = 0; ok && i < MVS_MAX_SLOTS; ++i)
         ok = cudaEventCreateWithFlags(&ctx->ev_slot_done[i], cudaEventDisableTiming) == cudaSuccess &&
              cudaEventCreateWithFlags(&ctx->ev_slot_fetched[i], cudaEventDisableTiming) == cudaSuccess;
@@ -138,7 +130,7 @@ extern "C" void mvs_ctx_destroy(mvs_ctx* ctx)
     if (ctx->ev_front_done) cudaEventDestroy(ctx->ev_front_done);
     for (int i = 0; i < 2; ++i)
         if (ctx->ev_tail_done[i]) cudaEventDestroy(ctx->ev_tail_done[i]);
-    if (ctx->tail_stream && ctx->tail_stream != ctx->stream) cudaStreamDestroy(ctx->tail_stream);
+    if (ctx->tail_stream) cudaStreamDestroy(ctx->tail_stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;

@@ -61,6 +61,11 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     SgbmGeom g;
     int rc = sgbm_geom(ctx, &d0.sgbm, w, h, &g);
     if (rc) return rc;
+    // With the winner-take-all step inside the backward sweep (256 disparities) the second half of a batch is 8 % of it, and
+    // running it beside the next batch's cost kernels measured slower than running it alone (c2, batch 16: 31.5 against
+    // 30.5 ms per step): the batch then starts behind the previous batch's second half.  Narrower disparity ranges keep
+    // the overlap (their second half includes the winner-take-all kernel; 896x672x128: 8.5 against 8.8 ms per step).
+    if (sgbm_wta_in_sweep(g) && ctx->tail_done_recorded[ctx->s_set ^ 1]) MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_tail_done[ctx->s_set ^ 1], 0));
     // per-camera histograms of all slots live in one array so that the camera sum is one kernel
     // (slots filled with another histogram size index this array differently: they are no longer fetchable)
     for (int i = 0; i < MVS_MAX_SLOTS; ++i)
@@ -194,8 +199,8 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     {
         const uint8_t *l[MVS_MAX_BATCH], *r[MVS_MAX_BATCH];
         for (int f = 0; f < n_frames; ++f) { l[f] = sb[f].grey[0]; r[f] = sb[f].grey[1]; }
-        // first half on the main stream: cost volumes + aggregation (with the winner-take-all step) into buffer set `sset`, whose
-        // previous reader must be done
+        // first half on the main stream: cost volumes + aggregation into buffer set `sset` (S, or the outcome of the
+        // winner-take-all step when it runs inside the sweep), whose previous reader must be done
         sset = ctx->s_set;
         ctx->s_set ^= 1;
         if (ctx->tail_done_recorded[sset]) MVS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_tail_done[sset], 0));

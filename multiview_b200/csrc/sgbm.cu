@@ -40,20 +40,28 @@ int sgbm_front_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const ui
     int rc = sgbm_geom(ctx, p, w, h, &g);
     if (rc) return rc;
     int16_t *C[MVS_MAX_BATCH], *S[MVS_MAX_BATCH];
+    const bool in_sweep = sgbm_wta_in_sweep(g);
     for (int f = 0; f < F; ++f) {
         C[f] = sgbm_volume(ctx, fname("sgbm.C", f).c_str(), g);
-        S[f] = sgbm_volume(ctx, fname("sgbm.S", f).c_str(), g);
+        // S is read by the tail only when the winner-take-all step is not in the sweep: then it alternates with the set
+        S[f] = sgbm_volume(ctx, fname(sset && !in_sweep ? "sgbm.S1" : "sgbm.S", f).c_str(), g);
         if (!C[f] || !S[f]) return MVS_ERR_NOMEM;
     }
     stage_begin(ctx, "cost");
     rc = sgbm_cost_volume_batch_dev(ctx, g, F, l, r, C);
     stage_end(ctx, "cost");
     if (rc) return rc;
-    rc = sgbm_wta_buffers_dev(ctx, g, F, sset, wta);
-    if (rc) return rc;
+    if (in_sweep) {
+        rc = sgbm_wta_buffers_dev(ctx, g, F, sset, wta);
+        if (rc) return rc;
+    } else
+        memset(wta, 0, sizeof(*wta));
+    for (int f = 0; f < F; ++f) wta->S[f] = S[f];
+    wta->in_sweep = in_sweep;
+    wta->sset = sset;
     wta->store_S = keep_S;
     stage_begin(ctx, "aggregate");
-    rc = sgbm_aggregate_batch_dev(ctx, g, F, C, S, wta);
+    rc = sgbm_aggregate_batch_dev(ctx, g, F, C, S, in_sweep ? wta : nullptr);
     stage_end(ctx, "aggregate");
     return rc;
 }
@@ -64,9 +72,17 @@ int sgbm_tail_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, int w, in
     SgbmGeom g;
     int rc = sgbm_geom(ctx, p, w, h, &g);
     if (rc) return rc;
-    // F == 1: "wta" (left-right check) and "post" are timed separately; a batch times both under "wta"
-    if (F > 1) stage_begin(ctx, "wta");
-    rc = sgbm_lr_post_batch_dev(ctx, g, p, F, wta, disp16, F == 1 ? raw16_tap : nullptr);
+    // "wta": the winner-take-all step when it is not in the sweep + the left-right check; F == 1 times the rest separately
+    // as "post", a batch times everything under "wta"
+    stage_begin(ctx, "wta");
+    SgbmWtaOut wo = wta;
+    if (!wo.in_sweep) {
+        rc = sgbm_wta_buffers_dev(ctx, g, F, wta.sset, &wo);
+        for (int f = 0; f < F; ++f) wo.S[f] = wta.S[f];
+        if (!rc) rc = sgbm_wta_from_s_batch_dev(ctx, g, F, wo);
+        if (rc) return rc;
+    }
+    rc = sgbm_lr_post_batch_dev(ctx, g, p, F, wo, disp16, F == 1 ? raw16_tap : nullptr);
     if (F > 1) stage_end(ctx, "wta");
     return rc;
 }

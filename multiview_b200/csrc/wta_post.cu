@@ -1,12 +1,124 @@
-// a3 (vi)-(vii) and a4: right-view consistency check, 3x3 median, speckle filter and float conversion (reference call sites
+// a3 (v)-(vii) and a4: winner-take-all with uniqueness and parabola sub-pixel (the form that reads S from memory),
+// right-view consistency check, 3x3 median, speckle filter and float conversion (reference call sites
 // cost-functions/disparity/strategies/stereosgbm_disp.cpp:121-125 and :141-150).
 #include "common.cuh"
 
-// The winner-take-all step itself (first minimum, uniqueness, sub-pixel fit, right-view key) runs inside the backward
-// aggregation sweep (aggregate_wave.cu: wta_pixel / wta_flush) on the sums the sweep holds in registers.  disp2 (the
-// right-view disparity) is a per-row argmin with "first writer in descending x wins ties": realised there as atomicMin on
-// key = minS << 16 | (0xFFFF - x), from which the winning d follows as x + minX1 - x2 - minD (x2 = x + minX1 - d - minD),
-// so no second array is needed.  Here: the initial values, and the left-right check that reads the keys.
+// The winner-take-all step (first minimum, uniqueness, sub-pixel fit, right-view key) exists twice: at 256 disparities it
+// runs inside the backward aggregation sweep on the sums the sweep holds in registers (aggregate_wave.cu: wta_stage_a/b,
+// wta_flush), which saves writing S and reading it back; at narrower disparity ranges its per-pixel reductions would weigh
+// more than the sweep's own arithmetic (measured at 128 disparities: +0.08 ms per frame in the sweep against 0.06 ms here),
+// and the kernel below reads S instead.  Both write the same buffers (sgbm_wta_buffers_dev).
+// disp2 (the right-view disparity) is a per-row argmin with "first writer in descending x wins ties": realised as atomicMin
+// on key = minS << 16 | (0xFFFF - x), from which the winning d follows as x + minX1 - x2 - minD (x2 = x + minX1 - d -
+// minD), so no second array is needed.
+// ---- WTA from S in memory: one warp per pixel ------------------------------------------------------------------------
+#define WTA_PPW 8  // pixels per warp: their loads are issued together (memory-level parallelism), then processed in turn
+// ur_magic = ceil(2^32 / (100 - ur)) (0 when the divisor is 1): n / (100 - ur) == umulhi(n, ur_magic) for n < 2^25
+template <int NW>
+__global__ void __launch_bounds__(256)
+wta_kernel(const uint32_t* __restrict__ S, SgbmGeom g, uint32_t ur_magic, int16_t* __restrict__ raw, uint32_t* __restrict__ disp2key,
+           int* __restrict__ sat_flag)
+{
+    __shared__ __align__(16) uint32_t sh[8][NW * 32];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const long long npix = (long long)g.W1 * g.H;
+    const long long pix0 = ((long long)blockIdx.x * 8 + wib) * WTA_PPW;
+    if (pix0 >= npix) return;
+    uint32_t wall[WTA_PPW][NW];
+#pragma unroll
+    for (int q = 0; q < WTA_PPW; ++q) {
+        const long long pix = min(pix0 + q, npix - 1);
+        const uint32_t* Sp = S + (size_t)pix * (NW * 32) + lane * NW;
+        if (NW == 4) { uint4 v = __ldcs((const uint4*)Sp); wall[q][0] = v.x; wall[q][1 % NW] = v.y; wall[q][2 % NW] = v.z; wall[q][3 % NW] = v.w; }
+        else if (NW == 2) { uint2 v = __ldcs((const uint2*)Sp); wall[q][0] = v.x; wall[q][1 % NW] = v.y; }
+        else {
+#pragma unroll
+            for (int j = 0; j < NW; ++j) wall[q][j] = __ldcs(Sp + j);
+        }
+    }
+    // split layout (common.cuh): word w of a pixel holds disparity w (low half) and w + Dp/2 (high half)
+    constexpr uint32_t HALF = NW * 32;
+    uint32_t padbits[NW];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+        const uint32_t d0 = (uint32_t)(lane * NW + j);
+        padbits[j] = (d0 >= (uint32_t)g.D ? 0xffffu : 0u) | (d0 + HALF >= (uint32_t)g.D ? 0xffff0000u : 0u);
+    }
+    auto hw_index = [](int d) -> int { return d >= (int)HALF ? 2 * (d - (int)HALF) + 1 : 2 * d; };  // halfword of disparity d in the staged copy
+    uint32_t* mysh = sh[wib];
+    uint16_t* hw = (uint16_t*)mysh;
+    // lane q keeps the outcome of pixel q; the divisions, the atomic and the store happen once per warp at the end
+    int my_best = -1, my_minS = 0, my_sm = 0, my_sp = 0;
+#pragma unroll
+    for (int q = 0; q < WTA_PPW; ++q) {
+        if (pix0 + q >= npix) break;
+        const uint32_t (&w)[NW] = wall[q];
+        // first argmin: min over (S << 16 | d); padding (d >= D) holds 32767 and never beats a real minimum below it
+        uint32_t key = 0xffffffffu;
+        __syncwarp();  // the previous pixel's staged copy has been read by every lane
+#pragma unroll
+        for (int j = 0; j < NW; ++j) {
+            const uint32_t d0 = (uint32_t)(lane * NW + j);
+            key = min(key, min(w[j] * 65536u + d0, (w[j] & 0xffff0000u) | (d0 + HALF)));
+            // staged copy for the uniqueness test: padding is taken out of it (0xFFFF never counts)
+            mysh[lane * NW + j] = w[j] | padbits[j];
+        }
+        key = __reduce_min_sync(0xffffffffu, key);
+        const int minS = (int)(key >> 16), best = (int)(key & 0xffffu);
+        // "minus (min Lp + P2)" form of the recurrence (g.K44 = directions * P2): S here is that form's S plus K44 wherever
+        // no sum saturated.  A saturated sum (32767 here, at least 32767 - K44 there) only matters where it takes part in a
+        // decision: as the minimum, as a neighbour of the minimum in the sub-pixel fit, or when the uniqueness threshold
+        // reaches it.  Those cases are reported (sat_flag), never guessed around; everywhere else the result is exact.
+        bool satp = false;
+        if (g.K44) {
+            uint32_t mx = 0;
+#pragma unroll
+            for (int j = 0; j < NW; ++j) mx = __vmaxu2(mx, w[j] & ~padbits[j]);
+            satp = __reduce_max_sync(0xffffffffu, max(mx & 0xffffu, mx >> 16)) >= 32767u;
+        }
+        if (minS >= 32767) {   // every cost saturated: the reference leaves / writes INV here
+            if (g.K44 && lane == 0) *sat_flag = 1;
+            continue;
+        }
+        __syncwarp();
+        // uniqueness: reject if some d outside best-1..best+1 has S*(100-ur) < minS*100, i.e. S <= thr.
+        // Lane q reads the two neighbours it needs for the sub-pixel fit, blanks best-1..best+1 in the staged copy,
+        // and the warp takes one packed minimum over what is left.
+        int sm = 0, sp = 0;
+        if (lane == q) {
+            if (best > 0) { sm = hw[hw_index(best - 1)]; hw[hw_index(best - 1)] = 0xffffu; }
+            if (best < g.D - 1) { sp = hw[hw_index(best + 1)]; hw[hw_index(best + 1)] = 0xffffu; }
+            hw[hw_index(best)] = 0xffffu;
+        }
+        __syncwarp();
+        uint32_t m = 0xffffffffu;
+#pragma unroll
+        for (int j = 0; j < NW; ++j) m = __vminu2(m, mysh[lane * NW + j]);
+        const uint32_t mn = __reduce_min_sync(0xffffffffu, min(m & 0xffffu, m >> 16));
+        // S(d) * (100 - ur) < minS * 100 in the reference's own S; with S' = S - K44 (the other form of the recurrence,
+        // K44 = 0 for OpenCV 4.13's form) that is S(d) * (100 - ur) < minS * 100 - K44 * ur on the S held here
+        const int rhs = minS * 100 - g.K44 * g.ur;
+        const uint32_t num = (uint32_t)(rhs - 1);
+        const uint32_t thr = rhs > 0 ? (ur_magic ? __umulhi(num, ur_magic) : num) : 0xffffffffu;  // ur <= 99 (mvs_sgbm_check)
+        if (satp && lane == q && ((rhs > 0 && thr >= 32767u) || (best > 0 && sm >= 32767) || (best < g.D - 1 && sp >= 32767))) *sat_flag = 1;
+        if (rhs > 0 && mn != 0xffffu && mn <= thr) continue;
+        if (lane == q) { my_best = best; my_minS = minS; my_sm = sm; my_sp = sp; }
+    }
+    if (lane < WTA_PPW && my_best >= 0) {
+        int y = (int)(pix0 / g.W1), x = (int)(pix0 - (long long)y * g.W1) + lane;
+        while (x >= g.W1) { x -= g.W1; ++y; }
+        const int x2 = x + g.minX1 - my_best - g.minD;
+        atomicMin(disp2key + (size_t)y * g.W + x2, ((uint32_t)my_minS << 16) | (uint32_t)(0xffff - x));
+        int d = my_best;
+        if (0 < d && d < g.D - 1) {
+            int den = max(my_sm + my_sp - 2 * my_minS, 1);
+            d = d * 16 + ((my_sm - my_sp) * 16 + den) / (den * 2);
+        } else
+            d *= 16;
+        raw[(size_t)y * g.W + x + g.minX1] = (int16_t)(d + g.minD * 16);
+    }
+}
+
 __device__ __forceinline__ void wta_init_body(int16_t* raw, uint32_t* disp2key, size_t n, int inv)
 {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -232,9 +344,32 @@ int sgbm_wta_buffers_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, int sset, SgbmW
     return MVS_OK;
 }
 
+// The winner-take-all step from S volumes in memory (the form used below 256 disparities), one launch per frame.
+int sgbm_wta_from_s_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const SgbmWtaOut& wta)
+{
+    cudaStream_t s = ctx->stream;
+    MVS_ARENA(ctx, int, sat, "sgbm.sat44", 1);
+    const int blocks = cdiv((long long)g.W1 * g.H, 8 * WTA_PPW);
+    const uint32_t udiv = (uint32_t)(100 - g.ur);
+    const uint32_t ur_magic = udiv <= 1 ? 0u : (uint32_t)(((1ull << 32) + udiv - 1) / udiv);
+    for (int f = 0; f < F; ++f) {
+        const uint32_t* S = (const uint32_t*)wta.S[f];
+        switch (g.Dp / 64) {
+        case 1: wta_kernel<1><<<blocks, 256, 0, s>>>(S, g, ur_magic, wta.raw[f], wta.disp2key[f], sat); break;
+        case 2: wta_kernel<2><<<blocks, 256, 0, s>>>(S, g, ur_magic, wta.raw[f], wta.disp2key[f], sat); break;
+        case 3: wta_kernel<3><<<blocks, 256, 0, s>>>(S, g, ur_magic, wta.raw[f], wta.disp2key[f], sat); break;
+        case 4: wta_kernel<4><<<blocks, 256, 0, s>>>(S, g, ur_magic, wta.raw[f], wta.disp2key[f], sat); break;
+        default: return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "wta: Dp=%d", g.Dp);
+        }
+        MVS_LAUNCH_CHECK(ctx, "wta_kernel");
+    }
+    return MVS_OK;
+}
+
 // Left-right check + median + speckle filter for the F frames of a batch whose raw disparities and right-view keys the
 // backward sweep has written (buffers of sgbm_wta_buffers_dev): the small per-image kernels run once per batch
-// (blockIdx.z = frame).  raw16_tap (F == 1): copy of the raw disparities after the left-right check.
+// (blockIdx.z = frame).  raw16_tap (F == 1): copy of the raw disparities after the left-right check.  The caller has opened
+// the stage timer "wta"; with F == 1 it is closed behind the left-right check and the rest is timed as "post".
 int sgbm_lr_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_params* p, int F, const SgbmWtaOut& wta, int16_t* const* disp16,
                            int16_t* raw16_tap)
 {
@@ -245,7 +380,6 @@ int sgbm_lr_post_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, const mvs_sgbm_param
     PostBatch b;
     memset(&b, 0, sizeof(b));
     for (int f = 0; f < F; ++f) b.disp16[f] = disp16[f];
-    if (F == 1) stage_begin(ctx, "wta");
     lr_check_batch_kernel<<<dim3(cdiv(g.W1, 128), g.H, F), 128, 0, s>>>(raw, d2, g);
     MVS_LAUNCH_CHECK(ctx, "lr_check_batch_kernel");
     if (raw16_tap) MVS_CUDA(ctx, cudaMemcpyAsync(raw16_tap, raw, n * sizeof(int16_t), cudaMemcpyDeviceToDevice, s));

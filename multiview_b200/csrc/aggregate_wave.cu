@@ -27,14 +27,18 @@
 // Data movement:
 //   * L0 stays in registers; L1/L2/L3 of the row above come from shared-memory rings (8 / 8 / WAVE_D3 pixels deep,
 //     plain vectors, no headers) written by warp r-1;
-//   * C (and S in the backward sweep) are loaded straight into registers WAVE_PF pixels ahead (one 16-byte load per
-//     lane and pixel), S is stored from registers: no shared-memory staging, so the rings get all of it;
+//   * C (and S in the backward sweep) are loaded straight into registers a few pixels ahead (one 16-byte load per lane and
+//     pixel), S is stored from registers: no shared-memory staging, so the rings get all of it.  Every second trip a warp
+//     also asks L2 for the lines eight pixels ahead: all loads of a warp complete through one hardware scoreboard, so a
+//     prefetched register is only usable once the YOUNGEST load has landed, and that age is what the L2 hit has to fit in
+//     (see the refill in the sweep loop);
 //   * the pixel loop is unrolled by four: slot offsets, barrier addresses and global offsets are immediates (plus a
 //     per-trip base that selects the half of the eight-deep rings);
 //   * neighbouring warps are coupled only by mbarriers: per ring row eight "pixel p written" and eight "pixel p
 //     consumed" barriers (index p mod 8, phase parity (p / 8) & 1; producer and consumer are never eight pixels
-//     apart, so a parity is never ambiguous).  arrive has release and try_wait acquire semantics at CTA scope: no
-//     memory fence is issued and a waiting warp is suspended by the hardware.  No CTA-wide barrier inside a band;
+//     apart, so a parity is never ambiguous).  arrive has release and test_wait / try_wait acquire semantics at CTA
+//     scope: no memory fence is issued.  A pixel's barriers are probed one pixel early (test_wait, in a predicate); a
+//     failed probe is retried with try_wait, which lets the hardware suspend the warp.  No CTA-wide barrier inside a band;
 //   * image borders need no branches: the slots "x = -1" and "x = W1" are zero vectors (Lr = 0, minLr = 0 outside
 //     the image, as the reference initialises its Lr buffers; a zero vector is its own normalised form);
 //   * bands are chained through global memory: the last warp of a band streams its vectors to a boundary buffer and
@@ -42,7 +46,9 @@
 //     the boundary row into ring row 0 with cp.async a few pixels ahead of its consumer;
 //   * a launch covers a batch of frames; (frame, band) items are handed out by an atomic ticket in dependency
 //     order, so the band a CTA waits for is always running or finished (no co-residency assumption); every wait
-//     is bounded in TIME and raises an error flag instead of hanging.
+//     is bounded in TIME and raises an error flag instead of hanging;
+//   * at 256 disparities the backward sweep also does the winner-take-all step of cv::StereoSGBM on the sums it holds in
+//     registers (wta_stage_a / wta_stage_b / wta_flush below): S is then neither written by it nor read back.
 #include "common.cuh"
 
 #define SENT2 0x7FFF7FFFu
@@ -78,7 +84,10 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #endif
 #ifndef WAVE_PUBLISH
 #define WAVE_PUBLISH 16      // a band's last row publishes its progress every this many pixels (a power of two >= 4;
-#endif                       // measured: 8 and 32 are slower)
+#endif                       // measured with the GPU full, c2 batch 16: 8 and 32 are slower)
+#ifndef WAVE_PUBLISH_FEW
+#define WAVE_PUBLISH_FEW 4   // the same when a launch has no more (frame, band) items than SMs: the sweep is then bound by the
+#endif                       // latency of the chain of bands (c2: one frame 6.9 -> 6.1 ms, two frames 3.5 -> 3.1 ms per frame)
 #ifndef WAVE_HELPER_LAG
 #define WAVE_HELPER_LAG 3    // boundary copies in flight in the helper warp (4 measured the same, 5 stalls)
 #endif
@@ -120,6 +129,7 @@ struct WaveParams {
     int* error;            // set when a bounded wait expires
     int W1, H, D, P1, P2, nbands, F;
     uint32_t one;          // 1, opaque to the compiler (see WAVE_FMA_ADDS)
+    int publish_mask;      // a band's last row publishes its progress every publish_mask + 1 pixels (a power of two >= 4)
     WaveWta wta;
 #ifdef WAVE_DBG_PROF       // developer build: per-row clock counts {row total, waiting for the row above, waiting for the row below, slow paths}
     unsigned long long* prof;
@@ -828,7 +838,7 @@ wave_kernel(WaveParams p)
                         if (to_ring) stw<NW>((RG::D3 == 8 ? wrc : wr) + RG::O3 + k * WPP, l[3]);
                         if (to_global) stg_stream<NW>(gout + (k * 3 + 2) * WPP, l[3]);
                     }
-                    if (to_global && ((k == UN - 1 && ((x + 1) & (WAVE_PUBLISH - 1)) == 0) || k + 1 == rem)) {
+                    if (to_global && ((k == UN - 1 && ((x + 1) & p.publish_mask) == 0) || k + 1 == rem)) {
                         // the warp barrier orders every lane's boundary stores before lane 0's release store
                         // (release is cumulative over what the warp barrier made visible to lane 0)
                         __syncwarp();
@@ -941,6 +951,7 @@ int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16
     WaveParams p;
     memset(&p, 0, sizeof(p));
     p.error = err; p.F = F; p.one = 1u;
+    p.publish_mask = (F * nbands <= ctx->sm_count ? WAVE_PUBLISH_FEW : WAVE_PUBLISH) - 1;
     p.W1 = g.W1; p.H = g.H; p.D = g.D; p.P1 = g.P1; p.P2 = g.P2; p.nbands = nbands;
     MVS_CUDA(ctx, cudaMemsetAsync(ctl, 0, sizeof(int) * 2 * ctl_pass, ctx->stream));
     int rc;

@@ -526,6 +526,37 @@ def test_sgbm_older_recurrence_form(ctx, params):
         assert differs > 0   # the two forms do disagree (uniqueness test) on these inputs: the switch is not a no-op
 
 
+@pytest.mark.parametrize("params", [
+    dict(block=3, p1=8, p2=32, ur=10, d12=1, sw=0, sr=0),
+    dict(block=7, p1=22, p2=1000, ur=3, d12=596, sw=0, sr=0),
+    dict(block=13, p1=22, p2=1000, ur=25, d12=1, sw=50, sr=2),
+])
+@pytest.mark.parametrize("D", [256, 208])
+def test_sgbm_older_recurrence_form_in_sweep(ctx, params, D):
+    """The same switch at 256 disparities (and 208, padded to 256), where the winner-take-all step runs inside the backward
+    sweep: its uniqueness test and its report of a saturated sum are the ones exercised here."""
+    W, H = D + 150, 40
+    exact = 0
+    try:
+        assert ctx.lib.mvs_set_sgbm_recurrence(ctx.h, 1) == 0
+        for mode in (1, 0, 3):
+            for noise in (False, True):
+                L, R = _pair(W, H, D, 11 + mode, noise)
+                sp = _sp(D, mode, **params)
+                got = np.empty((H, W), np.int16)
+                rc = ctx.lib.mvs_sgbm_compute16(ctx.h, ctypes.byref(sp.to_c()), L.ctypes.data, R.ctypes.data, W, H, W, got.ctypes.data, 2 * W)
+                if rc == -3 and b"saturated" in ctx.lib.mvs_last_error(ctx.h):
+                    continue   # reported, no result claimed
+                assert rc == 0
+                exact += 1
+                want = oracle.sgbm_compute(_op(sp), L, R, subtract_p2=True)
+                assert np.array_equal(got, want), f"mode {mode}: {(got != want).sum()} px differ"
+        if params["block"] <= 7:
+            assert exact >= 3
+    finally:
+        assert ctx.lib.mvs_set_sgbm_recurrence(ctx.h, 0) == 0
+
+
 @pytest.mark.parametrize("W,H,D,dtype", [(192, 96, 64, np.uint8), (320, 120, 128, np.uint16), (384, 130, 256, np.uint8),
                                          (330, 98, 256, np.uint16)])
 def test_census_sgm_strategy(ctx, W, H, D, dtype):

@@ -34,6 +34,7 @@ WORKLOADS = {  # name -> (W, H, D); c1..c4 are BASELINE.json configs[0..3], the 
     "720p128": (1280, 720, 128),
     "1440p256": (2560, 1440, 256),
     "4k256": (3840, 2160, 256),
+    "1080p192": (1920, 1080, 192),   # not a BASELINE config: the one disparity width (Dp = 192) the others do not exercise
 }
 C4_CAMS, C4_FRAMES, C4_FRAMES_PER_STEP = 16, 300, 2   # a c4 step = 2 frame times of all 16 cameras = 32 camera-frames, whatever N is
 METRIC = "stereo frames/s (rectify+SGM+cloud+floor_hist)"

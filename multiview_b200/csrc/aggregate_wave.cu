@@ -47,7 +47,7 @@
 //   * a launch covers a batch of frames; (frame, band) items are handed out by an atomic ticket in dependency
 //     order, so the band a CTA waits for is always running or finished (no co-residency assumption); every wait
 //     is bounded in TIME and raises an error flag instead of hanging;
-//   * at 256 disparities the backward sweep also does the winner-take-all step of cv::StereoSGBM on the sums it holds in
+//   * from 192 disparities (sgbm_wta_in_sweep) the backward sweep also does the winner-take-all step of cv::StereoSGBM on the sums it holds in
 //     registers (wta_stage_a / wta_stage_b / wta_flush below): S is then neither written by it nor read back.
 #include "common.cuh"
 
@@ -57,13 +57,13 @@
 #define WAVE_R4 15           // Dp = 256: 16 warps
 #endif
 #ifndef WAVE_R3
-#define WAVE_R3 19           // Dp = 192: 20 warps
+#define WAVE_R3 15           // Dp = 192: 16 warps (measured at 1920x1080x192, ms per frame: 11 rows 1.155, 15 1.023, 19 1.042, 23 1.151)
 #endif
 #ifndef WAVE_R2
-#define WAVE_R2 27           // Dp = 128: 28 warps
+#define WAVE_R2 19           // Dp = 128: 20 warps (measured at 896x672x128, ms per frame: 11 rows 0.287, 15 0.243, 17 0.251, 19 0.234, 23 0.251, 27 0.287, 31 0.340)
 #endif
 #ifndef WAVE_R1
-#define WAVE_R1 15           // Dp = 64: 16 warps
+#define WAVE_R1 19           // Dp = 64: 20 warps (measured at 640x480x64, ms per frame: 15 rows 0.132, 19 0.126, 23 0.126, 27 0.138, 31 0.152)
 #endif
 template <int NW> struct WaveRows { static constexpr int R = NW == 4 ? WAVE_R4 : NW == 3 ? WAVE_R3 : NW == 2 ? WAVE_R2 : WAVE_R1; };
 static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw == 2 ? WAVE_R2 : WAVE_R1; }
@@ -916,12 +916,16 @@ template <int DIRMASK, bool BWD, bool WTA>
 static int launch_wave_nw(mvs_ctx* ctx, const SgbmGeom& g, const WaveParams& p)
 {
     bool pad = g.Dp != g.D;
-#ifdef WAVE_ONLY_NW4   // quick experimental builds
+#if defined(WAVE_ONLY_NW4)   // quick experimental builds
     if (g.Dp == 256 && !pad) return launch_wave<4, DIRMASK, false, BWD, WTA>(ctx, p);
     return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "aggregate: experimental build (Dp = 256 only)");
+#elif defined(WAVE_ONLY_NW)
+    if (g.Dp == 64 * WAVE_ONLY_NW && !pad && !WTA) return launch_wave<WAVE_ONLY_NW, DIRMASK, false, BWD, false>(ctx, p);
+    return mvs_fail(ctx, MVS_ERR_UNSUPPORTED, "aggregate: experimental build (one Dp only)");
 #else
-    if constexpr (WTA) {   // the winner-take-all step is in the sweep at 256 disparities only (sgbm_wta_in_sweep)
+    if constexpr (WTA) {   // the winner-take-all step is in the sweep for the wide disparity ranges only (sgbm_wta_in_sweep)
         if (g.Dp == 256) return pad ? launch_wave<4, DIRMASK, true, BWD, true>(ctx, p) : launch_wave<4, DIRMASK, false, BWD, true>(ctx, p);
+        if (g.Dp == 192) return pad ? launch_wave<3, DIRMASK, true, BWD, true>(ctx, p) : launch_wave<3, DIRMASK, false, BWD, true>(ctx, p);
     } else {
         switch (g.Dp / 64) {
         case 1: return pad ? launch_wave<1, DIRMASK, true, BWD, false>(ctx, p) : launch_wave<1, DIRMASK, false, BWD, false>(ctx, p);

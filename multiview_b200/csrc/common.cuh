@@ -182,8 +182,11 @@ struct SgbmWtaOut {
     int sset;                    // buffer set (0 or 1) of raw / disp2key and, when !in_sweep, of S
     bool store_S;
 };
-// where the winner-take-all step runs: inside the backward sweep at 256 disparities, as its own kernel below (wta_post.cu)
-static inline bool sgbm_wta_in_sweep(const SgbmGeom& g) { return g.Dp == 256; }
+// where the winner-take-all step runs: inside the backward sweep from 192 disparities (Dp), as its own kernel below that (wta_post.cu)
+#ifndef MVS_WTA_IN_SWEEP_FROM
+#define MVS_WTA_IN_SWEEP_FROM 192
+#endif
+static inline bool sgbm_wta_in_sweep(const SgbmGeom& g) { return g.Dp >= MVS_WTA_IN_SWEEP_FROM; }
 int sgbm_wta_from_s_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const SgbmWtaOut& wta);
 int sgbm_aggregate_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const int16_t* const* C, int16_t* const* S, const SgbmWtaOut* wta);
 int sgbm_compute16_batch_dev(mvs_ctx* ctx, const mvs_sgbm_params* p, int F, const uint8_t* const* l, const uint8_t* const* r, int w, int h,

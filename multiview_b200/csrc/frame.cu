@@ -61,7 +61,7 @@ extern "C" int mvs_frame_run_batch(mvs_ctx* ctx, int first_slot, const mvs_frame
     SgbmGeom g;
     int rc = sgbm_geom(ctx, &d0.sgbm, w, h, &g);
     if (rc) return rc;
-    // With the winner-take-all step inside the backward sweep (256 disparities) the second half of a batch is 8 % of it, and
+    // With the winner-take-all step inside the backward sweep (from 192 disparities) the second half of a batch is 8 % of it, and
     // running it beside the next batch's cost kernels measured slower than running it alone (c2, batch 16: 31.5 against
     // 30.5 ms per step): the batch then starts behind the previous batch's second half.  Narrower disparity ranges keep
     // the overlap (their second half includes the winner-take-all kernel; 896x672x128: 8.5 against 8.8 ms per step).

@@ -3,7 +3,7 @@
 // cost-functions/disparity/strategies/stereosgbm_disp.cpp:121-125 and :141-150).
 #include "common.cuh"
 
-// The winner-take-all step (first minimum, uniqueness, sub-pixel fit, right-view key) exists twice: at 256 disparities it
+// The winner-take-all step (first minimum, uniqueness, sub-pixel fit, right-view key) exists twice: from 192 disparities it
 // runs inside the backward aggregation sweep on the sums the sweep holds in registers (aggregate_wave.cu: wta_stage_a/b,
 // wta_flush), which saves writing S and reading it back; at narrower disparity ranges its per-pixel reductions would weigh
 // more than the sweep's own arithmetic (measured at 128 disparities: +0.08 ms per frame in the sweep against 0.06 ms here),
@@ -344,7 +344,7 @@ int sgbm_wta_buffers_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, int sset, SgbmW
     return MVS_OK;
 }
 
-// The winner-take-all step from S volumes in memory (the form used below 256 disparities), one launch per frame.
+// The winner-take-all step from S volumes in memory (the form used up to 128 disparities), one launch per frame.
 int sgbm_wta_from_s_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const SgbmWtaOut& wta)
 {
     cudaStream_t s = ctx->stream;

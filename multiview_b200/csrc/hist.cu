@@ -105,8 +105,8 @@ floor_hist_kernel(HistArgs a, const double* __restrict__ Xs, const int32_t* __re
 //   (1) key (bin or label) and values per point, in parallel; rejected points and points past N get the key `nkeys`;
 //   (2) a STABLE least-significant-digit radix sort of the point indices by key (8 bits per pass, two passes for up to
 //       65535 keys): stability keeps the point order inside a key;
-//   (3) the values gathered into sorted order, segment bounds per key, and one thread per key adding its segment up
-//       front to back (independent loads eight deep, one dependent float add per element).
+//   (3) the values gathered into sorted order, segment bounds per key, and one warp per key adding its segment up
+//       front to back (coalesced loads, one dependent float add per element).
 #define RS_THREADS 256
 #define RS_ROWS 16                         // 32-item rows per warp
 #define RS_TILE (RS_THREADS * RS_ROWS)     // items per block
@@ -126,34 +126,54 @@ rs_count_kernel(const uint32_t* __restrict__ keys, int n, int shift, int nblk, i
     __syncthreads();
     cnt[threadIdx.x * nblk + blockIdx.x] = h[threadIdx.x];
 }
-// exclusive scan of cnt (digit-major, so digit d of block b starts after every smaller digit and after digit d of the
-// blocks before b): one block
-__global__ void __launch_bounds__(1024)
-rs_scan_kernel(int* __restrict__ cnt, int m)
+// exclusive scan of cnt in two levels (cnt is digit-major: digit d of block b starts after every smaller digit and after
+// digit d of the blocks before b): block d scans the counts of digit d over the sort's blocks and writes the digit's total
+// to tot[d]; the scatter kernel adds the exclusive scan of the 256 totals itself
+__global__ void __launch_bounds__(512)
+rs_scan_digit_kernel(int* __restrict__ cnt, int nblk, int* __restrict__ tot)
 {
-    __shared__ int part[1024];
-    const int per = (m + 1023) / 1024, i0 = threadIdx.x * per, i1 = min(i0 + per, m);
-    int s = 0;
-    for (int i = i0; i < i1; ++i) s += cnt[i];
-    part[threadIdx.x] = s;
-    __syncthreads();
-    for (int d = 1; d < 1024; d <<= 1) {   // inclusive Hillis-Steele scan of the partial sums
-        int v = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+    __shared__ int part[512];
+    int* row = cnt + (size_t)blockIdx.x * nblk;
+    int carry = 0;
+    for (int b0 = 0; b0 < nblk; b0 += 512) {
+        const int b = b0 + threadIdx.x;
+        const int c = b < nblk ? row[b] : 0;
+        part[threadIdx.x] = c;
         __syncthreads();
-        part[threadIdx.x] += v;
+        for (int d = 1; d < 512; d <<= 1) {   // inclusive Hillis-Steele scan
+            const int v = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+            __syncthreads();
+            part[threadIdx.x] += v;
+            __syncthreads();
+        }
+        if (b < nblk) row[b] = carry + part[threadIdx.x] - c;
+        carry += part[511];
         __syncthreads();
     }
-    int run = part[threadIdx.x] - s;
-    for (int i = i0; i < i1; ++i) { int c = cnt[i]; cnt[i] = run; run += c; }
+    if (threadIdx.x == 0) tot[blockIdx.x] = carry;
 }
 // stable scatter of (key, value) by the digit; vals_in == nullptr means the identity (the first pass sorts indices)
 __global__ void __launch_bounds__(RS_THREADS)
 rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, int n, int shift, int nblk,
-                  const int* __restrict__ offs, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out)
+                  const int* __restrict__ offs, const int* __restrict__ tot, uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out)
 {
     __shared__ int wcnt[RS_THREADS / 32][256];
+    __shared__ int dbase[256];   // exclusive scan of the digit totals
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (int k = threadIdx.x; k < (RS_THREADS / 32) * 256; k += RS_THREADS) (&wcnt[0][0])[k] = 0;
+    {   // RS_THREADS == 256: thread d holds digit d's total; warp scans, then the warp totals
+        static_assert(RS_THREADS == 256, "one thread per digit");
+        const int t = tot[threadIdx.x];
+        int v = t;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += u; }
+        __shared__ int wtot[8];
+        if (lane == 31) wtot[w] = v;
+        __syncthreads();
+        int before = 0;
+        for (int ww = 0; ww < w; ++ww) before += wtot[ww];
+        dbase[threadIdx.x] = before + v - t;
+    }
     __syncthreads();
     const int base = blockIdx.x * RS_TILE + w * (RS_ROWS * 32);   // a warp owns RS_ROWS consecutive rows of 32 items
     // per-warp digit counts
@@ -166,7 +186,7 @@ rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
     }
     __syncthreads();
     {   // digit threadIdx.x: running start of every warp
-        int run = offs[threadIdx.x * nblk + blockIdx.x];
+        int run = dbase[threadIdx.x] + offs[threadIdx.x * nblk + blockIdx.x];
         for (int ww = 0; ww < RS_THREADS / 32; ++ww) { int c = wcnt[ww][threadIdx.x]; wcnt[ww][threadIdx.x] = run; run += c; }
     }
     __syncthreads();
@@ -189,7 +209,7 @@ rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restri
 
 // sorted point indices by key: perm (and the sorted keys) in `keys` / `perm` on return; tmp buffers of n each
 static int stable_sort_by_key(mvs_ctx* ctx, uint32_t* keys, uint32_t* perm, uint32_t* keys_tmp, uint32_t* perm_tmp, int n, int nkeys,
-                              int* cnt /* 256 * nblk */)
+                              int* cnt /* 256 * nblk + 256 */)
 {
     cudaStream_t s = ctx->stream;
     const int nblk = cdiv(n, RS_TILE);
@@ -200,8 +220,8 @@ static int stable_sort_by_key(mvs_ctx* ctx, uint32_t* keys, uint32_t* perm, uint
     uint32_t *kout = keys_tmp, *vout = perm_tmp;
     for (int p = 0; p < passes; ++p) {
         rs_count_kernel<<<nblk, RS_THREADS, 0, s>>>(kin, n, 8 * p, nblk, cnt);
-        rs_scan_kernel<<<1, 1024, 0, s>>>(cnt, 256 * nblk);
-        rs_scatter_kernel<<<nblk, RS_THREADS, 0, s>>>(kin, vin, n, 8 * p, nblk, cnt, kout, vout);
+        rs_scan_digit_kernel<<<256, 512, 0, s>>>(cnt, nblk, cnt + (size_t)256 * nblk);
+        rs_scatter_kernel<<<nblk, RS_THREADS, 0, s>>>(kin, vin, n, 8 * p, nblk, cnt, cnt + (size_t)256 * nblk, kout, vout);
         MVS_LAUNCH_CHECK_N(ctx, "stable radix sort pass", 3);
         kin = kout; vin = vout;
         kout = kout == keys_tmp ? keys : keys_tmp;
@@ -254,42 +274,55 @@ __global__ void gather_f4_kernel(const float4* __restrict__ v, const uint32_t* _
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j < n) out[j] = v[perm[j]];
 }
-// cam_hist(x, y) += weight in point order: one thread per bin, loads eight deep, one dependent add per element
-__global__ void hist_ordered_sum_kernel(const float* __restrict__ w, const int* __restrict__ seg, int nbins, float* __restrict__ hist)
+// cam_hist(x, y) += weight in point order: one WARP per bin.  The lanes load 32 consecutive weights of the bin's segment
+// at once (the next 32 are already on their way), then every lane adds them up in order from shuffled copies: the sum is
+// the reference's sequential float sum, the loads are coalesced, and a crowded bin costs its length in dependent adds, not in
+// memory latencies.
+__global__ void __launch_bounds__(256)
+hist_ordered_sum_kernel(const float* __restrict__ w, const int* __restrict__ seg, int nbins, float* __restrict__ hist)
 {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (b >= nbins) return;
     float s = 0.0f;   // cam_hist.fill(0.0f), floor-histogram.cpp:200
-    int j = seg[b];
-    const int j1 = seg[b + 1];
-    for (; j + 8 <= j1; j += 8) {
-        float v[8];
+    const int j0 = seg[b], j1 = seg[b + 1];
+    float next = j0 + lane < j1 ? w[j0 + lane] : 0.0f;
+    for (int j = j0; j < j1; j += 32) {
+        const float v = next;
+        next = j + 32 + lane < j1 ? w[j + 32 + lane] : 0.0f;
+        const int cnt = min(32, j1 - j);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = w[j + k];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s += v[k];
+        for (int k = 0; k < 32; ++k) {
+            const float t = __shfl_sync(0xffffffffu, v, k);
+            if (k < cnt) s += t;
+        }
     }
-    for (; j < j1; ++j) s += w[j];
-    hist[b] = s;
+    if (lane == 0) hist[b] = s;
 }
 // slic_to_hist_xy: per super-pixel, in point order, sC += Vector4f(Yf * wf, sC.w + wf)  -- as written in the reference,
 // the fourth component doubles at every point (floor-histogram.cpp:270-272) -- then the cell of the centroid (:277-285)
-__global__ void slic_cells_kernel(const float4* __restrict__ c, const int* __restrict__ seg, int n_labels, double left, double top,
-                                  double hist_sz, mvs_sparse_hist_cell* __restrict__ out)
+__global__ void __launch_bounds__(256)
+slic_cells_kernel(const float4* __restrict__ c, const int* __restrict__ seg, int n_labels, double left, double top,
+                  double hist_sz, mvs_sparse_hist_cell* __restrict__ out)
 {
-    const int l = blockIdx.x * blockDim.x + threadIdx.x;
+    // one warp per super-pixel, like hist_ordered_sum_kernel: coalesced loads, the sums in point order from shuffled copies
+    const int l = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (l >= n_labels) return;
     float sx = 0.0f, sy = 0.0f, sz = 0.0f, sw = 0.0f;
-    int j = seg[l];
-    const int j1 = seg[l + 1];
-    for (; j + 4 <= j1; j += 4) {
-        float4 v[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) v[k] = c[j + k];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { sx += v[k].x; sy += v[k].y; sz += v[k].z; sw += sw + v[k].w; }
+    const int j0 = seg[l], j1 = seg[l + 1];
+    const float4 zero = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    float4 next = j0 + lane < j1 ? c[j0 + lane] : zero;
+    for (int j = j0; j < j1; j += 32) {
+        const float4 v = next;
+        next = j + 32 + lane < j1 ? c[j + 32 + lane] : zero;
+        const int cnt = min(32, j1 - j);
+#pragma unroll 8
+        for (int k = 0; k < 32; ++k) {
+            const float tx = __shfl_sync(0xffffffffu, v.x, k), ty = __shfl_sync(0xffffffffu, v.y, k);
+            const float tz = __shfl_sync(0xffffffffu, v.z, k), tw = __shfl_sync(0xffffffffu, v.w, k);
+            if (k < cnt) { sx += tx; sy += ty; sz += tz; sw += sw + tw; }
+        }
     }
-    for (; j < j1; ++j) { const float4 v = c[j]; sx += v.x; sy += v.y; sz += v.z; sw += sw + v.w; }
+    if (lane != 0) return;
     mvs_sparse_hist_cell cell = {-1, -1, 0.0f};   // SparseHistCell{{-1, -1}, 0}
     if (sw != 0.0f) {
         const double cx = (double)sx / (double)sw, cy = (double)sy / (double)sw;
@@ -333,7 +366,7 @@ static int floor_hist_ordered_dev(mvs_ctx* ctx, const HistArgs& a, const double*
     MVS_ARENA(ctx, uint32_t, keys, "hist.ordered.keys", (size_t)cap * 4);       // bins | tmp | labels | tmp
     MVS_ARENA(ctx, uint32_t, perm, "hist.ordered.perm", (size_t)cap * 2);       // perm | tmp
     MVS_ARENA(ctx, float, wts, "hist.ordered.weights", (size_t)cap * 2);        // weights | sorted weights
-    MVS_ARENA(ctx, int, cnt, "hist.ordered.cnt", (size_t)256 * nblk);
+    MVS_ARENA(ctx, int, cnt, "hist.ordered.cnt", (size_t)256 * nblk + 256);
     const int nk = max(nbins, cells ? a.n_labels : 0);
     MVS_ARENA(ctx, int, seg, "hist.ordered.seg", (size_t)nk + 2);
     float4* c4 = nullptr;
@@ -350,7 +383,7 @@ static int floor_hist_ordered_dev(mvs_ctx* ctx, const HistArgs& a, const double*
         if (rc) return rc;
         gather_f1_kernel<<<cdiv(cap, 256), 256, 0, s>>>(wts, perm, cap, wts + cap);
         seg_bounds_kernel<<<cdiv(cap, 256), 256, 0, s>>>(bins, cap, nbins, seg);
-        hist_ordered_sum_kernel<<<cdiv(nbins, 128), 128, 0, s>>>(wts + cap, seg, nbins, cam_hist);
+        hist_ordered_sum_kernel<<<cdiv(nbins, 8), 256, 0, s>>>(wts + cap, seg, nbins, cam_hist);
         MVS_LAUNCH_CHECK_N(ctx, "ordered histogram kernels", 3);
     }
     if (cells && a.n_labels > 0) {
@@ -358,7 +391,7 @@ static int floor_hist_ordered_dev(mvs_ctx* ctx, const HistArgs& a, const double*
         if (rc) return rc;
         gather_f4_kernel<<<cdiv(cap, 256), 256, 0, s>>>(c4, perm, cap, c4 + cap);
         seg_bounds_kernel<<<cdiv(cap, 256), 256, 0, s>>>(lkeys, cap, a.n_labels, seg);
-        slic_cells_kernel<<<cdiv(a.n_labels, 128), 128, 0, s>>>(c4 + cap, seg, a.n_labels, a.aabb[0], a.aabb[1], a.hist_sz, cells);
+        slic_cells_kernel<<<cdiv(a.n_labels, 8), 256, 0, s>>>(c4 + cap, seg, a.n_labels, a.aabb[0], a.aabb[1], a.hist_sz, cells);
         MVS_LAUNCH_CHECK_N(ctx, "super-pixel table kernels", 3);
     }
     return MVS_OK;

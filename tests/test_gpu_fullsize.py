@@ -80,10 +80,13 @@ def test_frame_path_matches_cv2_and_oracle_at_baseline_sizes(ctx, W, H, D):
     lab, still = _labels_and_still(W, H, 7)
     hp0 = api.FloorHistogramParams(weighting=api.WGT_NONE, apply_slic_still_weights=False)
     hp1 = api.FloorHistogramParams(weighting=api.WGT_NORM, apply_slic_still_weights=True, ordered=True)
+    # three frames: at c2 the launch then has more (frame, band) items than SMs, which is the regime of the benchmark (the
+    # sweeps publish their progress every 16 pixels there, every 4 in an underfilled launch: both are compared with cv2)
     descs = [api.make_frame_desc(cam, sp, hp0, synth.HIST_AABB),
-             api.make_frame_desc(cam, sp, hp1, synth.HIST_AABB, slic_lookup=lab, still_score=still)]
+             api.make_frame_desc(cam, sp, hp1, synth.HIST_AABB, slic_lookup=lab, still_score=still),
+             api.make_frame_desc(cam, sp, hp0, synth.HIST_AABB)]
     res = api.frame_run_batch(ctx, 0, descs)
-    outs = api.frame_fetch_batch(ctx, 0, 2, W, H, res[0].hw, res[0].hh)
+    outs = api.frame_fetch_batch(ctx, 0, 3, W, H, res[0].hw, res[0].hh)
     rect = [cv2ref.remap_cubic_bgr8(cam["sensor"][i], cam["mapx"][i], cam["mapy"][i]) for i in range(2)]
     want_d = cv2ref.disparity_calculate(oracle.SgbmParams.reference_defaults(D, 1), rect[0], rect[1], 2.15)
     ob = oracle.Bcam()

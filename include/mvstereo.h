@@ -123,9 +123,10 @@ int mvs_disparity_sgbm(mvs_ctx* ctx, const mvs_sgbm_params* p, double presmooth_
  * Hamming cost, 8 paths with P1 = 20 / P2 = 100, left / right winner with uniqueness 0.95, 3x3 median, left-right check;
  * disparities are stored + 1, 0 = invalid, values > 512 -> 0.  l, r: grey images of depth_bits 8 or 16 (use_16bit_greyscale,
  * sgm_disp.hpp:19-20), byte step `step`; disparity_size 64, 128 or 256; w and h even; out: CV_32FC1.  disp_tap (may be
- * NULL): the 16-bit disparity image before the float conversion.  Parity UNPINNED: bit-exact with the CPU restatement of
- * the vendored libSGM kernels (oracle/census_oracle.c, which lists where those kernels' artefacts are not reproduced); no
- * runnable libSGM or test vector exists to pin it against. */
+ * NULL): the 16-bit disparity image before the float conversion.  Bit-exact with the CPU restatement of the vendored libSGM
+ * kernels (oracle/census_oracle.c, which lists where those kernels' border artefacts are not reproduced); the restatement is
+ * pinned against those kernels themselves, compiled from the reference tree and run on the GPU, at disparity sizes 64 and 128
+ * (tests/test_gpu_census_ref.py); at 256 -- un-vendored libSGM 2.x in the reference -- nothing runnable exists to pin it. */
 int mvs_disparity_census(mvs_ctx* ctx, const void* l, const void* r, int depth_bits, int w, int h, size_t step,
                          int disparity_size, float* out, size_t ostep, uint16_t* disp_tap);
 

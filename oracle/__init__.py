@@ -119,18 +119,21 @@ def sgbm_compute(p: SgbmParams, L: np.ndarray, R: np.ndarray, taps: bool = False
     return disp
 
 
-def census_sgm(left: np.ndarray, right: np.ndarray, disparity_size: int = 256, taps: bool = False):
-    """The reference's CUDA_SGM strategy (sgm_disp.cpp:102-211 over the vendored libSGM kernels), restated; PARITY UNPINNED
-    (see census_oracle.c).  left / right: uint8 or uint16 grey (H, W).  Returns the float disparity, or a dict with taps."""
+def census_sgm(left: np.ndarray, right: np.ndarray, disparity_size: int = 256, taps: bool = False, vendored_edges: bool = False):
+    """The reference's CUDA_SGM strategy (sgm_disp.cpp:102-211 over the vendored libSGM kernels), restated (see
+    census_oracle.c).  vendored_edges: reproduce the vendored kernels' neighbour substitution at d = 0 / D-1 (64 and 128
+    disparities; the form pinned against oracle/_ref/libsgm_ref.so).  left / right: uint8 or uint16 grey (H, W).  Returns
+    the float disparity, or a dict with taps."""
     assert left.dtype == right.dtype and left.dtype in (np.uint8, np.uint16) and left.shape == right.shape
     left, right = np.ascontiguousarray(left), np.ascontiguousarray(right)
     H, W = left.shape
     out = np.empty((H, W), np.float32)
     S = np.empty((H, W, disparity_size), np.uint16) if taps else None
     d = np.empty((H, W), np.uint16) if taps else None
-    rc = lib().orc_census_sgm(_p(left), _p(right), 16 if left.dtype == np.uint16 else 8, W, H, disparity_size, _p(out), _p(S), _p(d))
+    rc = lib().orc_census_sgm_ex(_p(left), _p(right), 16 if left.dtype == np.uint16 else 8, W, H, disparity_size, _p(out), _p(S), _p(d),
+                                 1 if vendored_edges else 0)
     if rc:
-        raise RuntimeError(f"orc_census_sgm rc={rc}")
+        raise RuntimeError(f"orc_census_sgm_ex rc={rc}")
     return {"disp": out, "S": S, "disp16": d} if taps else out
 
 

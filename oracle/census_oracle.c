@@ -12,10 +12,12 @@
  *   median_filter.cu:24-32      NPP 3x3 median with anchor (0, 0) on both disparity images
  *   check_consistency.cu:20-35  left-right check (uses the +1 disparities as they are), source pixel 0 masks
  *
- * PARITY UNPINNED.  The vendored snapshot supports 64 / 128 disparities only while the reference calls it with 256
- * through an un-vendored libSGM 2.x (run.sh:86,182-184), it cannot run without a GPU, and the reference holds no test
- * vector for it.  Where the vendored kernels' behaviour is an artefact rather than an algorithm, this restatement takes
- * the plain reading and says so:
+ * PARITY: pinned against the vendored kernels themselves at 64 / 128 disparities -- oracle/Makefile builds them from the
+ * reference tree into oracle/_ref/libsgm_ref.so and tests/test_gpu_census_ref.py runs them on the GPU beside this file
+ * (orc_census_sgm_ex with vendored_edges = 1: bit-exact away from the image borders).  At 256 disparities, which the
+ * reference reaches through an un-vendored libSGM 2.x (run.sh:86,182-184), nothing runnable exists: unpinned there.
+ * Where the vendored kernels' behaviour is an artefact rather than an algorithm, this restatement (with vendored_edges = 0,
+ * the form the product implements) takes the plain reading and says so:
  *   - census descriptors of border pixels are never written there (uninitialised device memory): 0 here;
  *   - at d = 0 and d = D-1 the vendored path step substitutes an in-range neighbour that comes from a lane shuffle not
  *     wrapping (L[1] / L[D-2] in the 64 variant, L[3] / L[D-4] in the 128 variant, scan_scost.cu:81-82,158-159): no
@@ -56,14 +58,17 @@ static void census(const void* img, int depth_bits, int w, int h, uint64_t* out)
 
 static int popc64(uint64_t v) { return __builtin_popcountll(v); }
 
-/* one path step; Lp has D entries; returns min over d of the new L */
-static int path_step(const uint8_t* C, const uint16_t* Lp, int minLp, int D, uint16_t* Lo)
+/* one path step; Lp has D entries; returns min over d of the new L.  edge > 0 (the vendored kernels' edge artefact, see the
+ * header): d = 0 takes Lp[edge] as its "d - 1" neighbour and d = D-1 takes Lp[D-1-edge] as its "d + 1" neighbour. */
+static int path_step(const uint8_t* C, const uint16_t* Lp, int minLp, int D, uint16_t* Lo, int edge)
 {
     int mn = 1 << 30;
     for (int d = 0; d < D; ++d) {
         int v = Lp[d];
         if (d > 0 && Lp[d - 1] + CEN_P1 < v) v = Lp[d - 1] + CEN_P1;
         if (d < D - 1 && Lp[d + 1] + CEN_P1 < v) v = Lp[d + 1] + CEN_P1;
+        if (edge > 0 && d == 0 && Lp[edge] + CEN_P1 < v) v = Lp[edge] + CEN_P1;
+        if (edge > 0 && d == D - 1 && Lp[D - 1 - edge] + CEN_P1 < v) v = Lp[D - 1 - edge] + CEN_P1;
         if (minLp + CEN_P2 < v) v = minLp + CEN_P2;
         const int L = C[d] + v - minLp;
         Lo[d] = (uint16_t)L;
@@ -121,9 +126,23 @@ static void median3_anchor0(const uint16_t* src, int w, int h, uint16_t* dst)
 
 /* Returns 0 on success.  left/right: grey images (8 or 16 bit, packed w x h); out: float w x h.
  * S_tap (optional): the aggregated volume [h][w][D] uint16; disp_tap (optional): uint16 disparity + 1 after the checks. */
+int orc_census_sgm_ex(const void* left, const void* right, int depth_bits, int w, int h, int D, float* out, uint16_t* S_tap,
+                      uint16_t* disp_tap, int vendored_edges);
 int orc_census_sgm(const void* left, const void* right, int depth_bits, int w, int h, int D, float* out, uint16_t* S_tap,
                    uint16_t* disp_tap)
 {
+    return orc_census_sgm_ex(left, right, depth_bits, w, h, D, out, S_tap, disp_tap, 0);
+}
+/* vendored_edges != 0 (disparity sizes 64 and 128, the two the vendored snapshot has): the path step reproduces the
+ * vendored kernels' neighbour substitution at d = 0 and d = D-1 (scan_scost.cu:81-82,158-159: Lp[1] / Lp[D-2] in the 64
+ * variant, Lp[3] / Lp[D-4] in the 128 variant).  With it the restatement is PINNED against those kernels run on the GPU
+ * (oracle/_ref/libsgm_ref.so, tests/test_gpu_census_ref.py: bit-exact away from the image borders); without it it is the
+ * plain reading the product implements.  The two differ by that one rule. */
+int orc_census_sgm_ex(const void* left, const void* right, int depth_bits, int w, int h, int D, float* out, uint16_t* S_tap,
+                      uint16_t* disp_tap, int vendored_edges)
+{
+    const int edge = !vendored_edges ? 0 : D == 64 ? 1 : D == 128 ? 3 : -1;
+    if (edge < 0) return -1;
     if ((depth_bits != 8 && depth_bits != 16) || (D != 64 && D != 128 && D != 256) || w <= 8 || h <= 6 || (w & 1) || (h & 1)) return -1;
     const size_t n = (size_t)w * h;
     uint64_t* cl = (uint64_t*)malloc(n * 8);
@@ -152,7 +171,7 @@ int orc_census_sgm(const void* left, const void* right, int depth_bits, int w, i
                 int minLp = 0;
                 for (int x = sx, y = sy; x >= 0 && x < w && y >= 0 && y < h; x += dx, y += dy) {
                     const size_t o = ((size_t)y * w + x) * D;
-                    minLp = path_step(C + o, Lp, minLp, D, Ln);
+                    minLp = path_step(C + o, Lp, minLp, D, Ln, edge);
                     for (int d = 0; d < D; ++d) S[o + d] = (uint16_t)(S[o + d] + Ln[d]);
                     uint16_t* t = Lp; Lp = Ln; Ln = t;
                 }

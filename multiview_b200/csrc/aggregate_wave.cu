@@ -43,7 +43,8 @@
 //     the image, as the reference initialises its Lr buffers; a zero vector is its own normalised form);
 //   * bands are chained through global memory: the last warp of a band streams its vectors to a boundary buffer and
 //     publishes its progress every WAVE_PUBLISH pixels; a helper warp of the next band waits for that progress and copies
-//     the boundary row into ring row 0 with cp.async a few pixels ahead of its consumer;
+//     the boundary row into ring row 0 with bulk asynchronous copies (cp.async.bulk, completing on the pixel's "written"
+//     mbarrier) as far ahead of its consumer as the ring allows;
 //   * a launch covers a batch of frames; (frame, band) items are handed out by an atomic ticket in dependency
 //     order, so the band a CTA waits for is always running or finished (no co-residency assumption); every wait
 //     is bounded in TIME and raises an error flag instead of hanging;
@@ -88,9 +89,6 @@ static int wave_rows(int nw) { return nw == 4 ? WAVE_R4 : nw == 3 ? WAVE_R3 : nw
 #ifndef WAVE_PUBLISH_FEW
 #define WAVE_PUBLISH_FEW 4   // the same when a launch has no more (frame, band) items than SMs: the sweep is then bound by the
 #endif                       // latency of the chain of bands (c2: one frame 6.9 -> 6.1 ms, two frames 3.5 -> 3.1 ms per frame)
-#ifndef WAVE_HELPER_LAG
-#define WAVE_HELPER_LAG 3    // boundary copies in flight in the helper warp (4 measured the same, 5 stalls)
-#endif
 #ifndef WAVE_DEFER_LAST
 #define WAVE_DEFER_LAST 1    // the prefetch slot of a trip's last pixel is loaded inside the same trip (see the refill in the sweep loop)
 #endif
@@ -205,14 +203,16 @@ __device__ __forceinline__ void early_read(uint32_t& full_passed, uint32_t& cons
 {
     asm volatile("selp.u32 %0, 1, 0, wave_pf; selp.u32 %1, 1, 0, wave_pc;" : "=r"(full_passed), "=r"(cons_passed)::"memory");
 }
-__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gmem)
+// bulk asynchronous copy global -> shared (this GPU's memory only, no multicast) that reports its bytes to an mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t smem_addr, const void* gmem, uint32_t bytes, uint32_t bar)
 {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gmem) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr), "l"(gmem), "r"(bytes),
+                 "r"(bar) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t saddr, uint32_t bytes)
+{
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1; }" ::"r"(saddr), "r"(bytes) : "memory");
+}
 template <int NW>
 __device__ __forceinline__ void ldw(const uint32_t* p, uint32_t (&w)[NW])
 {
@@ -549,47 +549,55 @@ wave_kernel(WaveParams p)
 
         if (helper) {
             if (VERT && !first_band) {  // (first band: everything above the image is zero, warp 0 does not wait)
-                // boundary row of the previous band -> ring row 0, a few pixels ahead of publication
+                // boundary row of the previous band -> ring row 0, as far ahead of warp 0 as the ring allows.  Lane 0 moves a
+                // pixel's vectors with bulk asynchronous copies that report their bytes to the pixel's "written" barrier: the
+                // barrier's phase completes when the data has landed, nobody has to wait for the copies and arrive for them.
                 int seen = 0;
-                constexpr int HL = WAVE_HELPER_LAG;   // copy groups in flight behind the newest one
-                for (int xp = 0; xp <= W1 + HL; ++xp) {
-                    if (xp <= W1) {
-                        // the slots of pixel xp last held pixels xp - 8 (L1: read by warp 0 at its pixel xp - 7) and xp - D3
-                        // (L3: read at xp - D3 - 1)
-                        if (xp > WAVE_WAR) wait_bar(cons_s + (uint32_t)((xp - WAVE_WAR - 1) & 7) * 8u, (uint32_t)((xp - WAVE_WAR - 1) >> 3) & 1u, 2, xp);
-                        if (xp < W1) {
-                            const int need = xp + 1;
-                            if (seen < need && !failed) {
-                                unsigned long long t0 = 0;
-                                int spins = 0;
-                                while ((seen = ld_acquire(prev_progress)) < need) {
-                                    if ((++spins & 255) == 0) {
-                                        if (*(volatile int*)p.error) { failed = true; break; }
-                                        const unsigned long long t = global_ns();
-                                        if (!t0) t0 = t;
-                                        else if (t - t0 > WAVE_TIMEOUT_NS) { atomicCAS(p.error, 0, (3 << 28) | ((band & 127) << 16) | (xp & 0xffff)); failed = true; break; }
-                                    }
-                                    __nanosleep(32);
+                // (the zero slots above were written with ordinary stores; the copies write the same ring through the
+                // asynchronous proxy)
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                constexpr uint32_t VEC = WPP * 4u;
+                constexpr uint32_t NVEC = ((DIRMASK >> 1) & 1) + ((DIRMASK >> 2) & 1) + ((DIRMASK >> 3) & 1);
+                for (int xp = 0; xp <= W1; ++xp) {
+                    // the slots of pixel xp last held pixels xp - 8 (L1: read by warp 0 at its pixel xp - 7) and xp - D3
+                    // (L3: read at xp - D3 - 1)
+                    if (xp > WAVE_WAR) wait_bar(cons_s + (uint32_t)((xp - WAVE_WAR - 1) & 7) * 8u, (uint32_t)((xp - WAVE_WAR - 1) >> 3) & 1u, 2, xp);
+                    const uint32_t bar = full_s + (uint32_t)(xp & 7) * 8u;
+                    if (xp < W1) {
+                        const int need = xp + 1;
+                        if (seen < need && !failed) {
+                            unsigned long long t0 = 0;
+                            int spins = 0;
+                            while ((seen = ld_acquire(prev_progress)) < need) {
+                                if ((++spins & 255) == 0) {
+                                    if (*(volatile int*)p.error) { failed = true; break; }
+                                    const unsigned long long t = global_ns();
+                                    if (!t0) t0 = t;
+                                    else if (t - t0 > WAVE_TIMEOUT_NS) { atomicCAS(p.error, 0, (3 << 28) | ((band & 127) << 16) | (xp & 0xffff)); failed = true; break; }
                                 }
+                                __nanosleep(32);
                             }
+                            // the other band wrote these vectors with ordinary stores; the copies below read them through the
+                            // asynchronous proxy
+                            asm volatile("fence.proxy.async.global;" ::: "memory");
+                        }
+                        if (lane == 0) {
                             const uint32_t* src = bin + (size_t)xp * 3 * WPP;
+                            mbar_arrive_expect_tx(bar, NVEC * VEC);
 #pragma unroll
                             for (int dir = 1; dir <= 3; ++dir) {
                                 if (!(DIRMASK & (1 << dir))) continue;
                                 const int depth = dir == 3 ? RG::D3 : RG::D12;
-                                const uint32_t dst = ring_s + (uint32_t)(((dir - 1) * RG::D12 + (xp & (depth - 1))) * WPP) * 4u;
-                                if (lane < WPP / 4) cp_async16(dst + lane * 16, src + (dir - 1) * WPP + lane * 4);
+                                bulk_g2s(ring_s + (uint32_t)(((dir - 1) * RG::D12 + (xp & (depth - 1))) * WPP) * 4u, src + (dir - 1) * WPP, VEC, bar);
                             }
-                        } else if (DIRMASK & 8) {  // xp == W1: the zero vector behind the last pixel (direction 3 of warp 0's last pixel)
+                        }
+                    } else {   // xp == W1: the zero vector behind the last pixel (direction 3 of warp 0's last pixel)
+                        if (DIRMASK & 8) {
                             uint32_t* dst = ring + RG::O3 + (xp & (RG::D3 - 1)) * WPP;
                             for (int k = lane; k < WPP; k += 32) dst[k] = 0;
                         }
-                    }
-                    cp_async_commit();
-                    cp_async_wait<HL>();  // the group of pixel xp - HL has landed
-                    if (xp >= HL) {
-                        __syncwarp();  // all lanes' copies are in; lane 0 publishes pixel xp - HL
-                        if (lane == 0) mbar_arrive(full_s + (uint32_t)((xp - HL) & 7) * 8u);
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(bar);
                     }
                 }
             }
@@ -654,6 +662,10 @@ wave_kernel(WaveParams p)
 #endif
             // Barrier tests for the coming pixel are issued one pixel early (their ~90 cycles of latency overlap the
             // arithmetic); a direction that has nothing to wait for counts as passed.  Pixel 0 starts untested.
+            // Ring row 0 of a chained band is filled by bulk copies, which complete in any order: a pixel's code waits for the
+            // NEXT pixel's barrier only (for the rows written by a warp that implies the pixel itself), so pixel 0's own barrier
+            // is awaited here, once.
+            if (VERT && r == 0 && !first_band) wait_bar(my_full, 0u, 1, 0);
             early_set(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
             early_row(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
 #ifdef WAVE_DBG_PROF
@@ -891,7 +903,6 @@ wave_kernel(WaveParams p)
                 if (lane == 0) mbar_arrive(dn_full + (uint32_t)(W1 & 7) * 8u);
             }
         }
-        cp_async_wait<0>();
     }
 }
 

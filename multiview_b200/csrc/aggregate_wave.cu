@@ -591,6 +591,9 @@ wave_kernel(WaveParams p)
                                 bulk_g2s(ring_s + (uint32_t)(((dir - 1) * RG::D12 + (xp & (depth - 1))) * WPP) * 4u, src + (dir - 1) * WPP, VEC, bar);
                             }
                         }
+                        // Bulk copies complete in any order, and warp 0 waits for the NEXT pixel's barrier only (for the rows
+                        // written by a warp that implies the pixel itself): pixel 0 has landed before pixel 1 is asked for.
+                        if (xp == 0) wait_bar(bar, 0u, 1, 0);
                     } else {   // xp == W1: the zero vector behind the last pixel (direction 3 of warp 0's last pixel)
                         if (DIRMASK & 8) {
                             uint32_t* dst = ring + RG::O3 + (xp & (RG::D3 - 1)) * WPP;
@@ -662,10 +665,6 @@ wave_kernel(WaveParams p)
 #endif
             // Barrier tests for the coming pixel are issued one pixel early (their ~90 cycles of latency overlap the
             // arithmetic); a direction that has nothing to wait for counts as passed.  Pixel 0 starts untested.
-            // Ring row 0 of a chained band is filled by bulk copies, which complete in any order: a pixel's code waits for the
-            // NEXT pixel's barrier only (for the rows written by a warp that implies the pixel itself), so pixel 0's own barrier
-            // is awaited here, once.
-            if (VERT && r == 0 && !first_band) wait_bar(my_full, 0u, 1, 0);
             early_set(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
             early_row(wait_above ? 0u : 1u, to_ring ? 0u : 1u);
 #ifdef WAVE_DBG_PROF

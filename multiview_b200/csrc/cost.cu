@@ -70,24 +70,57 @@ __device__ __forceinline__ int pre_q(const uint8_t* __restrict__ r, int x, int W
     return (x <= 0 || x >= W - 1) ? ftzero : (int)r[x];
 }
 
+// Four pixels per thread: the six p / q values it needs (x0 - 1 .. x0 + 4) come from eight columns of three rows read once,
+// and every plane gets one 4-byte store (when the image width is a multiple of four; byte stores otherwise).
 __device__ __forceinline__ void prefilter_body(const uint8_t* __restrict__ img, int W, int H, int ftzero, uint8_t* __restrict__ planes)
 {
-    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
-    if (x >= W) return;
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y;
+    if (x0 >= W) return;
     const uint8_t* r = img + (size_t)y * W;
     const uint8_t* n = y > 0 ? r - W : r;
     const uint8_t* s = y < H - 1 ? r + W : r;
-    size_t plane = (size_t)W * H, o = (size_t)y * W + x;
-    int pc = pre_p(r, n, s, x, W, ftzero), qc = pre_q(r, x, W, ftzero);
-    int pl = pc, pr = pc, ql = qc, qr = qc;
-    if (x > 0) { pl = (pc + pre_p(r, n, s, x - 1, W, ftzero)) >> 1; ql = (qc + pre_q(r, x - 1, W, ftzero)) >> 1; }
-    if (x < W - 1) { pr = (pc + pre_p(r, n, s, x + 1, W, ftzero)) >> 1; qr = (qc + pre_q(r, x + 1, W, ftzero)) >> 1; }
-    planes[o] = (uint8_t)pc;
-    planes[plane + o] = (uint8_t)min(pc, min(pl, pr));
-    planes[2 * plane + o] = (uint8_t)max(pc, max(pl, pr));
-    planes[3 * plane + o] = (uint8_t)qc;
-    planes[4 * plane + o] = (uint8_t)min(qc, min(ql, qr));
-    planes[5 * plane + o] = (uint8_t)max(qc, max(ql, qr));
+    // Sobel column sums h(c) = 2 r[c] + n[c] + s[c] for c = x0 - 2 .. x0 + 5 (clamped reads: values outside are never used)
+    int h[8], q[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int c = min(max(x0 - 2 + k, 0), W - 1);
+        q[k] = r[c];
+        h[k] = 2 * q[k] + (int)n[c] + (int)s[c];
+    }
+    // p / q at x0 - 1 .. x0 + 4 (index k = x - x0 + 1); border columns hold ftzero
+    int pv[6], qv[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const int x = x0 - 1 + k;
+        const bool border = x <= 0 || x >= W - 1;
+        pv[k] = border ? ftzero : max(-ftzero, min(ftzero, h[k + 2] - h[k])) + ftzero;
+        qv[k] = border ? ftzero : q[k + 1];
+    }
+    uint32_t out[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int x = x0 + k;
+        const int pc = pv[k + 1], qc = qv[k + 1];
+        int pl = pc, pr = pc, ql = qc, qr = qc;
+        if (x > 0) { pl = (pc + pv[k]) >> 1; ql = (qc + qv[k]) >> 1; }
+        if (x < W - 1) { pr = (pc + pv[k + 2]) >> 1; qr = (qc + qv[k + 2]) >> 1; }
+        out[0] |= (uint32_t)pc << (8 * k);
+        out[1] |= (uint32_t)min(pc, min(pl, pr)) << (8 * k);
+        out[2] |= (uint32_t)max(pc, max(pl, pr)) << (8 * k);
+        out[3] |= (uint32_t)qc << (8 * k);
+        out[4] |= (uint32_t)min(qc, min(ql, qr)) << (8 * k);
+        out[5] |= (uint32_t)max(qc, max(ql, qr)) << (8 * k);
+    }
+    const size_t plane = (size_t)W * H, o = (size_t)y * W + x0;
+    if ((W & 3) == 0) {
+#pragma unroll
+        for (int pl_ = 0; pl_ < 6; ++pl_) *(uint32_t*)(planes + pl_ * plane + o) = out[pl_];
+    } else {
+        const int cnt = min(4, W - x0);
+#pragma unroll
+        for (int pl_ = 0; pl_ < 6; ++pl_)
+            for (int k = 0; k < cnt; ++k) planes[pl_ * plane + o + k] = (uint8_t)(out[pl_] >> (8 * k));
+    }
 }
 
 __global__ void prefilter_kernel(const uint8_t* __restrict__ img, int W, int H, int ftzero, uint8_t* __restrict__ planes)
@@ -372,7 +405,7 @@ int sgbm_cost_volume_batch_dev(mvs_ctx* ctx, const SgbmGeom& g, int F, const uin
     {
         PrefilterBatch pb;
         for (int f = 0; f < F; ++f) { pb.img[f] = l[f]; pb.img[F + f] = r[f]; }
-        prefilter_batch_kernel<<<dim3(cdiv(g.W, 128), g.H, 2 * F), 128, 0, s>>>(pb, g.W, g.H, g.ftzero, planes);
+        prefilter_batch_kernel<<<dim3(cdiv(g.W, 4 * 128), g.H, 2 * F), 128, 0, s>>>(pb, g.W, g.H, g.ftzero, planes);
         MVS_LAUNCH_CHECK(ctx, "prefilter_batch_kernel");
     }
     for (int k = 0; k <= F; ++k) {
